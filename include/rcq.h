@@ -1,0 +1,134 @@
+/*
+ * rcq.h — C ABI of librnaclique_b200.so, the B200-native replacement for RNA-clique's
+ * all-vs-all hot path.  Every entry point cites the reference interface it replaces
+ * (paths are under the upstream repository, actapia/rna_clique @ a55e40a).
+ *
+ * Conventions: every function returns 0 on success or a negative rcq_status; the message
+ * of the last failure on the calling thread is returned by rcq_last_error().  Nothing
+ * throws across the boundary.  Host buffers are caller-owned; handles (rcq_ctx, rcq_sample,
+ * rcq_table) are library-owned device objects released with the matching *_free call.
+ * One host thread per context.  No torch types appear in any signature.
+ */
+#ifndef RCQ_H
+#define RCQ_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    RCQ_OK = 0,
+    RCQ_ERR_CUDA = -1,      /* CUDA runtime failure (message has the CUDA error string) */
+    RCQ_ERR_ARG = -2,       /* bad argument */
+    RCQ_ERR_CAPACITY = -3,  /* an internal work list overflowed its hard cap */
+    RCQ_ERR_NO_IDEAL = -4   /* phase 2: some table restricted to ideal components is empty
+                               (reference: NoIdealComponentsError, filtered_distance.py:242-247) */
+} rcq_status;
+
+typedef struct rcq_ctx rcq_ctx;
+typedef struct rcq_sample rcq_sample;
+typedef struct rcq_table rcq_table;
+
+const char* rcq_last_error(void);
+int rcq_version(void);
+
+/* One context = one GPU + one stream + scratch arenas.  Replaces nothing in the reference
+ * (which has no device); plays the role of the joblib worker pool of find_all_pairs.py:224. */
+int rcq_ctx_create(int device, rcq_ctx** out);
+void rcq_ctx_destroy(rcq_ctx* ctx);
+int rcq_ctx_sync(rcq_ctx* ctx);
+/* cudaStream_t of the context, as void* (for timing with events on the launching stream). */
+void* rcq_ctx_stream(rcq_ctx* ctx);
+/* number of kernels this library launched on ctx since creation (bench.py's gpu_launches) */
+int64_t rcq_ctx_launches(rcq_ctx* ctx);
+
+/* ---- kernels (1)+(2): pack + seed index.  Replaces makeblastdb per sample
+ * (find_all_pairs.py:120-159 make_one_db/make_all_dbs -> BlastDBCache.makedb).
+ * ascii: concatenated nucleotide letters of the sample's top-gene transcripts (no newlines);
+ * offsets[n_seq+1]: start of each transcript in ascii; gene/iso: parsed FASTA ids
+ * (transcripts.py:60-126).  ascii_on_device!=0 means `ascii` is a device pointer. */
+int rcq_sample_create(rcq_ctx* ctx, const uint8_t* ascii, int ascii_on_device,
+                      const int64_t* offsets, const int32_t* gene, const int32_t* iso,
+                      int32_t n_seq, rcq_sample** out);
+void rcq_sample_free(rcq_sample* s);
+/* info[0]=n_seq, [1]=total bases, [2]=arena bases (padded), [3]=#index entries, [4]=#masked bases */
+int rcq_sample_info(const rcq_sample* s, int64_t info[5]);
+/* test hooks: copy the packed arenas / index back.  Any pointer may be NULL.
+ * fwd/rc: 2-bit words (arena_bases/16 uint32 each); mask: arena_bases/32 uint32;
+ * arena_off: int64[n_seq]; index: uint64[#entries] = hash<<32 | pos<<1 | orient */
+int rcq_sample_download(const rcq_sample* s, uint32_t* fwd, uint32_t* rc, uint32_t* mask,
+                        int64_t* arena_off, uint64_t* index);
+
+/* ---- kernel (3) + table assembly.  One UNORDERED sample pair: both blastn directions
+ * (find_homologs.py:82-133 gene_matches, :124 TabularBlastnSearch), the per-query-gene
+ * best-bitscore reduction (:135-164) and HomologFinder.get_match_table (:215-302).
+ * s1 plays transcripts1 (ssample side), s2 transcripts2 (qsample side). */
+typedef struct {
+    int64_t n_candidates;   /* minimizer join matches examined */
+    int64_t n_seeds;        /* exact runs >= 28 that triggered an ungapped extension */
+    int64_t n_ungapped;     /* distinct ungapped HSPs */
+    int64_t n_gapped;       /* gapped HSPs produced */
+    int64_t dp_cells;       /* DP cells evaluated by the gapped kernel */
+    int64_t ungapped_cells; /* base comparisons of the ungapped stage */
+    int64_t n_fwd, n_bwd;   /* rows of the two direction tables after best-hit selection */
+    int64_t n_rows;         /* rows of the gene-matches table */
+    int64_t band_retries;   /* gapped extensions re-run with a wider band */
+} rcq_search_stats;
+
+int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sample* s2, double evalue,
+                    int32_t top_n, int32_t keep_all, rcq_table** out, rcq_search_stats* stats);
+
+/* Gene-matches table columns (docs/formats.md:231-252), structure of arrays. */
+typedef struct {
+    int32_t *length, *mismatch, *gapopen, *qstart, *qend, *sstart, *send;
+    int32_t *score;         /* raw alignment score; bitscore/evalue/pident derive from it on the host */
+    int32_t *gaps, *nident;
+    int32_t *qgene, *qiso, *sgene, *siso;
+    int32_t *qlen;          /* length of the BLAST query transcript of that row (for evalue) */
+    uint8_t *minus;         /* sstrand == "minus" */
+    uint8_t *reverse;       /* row came from the reverse search (find_homologs.py:239,246) */
+} rcq_table_cols;
+int64_t rcq_table_rows(const rcq_table* t);
+int rcq_table_download(const rcq_table* t, rcq_table_cols* host_cols);
+void rcq_table_free(rcq_table* t);
+/* test hook: the symmetric gapped-HSP set of the last rcq_search_pair on ctx, 12 int32 per HSP:
+ * tx1, tx2, minus, q0, q1, s0, s1 (0-based half-open, s on the strand given), score2 (doubled
+ * score), mismatch, gaps, gapopen, nident.  Returns the count; copies min(count, cap) rows. */
+int64_t rcq_debug_last_hsps(rcq_ctx* ctx, int32_t* out, int64_t cap);
+/* Karlin-Altschul helpers shared by the host layer (blastn 1/-2 linear-gap parameters):
+ * length adjustment and evalue of a raw score for query length m against a db (n bases, nseq). */
+int32_t rcq_length_adjustment(int64_t m, int64_t n, int64_t nseq);
+double rcq_evalue(int32_t score, int64_t m, int64_t n, int64_t nseq);
+double rcq_bitscore(int32_t score);
+
+/* ---- kernel (4): gene-match graph, ideal components, per-table reductions.
+ * Replaces build_graph.py:40-68, filtered_distance.py:25-39,171-210,234-247 and
+ * similarity_computer.py:21-42.  Node id = sample_index*stride + gene.
+ * Rows of all tables are concatenated; table k owns rows [row_off[k], row_off[k+1]) and
+ * joins samples t_s[k] (ssample) and t_q[k] (qsample).  sample_count<=0 => count the samples
+ * present in the graph (filtered_distance.py:171-182).
+ * Outputs: nident_sum/denom_sum int64[n_tables] (denom = sum(length) - sum(gaps) over
+ * restricted rows); valid uint8[n_samples*stride] (may be NULL); counts[0]=#components,
+ * [1]=#ideal components, [2]=sample_count used, [3]=#nodes, [4]=#unique edges.
+ * Returns RCQ_ERR_NO_IDEAL when some denom_sum is 0 (sums are still filled in). */
+int rcq_phase2_host(rcq_ctx* ctx, int32_t n_samples, int64_t stride, int32_t n_tables,
+                    const int64_t* row_off, const int32_t* t_s, const int32_t* t_q,
+                    const int32_t* sgene, const int32_t* qgene, const int32_t* nident,
+                    const int32_t* length, const int32_t* gaps, int32_t sample_count,
+                    int64_t* nident_sum, int64_t* denom_sum, uint8_t* valid, int64_t counts[5]);
+/* Same, fed from device-resident tables produced by rcq_search_pair (no host round trip). */
+int rcq_phase2_tables(rcq_ctx* ctx, int32_t n_samples, int64_t stride, int32_t n_tables,
+                      const rcq_table* const* tables, const int32_t* t_s, const int32_t* t_q,
+                      int32_t sample_count, int64_t* nident_sum, int64_t* denom_sum,
+                      uint8_t* valid, int64_t counts[5]);
+
+/* ---- multi-GPU exchange: serialise a table to / from a flat int32 buffer that the
+ * host layer all-gathers with NCCL (torch.distributed) — device pointers in, device pointers out. */
+int64_t rcq_table_flat_words(const rcq_table* t);
+int rcq_table_flatten(rcq_ctx* ctx, const rcq_table* t, int32_t* dev_out);
+int rcq_table_from_flat(rcq_ctx* ctx, const int32_t* dev_in, int64_t n_rows, rcq_table** out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,143 @@
+// api_sample.cu — context lifetime and rcq_sample_* entry points of the C ABI (include/rcq.h).
+#include "sample.cuh"
+
+thread_local std::string g_rcq_err;
+
+int rcq_sample_build(rcq_ctx* ctx, rcq_sample* s, const uint8_t* d_ascii, int64_t ascii_len,
+                     const int64_t* d_offsets);  // sample.cu
+
+extern "C" {
+
+const char* rcq_last_error(void) { return g_rcq_err.c_str(); }
+int rcq_version(void) { return 1; }
+
+int rcq_ctx_create(int device, rcq_ctx** out) {
+    if (!out) return rcq_fail(RCQ_ERR_ARG, "rcq_ctx_create: out is NULL");
+    int n = 0;
+    CU(cudaGetDeviceCount(&n));
+    if (device < 0 || device >= n) return rcq_fail(RCQ_ERR_ARG, "rcq_ctx_create: no such device");
+    CU(cudaSetDevice(device));
+    rcq_ctx* c = new rcq_ctx();
+    c->device = device;
+    CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CU(cudaMallocHost((void**)&c->h_pin, 64 * sizeof(int64_t)));
+    CU(cudaMalloc((void**)&c->d_ctr, 64 * sizeof(int64_t)));
+    cudaMemPool_t pool;
+    CU(cudaDeviceGetDefaultMemPool(&pool, device));
+    uint64_t thr = UINT64_MAX;  // keep freed blocks in the pool: no OS round trips per pair
+    CU(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
+    *out = c;
+    return 0;
+}
+
+void rcq_ctx_destroy(rcq_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    if (c->dbg_hsp) cudaFree(c->dbg_hsp);
+    cudaFreeHost(c->h_pin);
+    cudaFree(c->d_ctr);
+    cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int rcq_ctx_sync(rcq_ctx* c) {
+    CU(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+void* rcq_ctx_stream(rcq_ctx* c) { return (void*)c->stream; }
+int64_t rcq_ctx_launches(rcq_ctx* c) { return c->launches; }
+
+int rcq_sample_create(rcq_ctx* ctx, const uint8_t* ascii, int ascii_on_device,
+                      const int64_t* offsets, const int32_t* gene, const int32_t* iso,
+                      int32_t n_seq, rcq_sample** out) {
+    if (!ctx || !out || n_seq < 0 || (n_seq > 0 && (!ascii || !offsets || !gene || !iso)))
+        return rcq_fail(RCQ_ERR_ARG, "rcq_sample_create: bad argument");
+    CU(cudaSetDevice(ctx->device));
+    rcq_sample* s = new rcq_sample();
+    s->ctx = ctx;
+    s->n_seq = n_seq;
+    // arena offsets on the host (n_seq is small): every transcript starts on a 32-base boundary
+    std::vector<int32_t> aoff(n_seq > 0 ? n_seq : 1), len(n_seq > 0 ? n_seq : 1);
+    int64_t pos = 64, total = 0;
+    int32_t max_len = 0;
+    for (int32_t t = 0; t < n_seq; t++) {
+        int64_t l = offsets[t + 1] - offsets[t];
+        if (l < 0 || l > 0x3fffffff) { delete s; return rcq_fail(RCQ_ERR_ARG, "rcq_sample_create: bad offsets"); }
+        aoff[t] = (int32_t)pos;
+        len[t] = (int32_t)l;
+        if (l > max_len) max_len = (int32_t)l;
+        total += l;
+        pos = (pos + l + 31) & ~31ll;
+        if (pos > 0x7ffffff0ll - 256) { delete s; return rcq_fail(RCQ_ERR_ARG, "rcq_sample_create: sample exceeds 2^31 bases"); }
+    }
+    s->total = total;
+    s->max_len = max_len;
+    s->arena = ((pos + 63) & ~63ll) + 128;
+    int64_t ascii_len = n_seq ? offsets[n_seq] : 0;
+    int64_t base0 = n_seq ? offsets[0] : 0;
+    const uint8_t* d_ascii = ascii;
+    uint8_t* own_ascii = nullptr;
+    int64_t* d_offsets = nullptr;
+    RC(dalloc(ctx, &d_offsets, n_seq + 1));
+    if (!ascii_on_device && n_seq) {
+        RC(dalloc(ctx, &own_ascii, ascii_len - base0 + 64));
+        CU(cudaMemcpyAsync(own_ascii, ascii + base0, ascii_len - base0, cudaMemcpyHostToDevice, ctx->stream));
+        d_ascii = own_ascii - base0;  // so that offsets index it directly
+    }
+    if (n_seq) CU(cudaMemcpyAsync(d_offsets, offsets, (n_seq + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, ctx->stream));
+    RC(dalloc(ctx, &s->off, n_seq));
+    RC(dalloc(ctx, &s->len, n_seq));
+    RC(dalloc(ctx, &s->gene, n_seq));
+    RC(dalloc(ctx, &s->iso, n_seq));
+    if (n_seq) {
+        CU(cudaMemcpyAsync(s->off, aoff.data(), n_seq * 4, cudaMemcpyHostToDevice, ctx->stream));
+        CU(cudaMemcpyAsync(s->len, len.data(), n_seq * 4, cudaMemcpyHostToDevice, ctx->stream));
+        CU(cudaMemcpyAsync(s->gene, gene, n_seq * 4, cudaMemcpyHostToDevice, ctx->stream));
+        CU(cudaMemcpyAsync(s->iso, iso, n_seq * 4, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    int rc = rcq_sample_build(ctx, s, d_ascii, ascii_len, d_offsets);
+    // the host staging vectors (aoff, len) must outlive the async copies
+    cudaStreamSynchronize(ctx->stream);
+    dfree(ctx, own_ascii);
+    dfree(ctx, d_offsets);
+    if (rc) { rcq_sample_free(s); return rc; }
+    *out = s;
+    return 0;
+}
+
+void rcq_sample_free(rcq_sample* s) {
+    if (!s) return;
+    rcq_ctx* c = s->ctx;
+    cudaSetDevice(c->device);
+    dfree(c, s->fwd); dfree(c, s->rc); dfree(c, s->mask); dfree(c, s->mask_rc);
+    dfree(c, s->off); dfree(c, s->len); dfree(c, s->gene); dfree(c, s->iso);
+    dfree(c, s->index); dfree(c, s->dir);
+    delete s;
+}
+
+int rcq_sample_info(const rcq_sample* s, int64_t info[5]) {
+    if (!s || !info) return rcq_fail(RCQ_ERR_ARG, "rcq_sample_info: bad argument");
+    info[0] = s->n_seq; info[1] = s->total; info[2] = s->arena; info[3] = s->n_index; info[4] = s->n_masked;
+    return 0;
+}
+
+int rcq_sample_download(const rcq_sample* s, uint32_t* fwd, uint32_t* rc, uint32_t* mask,
+                        int64_t* arena_off, uint64_t* index) {
+    if (!s) return rcq_fail(RCQ_ERR_ARG, "rcq_sample_download: bad argument");
+    rcq_ctx* c = s->ctx;
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    if (fwd) CU(cudaMemcpy(fwd, s->fwd, s->arena / 16 * 4, cudaMemcpyDeviceToHost));
+    if (rc) CU(cudaMemcpy(rc, s->rc, s->arena / 16 * 4, cudaMemcpyDeviceToHost));
+    if (mask) CU(cudaMemcpy(mask, s->mask, s->arena / 32 * 4, cudaMemcpyDeviceToHost));
+    if (arena_off && s->n_seq) {
+        std::vector<int32_t> t(s->n_seq);
+        CU(cudaMemcpy(t.data(), s->off, s->n_seq * 4, cudaMemcpyDeviceToHost));
+        for (int i = 0; i < s->n_seq; i++) arena_off[i] = t[i];
+    }
+    if (index && s->n_index) CU(cudaMemcpy(index, s->index, s->n_index * 8, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,97 @@
+// common.cuh — context, error plumbing and device-buffer helpers shared by the kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <string>
+#include <vector>
+#include "../../include/rcq.h"
+
+#define RCQ_SMS 148  // B200: grids are sized in multiples of the SM count
+
+extern thread_local std::string g_rcq_err;
+
+static inline int rcq_fail(int code, const char* fmt, const char* a = "", const char* b = "") {
+    char buf[512];
+    snprintf(buf, sizeof buf, fmt, a, b);
+    g_rcq_err = buf;
+    return code;
+}
+
+#define CU(x)                                                                             \
+    do {                                                                                  \
+        cudaError_t e_ = (x);                                                             \
+        if (e_ != cudaSuccess) {                                                          \
+            char b_[512];                                                                 \
+            snprintf(b_, sizeof b_, "%s:%d: %s: %s", __FILE__, __LINE__, #x,              \
+                     cudaGetErrorString(e_));                                             \
+            g_rcq_err = b_;                                                               \
+            return RCQ_ERR_CUDA;                                                          \
+        }                                                                                 \
+    } while (0)
+#define RC(x)                     \
+    do {                          \
+        int r_ = (x);             \
+        if (r_ != 0) return r_;   \
+    } while (0)
+
+struct rcq_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    int64_t launches = 0;
+    // pinned staging for small device->host result reads
+    int64_t* h_pin = nullptr;  // 64 int64
+    int64_t* d_ctr = nullptr;  // 64 int64 device counters
+    // debug: gapped HSPs of the last search (device, 12 int32 each)
+    int32_t* dbg_hsp = nullptr;
+    int64_t dbg_n = 0;
+};
+
+// stream-ordered device allocation (pool keeps memory; no OS round trips in steady state)
+template <typename T>
+static inline int dalloc(rcq_ctx* c, T** p, int64_t n) {
+    if (n < 1) n = 1;
+    CU(cudaMallocAsync((void**)p, (size_t)n * sizeof(T), c->stream));
+    return 0;
+}
+template <typename T>
+static inline void dfree(rcq_ctx* c, T* p) {
+    if (p) cudaFreeAsync((void*)p, c->stream);
+}
+
+#define LAUNCH(ctx, kern, grid, block, smem, ...)                       \
+    do {                                                                \
+        kern<<<(grid), (block), (smem), (ctx)->stream>>>(__VA_ARGS__);  \
+        (ctx)->launches++;                                              \
+        CU(cudaGetLastError());                                         \
+    } while (0)
+
+static inline int grid_for(int64_t n, int block, int per_thread = 1) {
+    int64_t g = (n + (int64_t)block * per_thread - 1) / ((int64_t)block * per_thread);
+    if (g < 1) g = 1;
+    if (g > (1 << 30)) g = 1 << 30;
+    return (int)g;
+}
+
+// ---- scoring constants (blastn megablast defaults) -------------------
+// Scores are kept doubled inside the gapped kernel so the linear gap cost 2.5 is integral.
+#define RCQ_WORD 28          // contiguous exact seed length
+#define RCQ_KMER 16          // minimizer k-mer (any 28-mer window holds 13 of them)
+#define RCQ_WIN 13           // RCQ_WORD - RCQ_KMER + 1
+#define RCQ_XDROP_UNGAPPED 10   // 20 bits  -> floor(20 ln2 / 1.28)
+#define RCQ_XDROP_GAPPED2 108   // 100 bits -> floor(100 ln2 / 1.28) = 54, doubled
+#define RCQ_MATCH2 2
+#define RCQ_MISMATCH2 (-4)
+#define RCQ_GAP2 (-5)
+#define RCQ_MAX_GAPPED_PER_GROUP 32
+#define RCQ_KA_LAMBDA 1.28
+#define RCQ_KA_K 0.46
+#define RCQ_KA_ALPHA 1.5
+#define RCQ_KA_BETA (-2.0)
+
+// invertible 32-bit mixer (so equal hashes <=> equal k-mers): murmur3 finaliser
+__host__ __device__ static inline uint32_t rcq_mix32(uint32_t x) {
+    x ^= x >> 16; x *= 0x85ebca6bu; x ^= x >> 13; x *= 0xc2b2ae35u; x ^= x >> 16;
+    return x;
+}

@@ -1,0 +1,256 @@
+// sample.cu — kernels (1) and (2): 2-bit packing of a sample's top-gene transcripts and the
+// sorted minimizer seed index.  Replaces `makeblastdb` per sample
+// (reference find_all_pairs.py:120-159).  HBM-bound streaming kernels; algorithmic bytes:
+//   pack   : 1 B/nt read + 0.25 B/nt written (+0.25 rc +2x1/32 masks)
+//   index  : 0.25 B/nt read, 8 B per selected minimizer written, then an 8-B-key radix sort.
+#include <cub/cub.cuh>
+#include "sample.cuh"
+
+#define GUARD_FRONT 64
+#define GUARD_BACK 128
+
+__device__ __forceinline__ uint32_t base_code(uint32_t c) {  // 0..3, or 4 = not ACGT(U)
+    uint32_t u = c & 0xDFu;
+    return u == 'A' ? 0u : u == 'C' ? 1u : u == 'G' ? 2u : (u == 'T' || u == 'U') ? 3u : 4u;
+}
+
+// Warp per transcript.  Each lane turns 16 letters into one 2-bit word per iteration; the 16
+// letters come from two aligned 16-byte vector loads funnel-shifted to the transcript's byte
+// alignment (coalesced: a warp iteration reads one contiguous 512(+16)-byte span).
+__global__ void k_pack(const uint8_t* __restrict__ ascii, int64_t ascii_len,
+                       const int64_t* __restrict__ offsets, const int32_t* __restrict__ aoff,
+                       int32_t n_seq, uint32_t* __restrict__ fwd, uint32_t* __restrict__ mask,
+                       unsigned long long* __restrict__ n_masked) {
+    int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    int nwarps = (gridDim.x * blockDim.x) >> 5;
+    for (int t = warp; t < n_seq; t += nwarps) {
+        int64_t src = offsets[t];
+        int32_t n = (int32_t)(offsets[t + 1] - src);
+        int64_t dst = aoff[t];
+        unsigned long long masked = 0;
+        for (int32_t c = 0; c < n; c += 512) {
+            int32_t b0 = c + lane * 16;
+            uint32_t word = 0, mbits = 0;
+            if (b0 < n) {
+                int64_t a = src + b0;
+                uint64_t A, B;  // the 16 letters, little-endian
+                int64_t al = a & ~15ll;
+                if (al + 32 <= ascii_len && (((uintptr_t)ascii) & 15) == 0) {
+                    uint4 v0 = __ldg((const uint4*)(ascii + al));
+                    uint4 v1 = __ldg((const uint4*)(ascii + al + 16));
+                    uint64_t q0 = ((uint64_t)v0.y << 32) | v0.x, q1 = ((uint64_t)v0.w << 32) | v0.z;
+                    uint64_t q2 = ((uint64_t)v1.y << 32) | v1.x, q3 = ((uint64_t)v1.w << 32) | v1.z;
+                    int s = (int)(a - al);
+                    if (s >= 8) { q0 = q1; q1 = q2; q2 = q3; s -= 8; }
+                    if (s == 0) { A = q0; B = q1; }
+                    else {
+                        A = (q0 >> (8 * s)) | (q1 << (64 - 8 * s));
+                        B = (q1 >> (8 * s)) | (q2 << (64 - 8 * s));
+                    }
+                } else {
+                    A = 0; B = 0;
+#pragma unroll
+                    for (int k = 0; k < 8; k++) {
+                        A |= (uint64_t)((a + k < ascii_len) ? ascii[a + k] : 'N') << (8 * k);
+                        B |= (uint64_t)((a + 8 + k < ascii_len) ? ascii[a + 8 + k] : 'N') << (8 * k);
+                    }
+                }
+                int lim = min(16, n - b0);
+#pragma unroll
+                for (int k = 0; k < 16; k++) {
+                    uint32_t chk = (uint32_t)((k < 8 ? A >> (8 * k) : B >> (8 * (k - 8))) & 0xFF);
+                    uint32_t code = (k < lim) ? base_code(chk) : 4u;
+                    if (code > 3u) {
+                        mbits |= 1u << k;
+                        if (k < lim) masked++;
+                    } else {
+                        word |= code << (2 * k);
+                    }
+                }
+                fwd[(dst + b0) >> 4] = word;
+            } else {
+                mbits = 0xFFFFu;
+            }
+            uint32_t other = __shfl_down_sync(0xffffffffu, mbits, 1);
+            if ((lane & 1) == 0 && b0 < n) mask[(dst + b0) >> 5] = mbits | (other << 16);
+        }
+        for (int o = 16; o; o >>= 1) masked += __shfl_down_sync(0xffffffffu, masked, o);
+        if (lane == 0 && masked) atomicAdd(n_masked, masked);
+    }
+}
+
+__device__ __forceinline__ uint32_t rev2_32(uint32_t x) {  // reverse the 16 2-bit groups
+    x = __brev(x);
+    return ((x >> 1) & 0x55555555u) | ((x & 0x55555555u) << 1);
+}
+
+// Per-transcript reverse complement of the packed arena (and of the mask).
+__global__ void k_revcomp(const uint32_t* __restrict__ fwd, const uint32_t* __restrict__ mask,
+                          const int32_t* __restrict__ aoff, const int32_t* __restrict__ len,
+                          int32_t n_seq, uint32_t* __restrict__ rc, uint32_t* __restrict__ mrc) {
+    int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    int nwarps = (gridDim.x * blockDim.x) >> 5;
+    for (int t = warp; t < n_seq; t += nwarps) {
+        int64_t off = aoff[t];
+        int32_t n = len[t];
+        int32_t nw = (n + 15) >> 4;
+        for (int32_t w = lane; w < nw; w += 32) {
+            int32_t q = n - 16 * w - 16;
+            uint32_t x = (uint32_t)fetch32(fwd, off + max(q, 0));
+            int v = 16;
+            if (q < 0) { v = 16 + q; x <<= 2 * (16 - v); }
+            uint32_t r = ~rev2_32(x);
+            if (v < 16) r &= (1u << (2 * v)) - 1u;
+            rc[(off >> 4) + w] = r;
+        }
+        int32_t nm = (n + 31) >> 5;
+        for (int32_t w = lane; w < nm; w += 32) {
+            int32_t q = n - 32 * w - 32;
+            uint32_t x = fetchmask32(mask, off + max(q, 0));
+            int v = 32;
+            if (q < 0) { v = 32 + q; x <<= (32 - v); }
+            uint32_t r = __brev(x);
+            if (v < 32) r |= ~((1u << v) - 1u);
+            mrc[(off >> 5) + w] = r;
+        }
+    }
+}
+
+// Canonical-16-mer hash at arena position p (0xFFFFFFFF = contains a masked base).
+__device__ __forceinline__ uint32_t kmer_hash(const uint32_t* fwd, const uint32_t* mask, int64_t p,
+                                              uint32_t* orient) {
+    if (fetchmask32(mask, p) & 0xFFFFu) return 0xFFFFFFFFu;
+    uint32_t f = (uint32_t)fetch32(fwd, p);
+    uint32_t r = rev2_32(~f);
+    uint32_t hf = rcq_mix32(f), hr = rcq_mix32(r);
+    *orient = hr < hf;
+    uint32_t h = min(hf, hr);
+    return min(h, 0xFFFFFFFEu);
+}
+
+// Window-minimizer selection (window = 13 consecutive 16-mers = one 28-mer).  Position p is
+// selected iff its hash equals the minimum of SOME window containing it (all tied minima are
+// kept, so the choice is symmetric under reverse complement).  Warp per transcript.
+template <bool FILL>
+__global__ void k_minimizers(const uint32_t* __restrict__ fwd, const uint32_t* __restrict__ mask,
+                             const int32_t* __restrict__ aoff, const int32_t* __restrict__ len,
+                             int32_t n_seq, unsigned long long* __restrict__ counter,
+                             uint64_t* __restrict__ out) {
+    __shared__ uint32_t sh[8][256 + 8];
+    __shared__ uint8_t so[8][256 + 8];
+    int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    int warp = blockIdx.x * (blockDim.x >> 5) + wib;
+    int nwarps = gridDim.x * (blockDim.x >> 5);
+    const int T = 224, H = RCQ_WIN - 1;  // tile and halo
+    for (int t = warp; t < n_seq; t += nwarps) {
+        int64_t off = aoff[t];
+        int32_t nk = len[t] - RCQ_KMER + 1;
+        if (nk < RCQ_WIN) continue;
+        for (int32_t c = 0; c < nk; c += T) {
+            __syncwarp();
+            for (int i = lane; i < T + 2 * H; i += 32) {
+                int32_t p = c - H + i;
+                uint32_t o = 0, h = 0xFFFFFFFFu;
+                if (p >= 0 && p < nk) h = kmer_hash(fwd, mask, off + p, &o);
+                sh[wib][i] = h;
+                so[wib][i] = (uint8_t)o;
+            }
+            __syncwarp();
+            for (int i0 = 0; i0 < T; i0 += 32) {
+                int i = i0 + lane;
+                int32_t p = c + i;
+                bool sel = false;
+                uint32_t h = 0xFFFFFFFFu;
+                if (i < T && p < nk) {
+                    h = sh[wib][i + H];
+                    if (h != 0xFFFFFFFFu) {
+                        int a = 0, b = 0;
+                        int amax = min(H, p), bmax = min(H, nk - 1 - p);
+                        while (a < amax && sh[wib][i + H - a - 1] >= h) a++;
+                        while (b < bmax && sh[wib][i + H + b + 1] >= h) b++;
+                        sel = (H - b) <= a;  // some window [p-j, p-j+12], j<=a, 12-j<=b
+                    }
+                }
+                unsigned m = __ballot_sync(0xffffffffu, sel);
+                if (m) {
+                    unsigned long long base = 0;
+                    if (lane == 0) base = atomicAdd(counter, (unsigned long long)__popc(m));
+                    base = __shfl_sync(0xffffffffu, base, 0);
+                    if (FILL && sel) {
+                        unsigned long long pos = (unsigned long long)(off + p);
+                        out[base + __popc(m & ((1u << lane) - 1u))] =
+                            ((unsigned long long)h << 32) | (pos << 1) | so[wib][i + H];
+                    }
+                }
+            }
+        }
+    }
+}
+
+__global__ void k_build_dir(const uint64_t* __restrict__ index, int64_t n, uint32_t* __restrict__ dir) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t nb = 1u << RCQ_DIRBITS;
+    if (i > n) return;
+    uint32_t lo = (i == 0) ? 0u : (uint32_t)(index[i - 1] >> (64 - RCQ_DIRBITS)) + 1u;
+    uint32_t hi = (i == n) ? nb : (uint32_t)(index[i] >> (64 - RCQ_DIRBITS));
+    for (uint32_t b = lo; b <= hi; b++) dir[b] = (uint32_t)i;
+}
+
+static int sort_u64(rcq_ctx* ctx, uint64_t* keys, int64_t n) {
+    if (n <= 1) return 0;
+    uint64_t* tmp = nullptr;
+    RC(dalloc(ctx, &tmp, n));
+    cub::DoubleBuffer<uint64_t> db(keys, tmp);
+    size_t bytes = 0;
+    CU(cub::DeviceRadixSort::SortKeys(nullptr, bytes, db, (int)n, 0, 64, ctx->stream));
+    void* ws = nullptr;
+    CU(cudaMallocAsync(&ws, bytes, ctx->stream));
+    CU(cub::DeviceRadixSort::SortKeys(ws, bytes, db, (int)n, 0, 64, ctx->stream));
+    ctx->launches += 8;
+    if (db.Current() != keys)
+        CU(cudaMemcpyAsync(keys, db.Current(), n * sizeof(uint64_t), cudaMemcpyDeviceToDevice,
+                           ctx->stream));
+    cudaFreeAsync(ws, ctx->stream);
+    dfree(ctx, tmp);
+    return 0;
+}
+int rcq_sort_u64(rcq_ctx* ctx, uint64_t* keys, int64_t n) { return sort_u64(ctx, keys, n); }
+
+// Pack + reverse complement + minimizer index for one sample (stream-ordered).
+int rcq_sample_build(rcq_ctx* ctx, rcq_sample* s, const uint8_t* d_ascii, int64_t ascii_len,
+                     const int64_t* d_offsets) {
+    int64_t words = s->arena / 16, mwords = s->arena / 32;
+    RC(dalloc(ctx, &s->fwd, words));
+    RC(dalloc(ctx, &s->rc, words));
+    RC(dalloc(ctx, &s->mask, mwords));
+    RC(dalloc(ctx, &s->mask_rc, mwords));
+    RC(dalloc(ctx, &s->dir, (1ll << RCQ_DIRBITS) + 1));
+    CU(cudaMemsetAsync(s->fwd, 0, words * 4, ctx->stream));
+    CU(cudaMemsetAsync(s->rc, 0, words * 4, ctx->stream));
+    CU(cudaMemsetAsync(s->mask, 0xFF, mwords * 4, ctx->stream));
+    CU(cudaMemsetAsync(s->mask_rc, 0xFF, mwords * 4, ctx->stream));
+    unsigned long long* ctr = (unsigned long long*)ctx->d_ctr;
+    CU(cudaMemsetAsync(ctr, 0, 2 * sizeof(unsigned long long), ctx->stream));
+    int blocks = RCQ_SMS * 8;
+    if (s->n_seq) {
+        LAUNCH(ctx, k_pack, blocks, 256, 0, d_ascii, ascii_len, d_offsets, s->off, s->n_seq, s->fwd,
+               s->mask, ctr);
+        LAUNCH(ctx, k_revcomp, blocks, 256, 0, s->fwd, s->mask, s->off, s->len, s->n_seq, s->rc,
+               s->mask_rc);
+        LAUNCH(ctx, k_minimizers<false>, blocks, 256, 0, s->fwd, s->mask, s->off, s->len, s->n_seq,
+               ctr + 1, (uint64_t*)nullptr);
+    }
+    CU(cudaMemcpyAsync(ctx->h_pin, ctr, 2 * sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    s->n_masked = ctx->h_pin[0];
+    s->n_index = ctx->h_pin[1];
+    RC(dalloc(ctx, &s->index, s->n_index));
+    if (s->n_index) {
+        CU(cudaMemsetAsync(ctr + 1, 0, sizeof(unsigned long long), ctx->stream));
+        LAUNCH(ctx, k_minimizers<true>, blocks, 256, 0, s->fwd, s->mask, s->off, s->len, s->n_seq,
+               ctr + 1, s->index);
+        RC(sort_u64(ctx, s->index, s->n_index));
+    }
+    LAUNCH(ctx, k_build_dir, grid_for(s->n_index + 1, 256), 256, 0, s->index, s->n_index, s->dir);
+    return 0;
+}
