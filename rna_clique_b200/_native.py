@@ -1,0 +1,241 @@
+"""ctypes loader for librnaclique_b200.so (the C ABI declared in include/rcq.h).
+
+There is no CPU fallback: if the library is missing, or no CUDA device is present, every
+entry point that needs the GPU raises."""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+import numpy as np
+
+HERE = Path(__file__).resolve().parent
+LIB_PATH = HERE / "librnaclique_b200.so"
+
+TABLE_COLS = ["length", "mismatch", "gapopen", "qstart", "qend", "sstart", "send", "score", "gaps",
+              "nident", "qgene", "qiso", "sgene", "siso", "qlen"]
+HSP_COLS = ["tx1", "tx2", "minus", "a0", "a1", "b0", "b1", "score2", "mismatch", "gaps", "gapopen", "nident"]
+
+# every symbol include/rcq.h declares (checked by tests/test_abi.py)
+SYMBOLS = [
+    "rcq_last_error", "rcq_version", "rcq_ctx_create", "rcq_ctx_destroy", "rcq_ctx_sync", "rcq_ctx_stream",
+    "rcq_ctx_launches", "rcq_sample_create", "rcq_sample_free", "rcq_sample_info", "rcq_sample_download",
+    "rcq_search_pair", "rcq_table_rows", "rcq_table_download", "rcq_table_free", "rcq_debug_last_hsps",
+    "rcq_length_adjustment", "rcq_evalue", "rcq_bitscore", "rcq_phase2_host", "rcq_phase2_tables",
+    "rcq_table_flat_words", "rcq_table_flatten", "rcq_table_from_flat",
+]
+
+
+class RcqError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"librnaclique_b200 error {code}: {msg}")
+        self.code = code
+
+
+class NoIdealComponents(RcqError):
+    pass
+
+
+class SearchStats(C.Structure):
+    _fields_ = [(n, C.c_int64) for n in ["n_candidates", "n_seeds", "n_ungapped", "n_gapped", "dp_cells",
+                                         "ungapped_cells", "n_fwd", "n_bwd", "n_rows", "band_retries"]]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+class TableCols(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in TABLE_COLS] + [("minus", C.c_void_p), ("reverse", C.c_void_p)]
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not LIB_PATH.exists():
+            raise RuntimeError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                               "(there is no CPU fallback)")
+        L = C.CDLL(str(LIB_PATH))
+        vp, i32, i64, dbl = C.c_void_p, C.c_int32, C.c_int64, C.c_double
+        L.rcq_last_error.restype = C.c_char_p
+        L.rcq_ctx_create.argtypes = [C.c_int, C.POINTER(vp)]
+        L.rcq_ctx_destroy.argtypes = [vp]
+        L.rcq_ctx_destroy.restype = None
+        L.rcq_ctx_sync.argtypes = [vp]
+        L.rcq_ctx_stream.argtypes = [vp]
+        L.rcq_ctx_stream.restype = vp
+        L.rcq_ctx_launches.argtypes = [vp]
+        L.rcq_ctx_launches.restype = i64
+        L.rcq_sample_create.argtypes = [vp, vp, C.c_int, vp, vp, vp, i32, C.POINTER(vp)]
+        L.rcq_sample_free.argtypes = [vp]
+        L.rcq_sample_free.restype = None
+        L.rcq_sample_info.argtypes = [vp, vp]
+        L.rcq_sample_download.argtypes = [vp, vp, vp, vp, vp, vp]
+        L.rcq_search_pair.argtypes = [vp, vp, vp, dbl, i32, i32, C.POINTER(vp), C.POINTER(SearchStats)]
+        L.rcq_table_rows.argtypes = [vp]
+        L.rcq_table_rows.restype = i64
+        L.rcq_table_download.argtypes = [vp, C.POINTER(TableCols)]
+        L.rcq_table_free.argtypes = [vp]
+        L.rcq_table_free.restype = None
+        L.rcq_debug_last_hsps.argtypes = [vp, vp, i64]
+        L.rcq_debug_last_hsps.restype = i64
+        L.rcq_length_adjustment.argtypes = [i64, i64, i64]
+        L.rcq_length_adjustment.restype = i32
+        L.rcq_evalue.argtypes = [i32, i64, i64, i64]
+        L.rcq_evalue.restype = dbl
+        L.rcq_bitscore.argtypes = [i32]
+        L.rcq_bitscore.restype = dbl
+        L.rcq_phase2_host.argtypes = [vp, i32, i64, i32, vp, vp, vp, vp, vp, vp, vp, vp, i32, vp, vp, vp, vp]
+        L.rcq_phase2_tables.argtypes = [vp, i32, i64, i32, vp, vp, vp, i32, vp, vp, vp, vp]
+        L.rcq_table_flat_words.argtypes = [vp]
+        L.rcq_table_flat_words.restype = i64
+        L.rcq_table_flatten.argtypes = [vp, vp, vp]
+        L.rcq_table_from_flat.argtypes = [vp, vp, i64, C.POINTER(vp)]
+        _lib = L
+    return _lib
+
+
+def check(code: int):
+    if code != 0:
+        msg = lib().rcq_last_error().decode(errors="replace")
+        if code == -4:
+            raise NoIdealComponents(code, msg)
+        raise RcqError(code, msg)
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data
+
+
+class Context:
+    """One GPU + one stream (rcq_ctx)."""
+
+    def __init__(self, device: int = 0):
+        h = C.c_void_p()
+        check(lib().rcq_ctx_create(device, C.byref(h)))
+        self.h = h
+        self.device = device
+
+    def sync(self):
+        check(lib().rcq_ctx_sync(self.h))
+
+    @property
+    def stream(self) -> int:
+        return lib().rcq_ctx_stream(self.h)
+
+    @property
+    def launches(self) -> int:
+        return lib().rcq_ctx_launches(self.h)
+
+    def close(self):
+        if self.h:
+            lib().rcq_ctx_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Sample:
+    """Device-resident packed sample + seed index (rcq_sample)."""
+
+    def __init__(self, ctx: Context, ascii_, offsets, gene, iso, name: str = ""):
+        self.ctx = ctx
+        self.name = name
+        offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+        gene = np.ascontiguousarray(gene, dtype=np.int32)
+        iso = np.ascontiguousarray(iso, dtype=np.int32)
+        n = len(gene)
+        assert len(offsets) == n + 1 and len(iso) == n
+        on_device = 0
+        if hasattr(ascii_, "data_ptr"):  # torch tensor
+            if ascii_.is_cuda:
+                on_device, p = 1, ascii_.data_ptr()
+                self._keep = ascii_
+            else:
+                a = ascii_.numpy()
+                p, self._keep = a.ctypes.data, a
+        else:
+            a = np.ascontiguousarray(ascii_, dtype=np.uint8)
+            p, self._keep = a.ctypes.data, a
+        h = C.c_void_p()
+        check(lib().rcq_sample_create(ctx.h, p, on_device, offsets.ctypes.data, gene.ctypes.data,
+                                      iso.ctypes.data, n, C.byref(h)))
+        self.h = h
+        self._keep = None
+        info = np.zeros(5, dtype=np.int64)
+        check(lib().rcq_sample_info(self.h, info.ctypes.data))
+        self.n_seq, self.total, self.arena, self.n_index, self.n_masked = (int(x) for x in info)
+
+    def download(self):
+        fwd = np.zeros(self.arena // 16, dtype=np.uint32)
+        rc = np.zeros(self.arena // 16, dtype=np.uint32)
+        mask = np.zeros(self.arena // 32, dtype=np.uint32)
+        off = np.zeros(self.n_seq, dtype=np.int64)
+        index = np.zeros(self.n_index, dtype=np.uint64)
+        check(lib().rcq_sample_download(self.h, fwd.ctypes.data, rc.ctypes.data, mask.ctypes.data,
+                                        off.ctypes.data, index.ctypes.data))
+        return dict(fwd=fwd, rc=rc, mask=mask, off=off, index=index)
+
+    def close(self):
+        if getattr(self, "h", None) and self.ctx.h:
+            lib().rcq_sample_free(self.h)
+        self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Table:
+    """Device-resident gene-matches table (rcq_table)."""
+
+    def __init__(self, ctx: Context, h, stats=None):
+        self.ctx, self.h, self.stats = ctx, h, stats
+
+    def __len__(self):
+        return int(lib().rcq_table_rows(self.h))
+
+    def download(self) -> dict:
+        n = len(self)
+        cols = {c: np.zeros(n, dtype=np.int32) for c in TABLE_COLS}
+        cols["minus"] = np.zeros(n, dtype=np.uint8)
+        cols["reverse"] = np.zeros(n, dtype=np.uint8)
+        tc = TableCols(**{k: v.ctypes.data for k, v in cols.items()})
+        check(lib().rcq_table_download(self.h, C.byref(tc)))
+        return cols
+
+    def close(self):
+        if getattr(self, "h", None) and self.ctx.h:
+            lib().rcq_table_free(self.h)
+        self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def search_pair(ctx: Context, s1: Sample, s2: Sample, evalue: float = 1e-99, top_n: int = 1,
+                keep_all: bool = True) -> Table:
+    h = C.c_void_p()
+    st = SearchStats()
+    check(lib().rcq_search_pair(ctx.h, s1.h, s2.h, float(evalue), int(top_n), int(bool(keep_all)),
+                                C.byref(h), C.byref(st)))
+    return Table(ctx, h, st.as_dict())
+
+
+def debug_last_hsps(ctx: Context) -> np.ndarray:
+    n = lib().rcq_debug_last_hsps(ctx.h, None, 0)
+    out = np.zeros((n, 12), dtype=np.int32)
+    if n:
+        lib().rcq_debug_last_hsps(ctx.h, out.ctypes.data, n)
+    return out

@@ -1,4 +1,5 @@
 // api_sample.cu — context lifetime and rcq_sample_* entry points of the C ABI (include/rcq.h).
+#include <algorithm>
 #include "sample.cuh"
 
 thread_local std::string g_rcq_err;
@@ -90,7 +91,18 @@ int rcq_sample_create(rcq_ctx* ctx, const uint8_t* ascii, int ascii_on_device,
     RC(dalloc(ctx, &s->len, n_seq));
     RC(dalloc(ctx, &s->gene, n_seq));
     RC(dalloc(ctx, &s->iso, n_seq));
+    RC(dalloc(ctx, &s->gidx, n_seq));
+    std::vector<int32_t> gidx(n_seq > 0 ? n_seq : 1);
+    {
+        std::vector<int32_t> u(gene, gene + n_seq);
+        std::sort(u.begin(), u.end());
+        u.erase(std::unique(u.begin(), u.end()), u.end());
+        s->n_genes = (int32_t)u.size();
+        for (int32_t t = 0; t < n_seq; t++)
+            gidx[t] = (int32_t)(std::lower_bound(u.begin(), u.end(), gene[t]) - u.begin());
+    }
     if (n_seq) {
+        CU(cudaMemcpyAsync(s->gidx, gidx.data(), n_seq * 4, cudaMemcpyHostToDevice, ctx->stream));
         CU(cudaMemcpyAsync(s->off, aoff.data(), n_seq * 4, cudaMemcpyHostToDevice, ctx->stream));
         CU(cudaMemcpyAsync(s->len, len.data(), n_seq * 4, cudaMemcpyHostToDevice, ctx->stream));
         CU(cudaMemcpyAsync(s->gene, gene, n_seq * 4, cudaMemcpyHostToDevice, ctx->stream));
@@ -112,7 +124,7 @@ void rcq_sample_free(rcq_sample* s) {
     cudaSetDevice(c->device);
     dfree(c, s->fwd); dfree(c, s->rc); dfree(c, s->mask); dfree(c, s->mask_rc);
     dfree(c, s->off); dfree(c, s->len); dfree(c, s->gene); dfree(c, s->iso);
-    dfree(c, s->index); dfree(c, s->dir);
+    dfree(c, s->index); dfree(c, s->dir); dfree(c, s->sel); dfree(c, s->gidx);
     delete s;
 }
 

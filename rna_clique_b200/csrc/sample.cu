@@ -135,7 +135,7 @@ template <bool FILL>
 __global__ void k_minimizers(const uint32_t* __restrict__ fwd, const uint32_t* __restrict__ mask,
                              const int32_t* __restrict__ aoff, const int32_t* __restrict__ len,
                              int32_t n_seq, unsigned long long* __restrict__ counter,
-                             uint64_t* __restrict__ out) {
+                             uint64_t* __restrict__ out, uint32_t* __restrict__ selmap) {
     __shared__ uint32_t sh[8][256 + 8];
     __shared__ uint8_t so[8][256 + 8];
     int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -180,6 +180,7 @@ __global__ void k_minimizers(const uint32_t* __restrict__ fwd, const uint32_t* _
                         unsigned long long pos = (unsigned long long)(off + p);
                         out[base + __popc(m & ((1u << lane) - 1u))] =
                             ((unsigned long long)h << 32) | (pos << 1) | so[wib][i + H];
+                        atomicOr(selmap + (pos >> 5), 1u << (pos & 31));
                     }
                 }
             }
@@ -229,6 +230,8 @@ int rcq_sample_build(rcq_ctx* ctx, rcq_sample* s, const uint8_t* d_ascii, int64_
     CU(cudaMemsetAsync(s->rc, 0, words * 4, ctx->stream));
     CU(cudaMemsetAsync(s->mask, 0xFF, mwords * 4, ctx->stream));
     CU(cudaMemsetAsync(s->mask_rc, 0xFF, mwords * 4, ctx->stream));
+    RC(dalloc(ctx, &s->sel, mwords));
+    CU(cudaMemsetAsync(s->sel, 0, mwords * 4, ctx->stream));
     unsigned long long* ctr = (unsigned long long*)ctx->d_ctr;
     CU(cudaMemsetAsync(ctr, 0, 2 * sizeof(unsigned long long), ctx->stream));
     int blocks = RCQ_SMS * 8;
@@ -238,7 +241,7 @@ int rcq_sample_build(rcq_ctx* ctx, rcq_sample* s, const uint8_t* d_ascii, int64_
         LAUNCH(ctx, k_revcomp, blocks, 256, 0, s->fwd, s->mask, s->off, s->len, s->n_seq, s->rc,
                s->mask_rc);
         LAUNCH(ctx, k_minimizers<false>, blocks, 256, 0, s->fwd, s->mask, s->off, s->len, s->n_seq,
-               ctr + 1, (uint64_t*)nullptr);
+               ctr + 1, (uint64_t*)nullptr, (uint32_t*)nullptr);
     }
     CU(cudaMemcpyAsync(ctx->h_pin, ctr, 2 * sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
@@ -248,7 +251,7 @@ int rcq_sample_build(rcq_ctx* ctx, rcq_sample* s, const uint8_t* d_ascii, int64_
     if (s->n_index) {
         CU(cudaMemsetAsync(ctr + 1, 0, sizeof(unsigned long long), ctx->stream));
         LAUNCH(ctx, k_minimizers<true>, blocks, 256, 0, s->fwd, s->mask, s->off, s->len, s->n_seq,
-               ctr + 1, s->index);
+               ctr + 1, s->index, s->sel);
         RC(sort_u64(ctx, s->index, s->n_index));
     }
     LAUNCH(ctx, k_build_dir, grid_for(s->n_index + 1, 256), 256, 0, s->index, s->n_index, s->dir);

@@ -9,6 +9,7 @@
 //   gene/iso[n_seq] int32
 //   index[n_index]  uint64  sorted minimizer entries  hash(canonical 16-mer)<<32 | pos<<1 | orient
 //   dir[2^DIRBITS+1] uint32 first index entry of each hash-prefix bucket
+//   sel[arena/32]   uint32  bitmap of indexed positions;  gidx[n_seq] dense gene index
 #pragma once
 #include "common.cuh"
 
@@ -26,6 +27,9 @@ struct rcq_sample {
     int32_t *off = nullptr, *len = nullptr, *gene = nullptr, *iso = nullptr;
     uint64_t* index = nullptr;
     uint32_t* dir = nullptr;
+    uint32_t* sel = nullptr;   // arena/32 words: bit p set = position p holds an index entry
+    int32_t* gidx = nullptr;   // dense index of gene[t] among the sample's sorted distinct genes
+    int32_t n_genes = 0;
 };
 
 // A strand view of a sample: which arena to read for subject-side bases.

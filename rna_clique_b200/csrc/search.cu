@@ -1,0 +1,234 @@
+// search.cu — host orchestration of one unordered pair search (rcq_search_pair) and the
+// rcq_table_* entry points.  Replaces, per sample pair, two `blastn` subprocesses plus the
+// pandas post-processing of find_homologs.py:82-164,215-302.
+#include <cub/cub.cuh>
+#include <math.h>
+#include "search.cuh"
+
+#include "seed_kernels.cuh"
+#include "gapped_kernels.cuh"
+#include "select_kernels.cuh"
+
+struct GappedValid {
+    __host__ __device__ bool operator()(const Gapped& g) const { return g.ta >= 0; }
+};
+
+static int sort_pairs_u64_u32(rcq_ctx* ctx, uint64_t** keys, uint32_t** vals, int64_t n, int end_bit) {
+    if (n <= 1) return 0;
+    uint64_t* k2 = nullptr; uint32_t* v2 = nullptr;
+    RC(dalloc(ctx, &k2, n));
+    RC(dalloc(ctx, &v2, n));
+    cub::DoubleBuffer<uint64_t> dk(*keys, k2);
+    cub::DoubleBuffer<uint32_t> dv(*vals, v2);
+    size_t bytes = 0;
+    CU(cub::DeviceRadixSort::SortPairs(nullptr, bytes, dk, dv, (int)n, 0, end_bit, ctx->stream));
+    void* ws = nullptr;
+    CU(cudaMallocAsync(&ws, bytes, ctx->stream));
+    CU(cub::DeviceRadixSort::SortPairs(ws, bytes, dk, dv, (int)n, 0, end_bit, ctx->stream));
+    ctx->launches += (end_bit + 7) / 8 + 1;
+    cudaFreeAsync(ws, ctx->stream);
+    uint64_t* ko = dk.Current(); uint32_t* vo = dv.Current();
+    dfree(ctx, ko == *keys ? k2 : *keys);
+    dfree(ctx, vo == *vals ? v2 : *vals);
+    *keys = ko; *vals = vo;
+    return 0;
+}
+
+static int read_counters(rcq_ctx* ctx, int n) {
+    CU(cudaMemcpyAsync(ctx->h_pin, ctx->d_ctr, n * sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sample* s2, double evalue,
+                               int32_t top_n, int32_t keep_all, rcq_table** out, rcq_search_stats* stats) {
+    if (!ctx || !s1 || !s2 || !out) return rcq_fail(RCQ_ERR_ARG, "rcq_search_pair: bad argument");
+    if (top_n != 1)
+        return rcq_fail(RCQ_ERR_ARG, "rcq_search_pair: only top_n == 1 (the reference default) is implemented on the device");
+    if (s1->n_genes >= (1 << 20) || s2->n_genes >= (1 << 20))
+        return rcq_fail(RCQ_ERR_CAPACITY, "rcq_search_pair: more than 2^20 genes in a sample");
+    CU(cudaSetDevice(ctx->device));
+    rcq_search_stats st;
+    memset(&st, 0, sizeof st);
+    const bool has_n = s1->n_masked > 0 || s2->n_masked > 0;
+    PairView P;
+    P.Af = {s1->fwd, s1->n_masked ? s1->mask : nullptr};
+    P.Ar = {s1->rc, s1->n_masked ? s1->mask_rc : nullptr};
+    P.Bf = {s2->fwd, s2->n_masked ? s2->mask : nullptr};
+    P.Br = {s2->rc, s2->n_masked ? s2->mask_rc : nullptr};
+    P.offA = s1->off; P.lenA = s1->len; P.offB = s2->off; P.lenB = s2->len;
+    P.nA = s1->n_seq; P.nB = s2->n_seq; P.selA = s1->sel; P.selB = s2->sel;
+    unsigned long long* ctr = (unsigned long long*)ctx->d_ctr;
+    rcq_table* T = new rcq_table();
+    T->ctx = ctx;
+    *out = T;
+
+    // ---- seeds
+    Seed* seeds = nullptr;
+    int64_t n_seeds = 0, cap = std::max<int64_t>(1 << 20, 48ll * std::max(s1->n_seq, s2->n_seq));
+    for (int attempt = 0; attempt < 2 && s1->n_index && s2->n_index; attempt++) {
+        RC(dalloc(ctx, &seeds, cap));
+        CU(cudaMemsetAsync(ctr, 0, 16 * sizeof(int64_t), ctx->stream));
+        LAUNCH(ctx, k_seed_join, grid_for(s1->n_index, 256), 256, 0, s1->index, s1->n_index, s2->index,
+               s2->dir, P, seeds, cap, ctr);
+        RC(read_counters(ctx, 2));
+        n_seeds = ctx->h_pin[0];
+        st.n_candidates = ctx->h_pin[1];
+        if (n_seeds <= cap) break;
+        dfree(ctx, seeds); seeds = nullptr;
+        cap = n_seeds;
+    }
+    st.n_seeds = n_seeds;
+    if (n_seeds >= (1ll << 31)) return rcq_fail(RCQ_ERR_CAPACITY, "rcq_search_pair: too many seeds");
+    int64_t n_gapped = 0;
+    Gapped* Gd = nullptr;
+    if (n_seeds > 0) {
+        // ---- ungapped HSPs, grouped by (tx1, tx2, strand)
+        Ungapped* U = nullptr;
+        RC(dalloc(ctx, &U, n_seeds));
+        CU(cudaMemsetAsync(ctr, 0, 16 * sizeof(int64_t), ctx->stream));
+        LAUNCH(ctx, k_ungapped, grid_for(n_seeds, 256), 256, 0, seeds, n_seeds, P, U, ctr + 4);
+        dfree(ctx, seeds); seeds = nullptr;
+        uint64_t* keys = nullptr; uint32_t* order = nullptr; uint32_t* heads = nullptr;
+        RC(dalloc(ctx, &keys, n_seeds));
+        RC(dalloc(ctx, &order, n_seeds));
+        RC(dalloc(ctx, &heads, n_seeds));
+        LAUNCH(ctx, k_group_keys, grid_for(n_seeds, 256), 256, 0, U, n_seeds, keys, order);
+        RC(sort_pairs_u64_u32(ctx, &keys, &order, n_seeds, 64));
+        LAUNCH(ctx, k_group_heads, grid_for(n_seeds, 256), 256, 0, keys, n_seeds, heads, ctr + 5);
+        RC(read_counters(ctx, 6));
+        st.ungapped_cells = ctx->h_pin[4];
+        int64_t n_groups = ctx->h_pin[5];
+        st.n_ungapped = n_seeds;
+        // ---- gapped extension, warp per group
+        Gapped* G = nullptr;
+        RC(dalloc(ctx, &G, n_seeds));
+        CU(cudaMemsetAsync(G, 0xFF, n_seeds * sizeof(Gapped), ctx->stream));
+        const int blocks = RCQ_SMS * 8, threads = 128;
+        int64_t per_warp = 3ll * ((int64_t)s1->max_len + s2->max_len + 8);
+        int32_t* scratch = nullptr;
+        RC(dalloc(ctx, &scratch, per_warp * blocks * (threads / 32)));
+        CU(cudaMemsetAsync(ctr, 0, 16 * sizeof(int64_t), ctx->stream));
+        if (has_n) LAUNCH(ctx, k_gapped<true>, blocks, threads, 0, U, order, keys, n_seeds, heads, n_groups, P, G, scratch, per_warp, ctr);
+        else LAUNCH(ctx, k_gapped<false>, blocks, threads, 0, U, order, keys, n_seeds, heads, n_groups, P, G, scratch, per_warp, ctr);
+        dfree(ctx, scratch); dfree(ctx, U); dfree(ctx, keys); dfree(ctx, order); dfree(ctx, heads);
+        // ---- compact (stable: group order, then processing order inside the group)
+        RC(dalloc(ctx, &Gd, n_seeds));
+        size_t bytes = 0;
+        CU(cub::DeviceSelect::If(nullptr, bytes, G, Gd, (int*)(ctr + 8), (int)n_seeds, GappedValid(), ctx->stream));
+        void* ws = nullptr;
+        CU(cudaMallocAsync(&ws, bytes, ctx->stream));
+        CU(cub::DeviceSelect::If(ws, bytes, G, Gd, (int*)(ctr + 8), (int)n_seeds, GappedValid(), ctx->stream));
+        ctx->launches += 2;
+        cudaFreeAsync(ws, ctx->stream);
+        dfree(ctx, G);
+        RC(read_counters(ctx, 9));
+        st.dp_cells = ctx->h_pin[1];
+        st.band_retries = ctx->h_pin[2];
+        n_gapped = (int64_t)(int32_t)(ctx->h_pin[8] & 0xFFFFFFFF);
+        st.n_gapped = n_gapped;
+    } else {
+        dfree(ctx, seeds);
+    }
+    // debug copy of the HSP list
+    if (ctx->dbg_hsp) { cudaFree(ctx->dbg_hsp); ctx->dbg_hsp = nullptr; }
+    ctx->dbg_n = n_gapped;
+    if (n_gapped) {
+        CU(cudaMalloc((void**)&ctx->dbg_hsp, n_gapped * sizeof(Gapped)));
+        CU(cudaMemcpyAsync(ctx->dbg_hsp, Gd, n_gapped * sizeof(Gapped), cudaMemcpyDeviceToDevice, ctx->stream));
+    }
+    if (n_gapped >= (1 << 22)) return rcq_fail(RCQ_ERR_CAPACITY, "rcq_search_pair: more than 2^22 gapped HSPs in one pair");
+    // ---- selection + table
+    int64_t n_rows = 0;
+    if (n_gapped > 0) {
+        SelView V;
+        V.G = Gd; V.n = n_gapped;
+        V.lenA = s1->len; V.lenB = s2->len; V.gidxA = s1->gidx; V.gidxB = s2->gidx;
+        V.totalA = s1->total; V.totalB = s2->total; V.nA = s1->n_seq; V.nB = s2->n_seq;
+        V.log_cut = evalue > 0 ? log(evalue) : -INFINITY;
+        int64_t hcap = 1024;
+        while (hcap < 4 * n_gapped) hcap <<= 1;
+        V.hmask = (uint32_t)(hcap - 1);
+        RC(dalloc(ctx, &V.pass, n_gapped));
+        RC(dalloc(ctx, &V.bestF, s2->n_genes));
+        RC(dalloc(ctx, &V.bestB, s1->n_genes));
+        RC(dalloc(ctx, &V.bestQ, s2->n_genes));
+        RC(dalloc(ctx, &V.firstkey, s2->n_genes));
+        RC(dalloc(ctx, &V.hkeys, hcap));
+        RC(dalloc(ctx, &V.hflags, hcap));
+        RC(dalloc(ctx, &V.hbest, hcap));
+        CU(cudaMemsetAsync(V.bestF, 0xFF, s2->n_genes * 4, ctx->stream));
+        CU(cudaMemsetAsync(V.bestB, 0xFF, s1->n_genes * 4, ctx->stream));
+        CU(cudaMemsetAsync(V.bestQ, 0xFF, s2->n_genes * 4, ctx->stream));
+        CU(cudaMemsetAsync(V.firstkey, 0xFF, s2->n_genes * 8, ctx->stream));
+        CU(cudaMemsetAsync(V.hkeys, 0xFF, hcap * 8, ctx->stream));
+        CU(cudaMemsetAsync(V.hflags, 0, hcap * 4, ctx->stream));
+        CU(cudaMemsetAsync(V.hbest, 0xFF, hcap * 4, ctx->stream));
+        CU(cudaMemsetAsync(ctr, 0, 16 * sizeof(int64_t), ctx->stream));
+        uint64_t* rkeys = nullptr; uint32_t* rdesc = nullptr;
+        RC(dalloc(ctx, &rkeys, 2 * n_gapped));
+        RC(dalloc(ctx, &rdesc, 2 * n_gapped));
+        int g = grid_for(n_gapped, 256);
+        LAUNCH(ctx, k_sel_best, g, 256, 0, V);
+        LAUNCH(ctx, k_sel_pairs, g, 256, 0, V);
+        LAUNCH(ctx, k_sel_pairbest, g, 256, 0, V);
+        LAUNCH(ctx, k_sel_genebest, g, 256, 0, V);
+        if (!keep_all) LAUNCH(ctx, k_sel_first, g, 256, 0, V);
+        LAUNCH(ctx, k_sel_emit, g, 256, 0, V, (int)keep_all, rkeys, rdesc, ctr);
+        RC(read_counters(ctx, 3));
+        n_rows = ctx->h_pin[0];
+        st.n_fwd = ctx->h_pin[1];
+        st.n_bwd = ctx->h_pin[2];
+        if (n_rows > 0) {
+            RC(sort_pairs_u64_u32(ctx, &rkeys, &rdesc, n_rows, 64));
+            RC(dalloc(ctx, &T->cols, (int64_t)RCQ_NCOLS * n_rows));
+            LAUNCH(ctx, k_sel_fill, grid_for(n_rows, 256), 256, 0, Gd, rdesc, n_rows, s1->len, s2->len,
+                   s1->gene, s1->iso, s2->gene, s2->iso, T->cols);
+        }
+        dfree(ctx, rkeys); dfree(ctx, rdesc);
+        dfree(ctx, V.pass); dfree(ctx, V.bestF); dfree(ctx, V.bestB); dfree(ctx, V.bestQ);
+        dfree(ctx, V.firstkey); dfree(ctx, V.hkeys); dfree(ctx, V.hflags); dfree(ctx, V.hbest);
+    }
+    dfree(ctx, Gd);
+    T->n = n_rows;
+    st.n_rows = n_rows;
+    if (stats) *stats = st;
+    return 0;
+}
+
+extern "C" int64_t rcq_table_rows(const rcq_table* t) { return t ? t->n : 0; }
+
+extern "C" void rcq_table_free(rcq_table* t) {
+    if (!t) return;
+    cudaSetDevice(t->ctx->device);
+    dfree(t->ctx, t->cols);
+    delete t;
+}
+
+extern "C" int rcq_table_download(const rcq_table* t, rcq_table_cols* h) {
+    if (!t || !h) return rcq_fail(RCQ_ERR_ARG, "rcq_table_download: bad argument");
+    if (t->n == 0) return 0;
+    rcq_ctx* ctx = t->ctx;
+    CU(cudaSetDevice(ctx->device));
+    std::vector<int32_t> buf((size_t)RCQ_NCOLS * t->n);
+    CU(cudaMemcpyAsync(buf.data(), t->cols, buf.size() * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    int32_t* dst[15] = {h->length, h->mismatch, h->gapopen, h->qstart, h->qend, h->sstart, h->send, h->score,
+                        h->gaps, h->nident, h->qgene, h->qiso, h->sgene, h->siso, h->qlen};
+    for (int c = 0; c < 15; c++)
+        if (dst[c]) memcpy(dst[c], buf.data() + (size_t)c * t->n, t->n * 4);
+    for (int64_t r = 0; r < t->n; r++) {
+        if (h->minus) h->minus[r] = (uint8_t)buf[(size_t)RCQ_COL_MINUS * t->n + r];
+        if (h->reverse) h->reverse[r] = (uint8_t)buf[(size_t)RCQ_COL_REVERSE * t->n + r];
+    }
+    return 0;
+}
+
+extern "C" int64_t rcq_debug_last_hsps(rcq_ctx* ctx, int32_t* out, int64_t cap) {
+    if (!ctx) return 0;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    int64_t n = ctx->dbg_n < cap ? ctx->dbg_n : cap;
+    if (out && n > 0) cudaMemcpy(out, ctx->dbg_hsp, n * sizeof(Gapped), cudaMemcpyDeviceToHost);
+    return ctx->dbg_n;
+}

@@ -1,0 +1,243 @@
+// seed_kernels.cuh — kernel (3a): minimizer join -> exact 28-mer runs -> X-drop ungapped HSPs.
+//
+// For one unordered sample pair (A = sample 1 on its plus strand, B = sample 2 on both strands)
+// the kernels find every maximal exact-match run of >= 28 bases between a transcript of A and a
+// transcript of B (the megablast seed condition, blastn word_size 28) and extend each run without
+// gaps under an X-drop of 10 (20 bits).  Any 28-mer window contains the window minimum of its 13
+// canonical 16-mers, and both samples index every position that is a window minimum, so joining
+// the two sorted minimizer lists on the hash finds at least one anchor inside every such run.
+// Exactly one anchor per run survives (the leftmost position indexed on both sides).
+//
+// Roofline: HBM/L2-bound.  Algorithmic bytes per pair: 8 B per index entry of A streamed +
+// 4 B directory + 8 B entry of B per probe (sorted probes => sequential), then 2-bit sequence
+// words for verification (L2-resident: 3 arenas of L/4 bytes).
+#pragma once
+#include "sample.cuh"
+#include "search.cuh"
+
+// transcript containing arena position p: last t with off[t] <= p
+__device__ __forceinline__ int32_t find_tx(const int32_t* __restrict__ off, int32_t n, int32_t p) {
+    int32_t lo = 0, hi = n;  // invariant: off[lo] <= p < off[hi]
+    while (hi - lo > 1) {
+        int32_t mid = (lo + hi) >> 1;
+        if (__ldg(off + mid) <= p) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+// number of consecutive matching base pairs going forward from (pa, pb), at most lim
+__device__ __forceinline__ int32_t run_fwd(const SeqArena& A, int64_t pa, const SeqArena& B, int64_t pb,
+                                           int32_t lim) {
+    int32_t n = 0;
+    while (n < lim) {
+        uint32_t m = match32(A, pa + n, B, pb + n);
+        int32_t z = (m == 0xFFFFFFFFu) ? 32 : (__ffs(~m) - 1);
+        if (z > lim - n) z = lim - n;
+        n += z;
+        if (z < 32) break;
+    }
+    return n;
+}
+// same going backward from (pa, pb) inclusive
+__device__ __forceinline__ int32_t run_back(const SeqArena& A, int64_t pa, const SeqArena& B, int64_t pb,
+                                            int32_t lim) {
+    int32_t n = 0;
+    while (n < lim) {
+        uint32_t m = match32_back(A, pa - n, B, pb - n);
+        int32_t z = (m == 0xFFFFFFFFu) ? 32 : (__ffs(~m) - 1);
+        if (z > lim - n) z = lim - n;
+        n += z;
+        if (z < 32) break;
+    }
+    return n;
+}
+
+// Try one (A position, B position, strand) anchor; on success append a seed record.
+__device__ __forceinline__ bool try_anchor(const PairView& P, int32_t pA, int32_t pB, int minus,
+                                           Seed* out) {
+    int32_t ta = find_tx(P.offA, P.nA, pA), tb = find_tx(P.offB, P.nB, pB);
+    int32_t oa = __ldg(P.offA + ta), ob = __ldg(P.offB + tb);
+    int32_t la = __ldg(P.lenA + ta), lb = __ldg(P.lenB + tb);
+    int32_t ia = pA - oa, jf = pB - ob;
+    int32_t j = minus ? lb - jf - RCQ_KMER : jf;
+    const SeqArena& B = minus ? P.Br : P.Bf;
+    int64_t ba = oa, bb = ob;
+    if ((match32(P.Af, ba + ia, B, bb + j) & 0xFFFFu) != 0xFFFFu) return false;
+    int32_t right = run_fwd(P.Af, ba + ia + RCQ_KMER, B, bb + j + RCQ_KMER,
+                            min(la - ia - RCQ_KMER, lb - j - RCQ_KMER));
+    int32_t left = (ia > 0 && j > 0) ? run_back(P.Af, ba + ia - 1, B, bb + j - 1, min(ia, j)) : 0;
+    int32_t rs = ia - left, re = ia + RCQ_KMER + right, d = j - ia;
+    if (re - rs < RCQ_WORD) return false;
+    // leftmost jointly indexed position of the run wins
+    for (int32_t p0 = rs; p0 < ia; p0 += 32) {
+        uint32_t wa = fetchmask32(P.selA, ba + p0), wb;
+        if (!minus) wb = fetchmask32(P.selB, bb + p0 + d);
+        else wb = __brev(fetchmask32(P.selB, bb + lb - d - RCQ_KMER - p0 - 31));
+        uint32_t both = wa & wb;
+        int32_t v = ia - p0;
+        if (v < 32) both &= (1u << v) - 1u;
+        if (both) return false;
+    }
+    out->ta = ta; out->tb = tb; out->minus = minus; out->rs = rs; out->re = re; out->diag = d;
+    return true;
+}
+
+// Thread per index entry of A.  Seeds are staged in shared memory and flushed with one global
+// atomic per block.
+__global__ void __launch_bounds__(256) k_seed_join(
+    const uint64_t* __restrict__ idxA, int64_t nIdxA, const uint64_t* __restrict__ idxB,
+    const uint32_t* __restrict__ dirB, PairView P, Seed* __restrict__ seeds, int64_t cap,
+    unsigned long long* __restrict__ counters /* [0]=seeds [1]=candidates */) {
+    __shared__ Seed stage[512];
+    __shared__ int n_stage;
+    __shared__ unsigned long long base;
+    if (threadIdx.x == 0) n_stage = 0;
+    __syncthreads();
+    int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned cand = 0;
+    if (e < nIdxA) {
+        uint64_t ka = idxA[e];
+        uint32_t h = (uint32_t)(ka >> 32);
+        int32_t pA = (int32_t)((ka & 0xFFFFFFFFu) >> 1);
+        int oA = (int)(ka & 1);
+        uint32_t b = h >> (32 - RCQ_DIRBITS);
+        uint32_t lo = __ldg(dirB + b), hi = __ldg(dirB + b + 1);
+        // palindromic 16-mers match on both strands
+        uint32_t f = (uint32_t)fetch32(P.Af.bits, pA);
+        uint32_t x = ~f;
+        x = __brev(x);
+        x = ((x >> 1) & 0x55555555u) | ((x & 0x55555555u) << 1);
+        bool pal = (x == f);
+        for (uint32_t k = lo; k < hi; k++) {
+            uint64_t kb = __ldg(idxB + k);
+            uint32_t hb = (uint32_t)(kb >> 32);
+            if (hb < h) continue;
+            if (hb > h) break;
+            int32_t pB = (int32_t)((kb & 0xFFFFFFFFu) >> 1);
+            int minus = oA ^ (int)(kb & 1);
+            for (int rep = 0; rep < (pal ? 2 : 1); rep++) {
+                cand++;
+                Seed s;
+                if (try_anchor(P, pA, pB, minus ^ rep, &s)) {
+                    int slot = atomicAdd(&n_stage, 1);
+                    if (slot < 512) stage[slot] = s;
+                    else {  // rare: staging full, go straight to global
+                        unsigned long long g = atomicAdd(counters, 1ull);
+                        if ((int64_t)g < cap) seeds[g] = s;
+                    }
+                }
+            }
+        }
+    }
+    for (int o = 16; o; o >>= 1) cand += __shfl_down_sync(0xffffffffu, cand, o);
+    if ((threadIdx.x & 31) == 0 && cand) atomicAdd(counters + 1, (unsigned long long)cand);
+    __syncthreads();
+    int ns = min(n_stage, 512);
+    if (threadIdx.x == 0 && ns) base = atomicAdd(counters, (unsigned long long)ns);
+    __syncthreads();
+    for (int i = threadIdx.x; i < ns; i += blockDim.x)
+        if ((int64_t)(base + i) < cap) seeds[base + i] = stage[i];
+}
+
+// X-drop ungapped extension (thread per seed) + start point of the gapped extension.
+// Word-parallel: 32 base pairs per match mask; a run of matches is consumed in one step.
+__global__ void __launch_bounds__(256) k_ungapped(const Seed* __restrict__ seeds, int64_t n, PairView P,
+                                                  Ungapped* __restrict__ out,
+                                                  unsigned long long* __restrict__ cells) {
+    int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long work = 0;
+    if (e < n) {
+        Seed s = seeds[e];
+        const SeqArena& B = s.minus ? P.Br : P.Bf;
+        int64_t ba = __ldg(P.offA + s.ta), bb = __ldg(P.offB + s.tb);
+        int32_t la = __ldg(P.lenA + s.ta), lb = __ldg(P.lenB + s.tb), d = s.diag;
+        // ---- right
+        int32_t sum = 0, best = 0, ext = 0, k = 0, lim = min(la - s.re, lb - s.re - d);
+        bool stop = false;
+        while (k < lim && !stop) {
+            uint32_t m = match32(P.Af, ba + s.re + k, B, bb + s.re + d + k);
+            int32_t v = min(32, lim - k), i = 0;
+            while (i < v) {
+                uint32_t rest = ~(m >> i);
+                int32_t z = rest ? (__ffs(rest) - 1) : 32;
+                if (z > v - i) z = v - i;
+                if (z) { sum += z; i += z; if (sum > best) { best = sum; ext = k + i; } }
+                if (i < v) {  // mismatch at bit i
+                    sum -= 2; i++;
+                    if (best - sum > RCQ_XDROP_UNGAPPED) { stop = true; break; }
+                }
+            }
+            k += i;
+        }
+        work += k;
+        int32_t a1 = s.re + ext, score = (s.re - s.rs) + best;
+        // ---- left
+        sum = 0; best = 0; ext = 0; k = 0; lim = min(s.rs, s.rs + d); stop = false;
+        while (k < lim && !stop) {
+            uint32_t m = match32_back(P.Af, ba + s.rs - 1 - k, B, bb + s.rs - 1 + d - k);
+            int32_t v = min(32, lim - k), i = 0;
+            while (i < v) {
+                uint32_t rest = ~(m >> i);
+                int32_t z = rest ? (__ffs(rest) - 1) : 32;
+                if (z > v - i) z = v - i;
+                if (z) { sum += z; i += z; if (sum > best) { best = sum; ext = k + i; } }
+                if (i < v) {
+                    sum -= 2; i++;
+                    if (best - sum > RCQ_XDROP_UNGAPPED) { stop = true; break; }
+                }
+            }
+            k += i;
+        }
+        work += k;
+        int32_t a0 = s.rs - ext;
+        score += best;
+        // ---- longest exact run inside [a0, a1) (earliest on ties) -> gapped start point
+        int32_t run = 0, best_len = 0, best_s = a0;
+        for (int32_t p = a0; p < a1; p += 32) {
+            uint32_t m = match32(P.Af, ba + p, B, bb + p + d);
+            int32_t v = min(32, a1 - p), i = 0;
+            while (i < v) {
+                uint32_t rest = ~(m >> i);
+                int32_t z = rest ? (__ffs(rest) - 1) : 32;
+                if (z > v - i) z = v - i;
+                run += z; i += z;
+                if (i < v) {
+                    if (run > best_len) { best_len = run; best_s = p + i - run; }
+                    run = 0; i++;
+                }
+            }
+        }
+        if (run > best_len) { best_len = run; best_s = a1 - run; }
+        work += a1 - a0;
+        Ungapped u;
+        u.ta = s.ta; u.tb = s.tb; u.minus = s.minus; u.diag = d; u.a0 = a0; u.a1 = a1;
+        u.score = score; u.i0 = best_s + best_len / 2;
+        out[e] = u;
+    }
+    for (int o = 16; o; o >>= 1) work += __shfl_down_sync(0xffffffffu, work, o);
+    if ((threadIdx.x & 31) == 0 && work) atomicAdd(cells, work);
+}
+
+// group key of each ungapped HSP for the sort: (ta, tb, strand)
+__global__ void k_group_keys(const Ungapped* __restrict__ u, int64_t n, uint64_t* __restrict__ keys,
+                             uint32_t* __restrict__ vals) {
+    int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n) return;
+    keys[e] = ((uint64_t)(uint32_t)u[e].ta << 32) | ((uint64_t)(uint32_t)u[e].tb << 1) | (uint64_t)u[e].minus;
+    vals[e] = (uint32_t)e;
+}
+// group heads after the sort: heads[g] = first sorted slot of group g
+__global__ void k_group_heads(const uint64_t* __restrict__ keys, int64_t n, uint32_t* __restrict__ heads,
+                              unsigned long long* __restrict__ n_groups) {
+    int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n) return;
+    bool head = (e == 0) || keys[e] != keys[e - 1];
+    unsigned m = __ballot_sync(__activemask(), head);
+    // order of heads[] does not matter: the gapped kernel only needs the set of group starts
+    if (head) {
+        unsigned long long g = atomicAdd(n_groups, 1ull);
+        heads[g] = (uint32_t)e;
+    }
+    (void)m;
+}
+

@@ -1,0 +1,110 @@
+"""GPU parity: pack / index / per-pair search through the C ABI against the CPU oracle."""
+import numpy as np
+import pytest
+
+from helpers import make_samples, np_pack, unpack_arena, unpack_mask
+
+pytestmark = pytest.mark.gpu
+
+
+def _gpu_samples(ctx, raw):
+    from rna_clique_b200 import _native
+    return [_native.Sample(ctx, *r) for r in raw]
+
+
+def _oracle_samples(raw):
+    from oracle import oracle as O
+    return [O.Sample(*r) for r in raw]
+
+
+def test_pack_revcomp_mask(ctx):
+    rng = np.random.default_rng(5)
+    lens = [1, 15, 16, 17, 31, 32, 33, 100, 511, 512, 513, 2050, 0, 64]
+    letters = np.frombuffer(b"ACGTacgtNnRYU-", dtype=np.uint8)
+    ascii_ = letters[rng.integers(0, len(letters), size=sum(lens))]
+    offsets = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    from rna_clique_b200 import _native
+    s = _native.Sample(ctx, ascii_, offsets, np.arange(len(lens), dtype=np.int32), np.ones(len(lens), dtype=np.int32))
+    d = s.download()
+    codes = np_pack(ascii_, offsets)
+    assert s.n_masked == int((codes > 3).sum())
+    for t, n in enumerate(lens):
+        c = codes[offsets[t]:offsets[t + 1]]
+        got = unpack_arena(d["fwd"], d["off"][t], n)
+        gm = unpack_mask(d["mask"], d["off"][t], n)
+        assert np.array_equal(gm, (c > 3).astype(np.uint8))
+        assert np.array_equal(got[c < 4], c[c < 4])
+        rc = unpack_arena(d["rc"], d["off"][t], n)
+        exp = (3 - c[::-1]).astype(np.uint8)
+        ok = c[::-1] < 4
+        assert np.array_equal(rc[ok], exp[ok])
+        assert d["off"][t] % 32 == 0
+
+
+def test_index_covers_every_28mer_window(ctx):
+    """Winnowing guarantee: every N-free 28-base window holds at least one indexed 16-mer."""
+    _, raw = make_samples(taxa=1, count=30, seed=3)
+    s = _gpu_samples(ctx, raw)[0]
+    d = s.download()
+    pos = ((d["index"] & np.uint64(0xFFFFFFFF)) >> np.uint64(1)).astype(np.int64)
+    assert np.all(np.diff(d["index"].astype(np.uint64)) >= 0)
+    sel = np.zeros(s.arena, dtype=bool)
+    sel[pos] = True
+    offsets = raw[0][1]
+    for t in range(s.n_seq):
+        n = int(offsets[t + 1] - offsets[t])
+        o = int(d["off"][t])
+        cs = np.concatenate([[0], np.cumsum(sel[o:o + n - 15])])
+        win = cs[13:] - cs[:-13]           # windows of 13 consecutive 16-mers
+        assert win.min() >= 1
+
+
+@pytest.mark.parametrize("kw", [
+    dict(taxa=2, count=150, seed=1),
+    dict(taxa=2, count=60, seed=2, mutation_rate=0.08),
+    dict(taxa=2, count=60, seed=3, mutation_rate=0.03, indel_rate=0.004),
+])
+def test_search_pair_matches_oracle(ctx, kw):
+    from rna_clique_b200 import _native
+    from oracle import oracle as O
+    _, raw = make_samples(**kw)
+    g = _gpu_samples(ctx, raw)
+    o = _oracle_samples(raw)
+    tab = _native.search_pair(ctx, g[0], g[1])
+    res = O.search_pair(o[0], o[1])
+    hs = _native.debug_last_hsps(ctx)
+    assert tab.stats["n_seeds"] == res.counts["seeds"]
+    assert np.array_equal(hs, res.hsps())
+    cols = tab.download()
+    got = np.stack([cols[c] for c in _native.TABLE_COLS] + [cols["minus"].astype(np.int32), cols["reverse"].astype(np.int32)], axis=1)
+    assert np.array_equal(got, res.rows(2))
+    assert tab.stats["n_fwd"] == res.counts["fwd"] and tab.stats["n_bwd"] == res.counts["bwd"]
+    assert len(tab) > 0
+
+
+def test_search_minus_strand_and_masked_bases(ctx):
+    """Half of sample 2's transcripts are reverse-complemented; a few bases become N."""
+    from rna_clique_b200 import _native
+    from oracle import oracle as O
+    _, raw = make_samples(taxa=2, count=80, seed=7, mutation_rate=0.02)
+    a2, off2, gene2, iso2 = raw[1]
+    a2 = a2.copy()
+    comp = np.zeros(256, dtype=np.uint8)
+    for x, y in zip(b"ACGT", b"TGCA"):
+        comp[x] = y
+    for t in range(0, len(gene2), 2):
+        seg = a2[off2[t]:off2[t + 1]]
+        a2[off2[t]:off2[t + 1]] = comp[seg[::-1]]
+    rng = np.random.default_rng(0)
+    a2[rng.integers(0, len(a2), size=40)] = ord("N")
+    raw = [raw[0], (a2, off2, gene2, iso2)]
+    g = _gpu_samples(ctx, raw)
+    o = _oracle_samples(raw)
+    tab = _native.search_pair(ctx, g[0], g[1])
+    res = O.search_pair(o[0], o[1])
+    hs = _native.debug_last_hsps(ctx)
+    assert np.array_equal(hs, res.hsps())
+    assert hs[:, 2].sum() > 0
+    cols = tab.download()
+    got = np.stack([cols[c] for c in _native.TABLE_COLS] + [cols["minus"].astype(np.int32), cols["reverse"].astype(np.int32)], axis=1)
+    assert np.array_equal(got, res.rows(2))
