@@ -535,8 +535,11 @@ static rvec_t match_table(rvec_t* F, rvec_t* B, int n, int keep_all) {
     for (int64_t i = 0; i < F->n; i++) if (has_pair(pb, B->n, F->v[i].qgene, F->v[i].sgene)) rpush(&T, F->v[i]);
     for (int64_t i = 0; i < B->n; i++) if (has_pair(pf, F->n, B->v[i].qgene, B->v[i].sgene)) rpush(&T, B->v[i]);
     free(pf); free(pb);
-    select_topn(&T, 1, n, 1);
-    select_topn(&T, 0, n, keep_all);
+    /* the reference calls highest_bitscores here WITHOUT n (find_homologs.py:281-301), so both
+     * steps use n = 1 whatever top_n is; top_n only shapes the two direction frames */
+    (void)n;
+    select_topn(&T, 1, 1, 1);
+    select_topn(&T, 0, 1, keep_all);
     return T;
 }
 
