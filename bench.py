@@ -1,0 +1,303 @@
+#!/usr/bin/env python
+"""bench.py — RNA-clique hot path on B200: all-vs-all top-gene matching -> gene-match graph ->
+ideal components -> distance matrix, on transcriptomes synthesised like the reference's
+distance_sequence_simulator.  One JSON line on stdout (rank 0).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+                  [--taxa 10 --count 60000 --top 50000]        # BASELINE.json configs[1]
+
+A step = one full pass: pack + seed index of every sample, every unordered pair searched
+(both blastn directions), phase 2, distance matrix.  `value` starts with the ASCII transcripts
+resident in HBM; `e2e` starts from pinned host buffers (top-gene selection, H2D, D2H inside).
+N > 1: the same workload with the sample pairs sharded over the ranks (strong scaling); the only
+collective is the all-gather of hit tables.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+INT32_LANES_PER_SM = 128   # Blackwell SM: 128 FP32/INT32 lanes
+SMS = 148
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--taxa", type=int, default=10)
+    ap.add_argument("--count", type=int, default=60000)
+    ap.add_argument("--top", type=int, default=50000)
+    ap.add_argument("--seed", type=int, default=487)
+    ap.add_argument("--cpu-sample", type=int, default=600, help="top-gene transcripts per sample in the CPU legs")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def workload_name(a):
+    return (f"{a.taxa} simulated samples x {a.count} transcripts, top_genes={a.top} "
+            f"(BASELINE.json configs[1]; birth-death tree, JC/HKY85 mu=0.01, seed {a.seed})")
+
+
+def equiv_cells(lengths):
+    """Smith-Waterman-equivalent cells of the all-vs-all: sum over ORDERED searches of L_q * L_d."""
+    tot = float(sum(lengths))
+    return tot * tot - float(sum(float(x) * x for x in lengths))
+
+
+class ClockSampler(threading.Thread):
+    def __init__(self, device):
+        super().__init__(daemon=True)
+        self.device, self.samples, self.reasons, self.stop_flag, self.max_mhz = device, [], set(), False, None
+
+    def run(self):
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            h = pynvml.nvmlDeviceGetHandleByIndex(self.device)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM)
+            names = {pynvml.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap",
+                     pynvml.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+                     pynvml.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+                     pynvml.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown"}
+            while not self.stop_flag:
+                self.samples.append(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM))
+                r = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                for bit, n in names.items():
+                    if r & bit:
+                        self.reasons.add(n)
+                time.sleep(0.05)
+        except Exception as e:  # noqa: BLE001
+            self.reasons.add(f"nvml_unavailable:{type(e).__name__}")
+
+    def summary(self):
+        return {"sm_mhz": float(np.median(self.samples)) if self.samples else None,
+                "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+
+
+def make_inputs(a, device):
+    from rna_clique_b200.simulate import simulate
+    tree, ts = simulate(a.taxa, a.count, seed=a.seed, device=device)
+    inputs, labels = [], []
+    for t in ts:
+        offs = t.offsets.numpy()
+        inputs.append(dict(ascii=t.ascii, starts=offs[:-1].copy(), lengths=np.diff(offs).astype(np.int32),
+                           coverage=t.coverage, gene=t.gene, iso=t.iso))
+        labels.append(f"od1/{t.name}_top.fasta")
+    return tree, inputs, labels
+
+
+def cpu_pair_job(args):
+    """One unordered pair through the CPU oracle (runs in a worker process)."""
+    sys.path.insert(0, ROOT)
+    from oracle import oracle as O
+    (a1, o1, g1, i1), (a2, o2, g2, i2) = args
+    t0 = time.perf_counter()
+    s1, s2 = O.Sample(a1, o1, g1, i1), O.Sample(a2, o2, g2, i2)
+    r = O.search_pair(s1, s2)
+    return time.perf_counter() - t0, r.counts["rows"], r.counts["dp_cells"]
+
+
+def cpu_sample_inputs(inputs, a, n_sub):
+    """The same workload cut down to the n_sub highest-coverage genes of every sample."""
+    from rna_clique_b200.engine import select_top_genes
+    out = []
+    for s in inputs:
+        keep = select_top_genes(s["coverage"], s["gene"], min(n_sub, a.top))
+        asc = s["ascii"].cpu().numpy() if hasattr(s["ascii"], "cpu") else np.asarray(s["ascii"])
+        st, ln = s["starts"][keep], s["lengths"][keep]
+        offs = np.concatenate([[0], np.cumsum(ln)]).astype(np.int64)
+        buf = np.empty(int(offs[-1]), dtype=np.uint8)
+        for k in range(len(keep)):
+            buf[offs[k]:offs[k + 1]] = asc[st[k]:st[k] + ln[k]]
+        out.append((buf, offs, s["gene"][keep].astype(np.int32), s["iso"][keep].astype(np.int32)))
+    return out
+
+
+def run_cpu_leg(inputs, a, lengths_full, steps, warmup):
+    """CPU oracle over every pair of the cut-down workload, one pair per host core at a time.
+    Returns (seconds per step, cores, description, GCUPS-equivalent scaled to the full workload)."""
+    import itertools
+    import multiprocessing as mp
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    n_sub = min(a.cpu_sample, a.top)
+    sub = cpu_sample_inputs(inputs, a, n_sub)
+    jobs = [(sub[i], sub[j]) for i, j in itertools.combinations(range(len(sub)), 2)]
+    times = []
+    with mp.get_context("fork").Pool(cores) as pool:
+        for s in range(warmup + steps):
+            t0 = time.perf_counter()
+            pool.map(cpu_pair_job, jobs, chunksize=1)
+            if s >= warmup:
+                times.append(time.perf_counter() - t0)
+    t = float(np.mean(times))
+    scale = a.top / n_sub
+    gcups = equiv_cells(lengths_full) / (t * scale) / 1e9
+    desc = (f"CPU oracle (C restatement, -O2), all {len(jobs)} pairs with the {n_sub} highest-coverage top genes of "
+            f"each sample ({n_sub}/{a.top} of the workload), one pair per core; time scaled x{scale:.1f} (work is "
+            f"linear in transcripts) to the full workload")
+    return t, cores, desc, gcups
+
+
+def main():
+    a = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if a.impl == "reference":
+        if rank != 0:
+            return
+        import torch
+        _, inputs, labels = make_inputs(a, "cpu" if not torch.cuda.is_available() else "cuda")
+        from rna_clique_b200.engine import select_top_genes
+        lengths_full = [int(s["lengths"][select_top_genes(s["coverage"], s["gene"], a.top)].sum()) for s in inputs]
+        t, cores, desc, gcups = run_cpu_leg(inputs, a, lengths_full, a.steps, min(a.warmup, 1))
+        print(json.dumps({
+            "impl": "reference", "metric": "all_vs_all_alignment_gcups_equiv", "value": gcups, "unit": "GCUPS",
+            "n_gpus": a.gpus, "steps": a.steps, "warmup": min(a.warmup, 1), "ms_per_step": t * 1e3 * (a.top / min(a.cpu_sample, a.top)),
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
+            "config": {"workload": workload_name(a)},
+            "cpu_baseline": {"value": gcups, "unit": "GCUPS", "cores": cores, "kind": "port", "sample": desc},
+            "e2e": {"value": gcups, "unit": "GCUPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "note": "BLAST+ (the reference's native component) is unavailable on this box; the CPU arm is the C oracle",
+        }))
+        return
+
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback)")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+        dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local))
+        dist = dist_mod
+    from rna_clique_b200.engine import Engine, select_top_genes
+    eng = Engine(local)
+    stream = torch.cuda.ExternalStream(eng.ctx.stream, device=torch.device("cuda", local))
+
+    _, inputs_dev, labels = make_inputs(a, f"cuda:{local}")
+    torch.cuda.synchronize()
+    # HBM-resident variant: top-gene selection already applied (starts/lengths of the kept transcripts)
+    resident = []
+    for s in inputs_dev:
+        keep = select_top_genes(s["coverage"], s["gene"], a.top)
+        resident.append(dict(ascii=s["ascii"], starts=s["starts"][keep], lengths=s["lengths"][keep],
+                             coverage=s["coverage"][keep], gene=s["gene"][keep], iso=s["iso"][keep]))
+    # host variant: pinned ASCII + unselected id arrays
+    host = [dict(s, ascii=s["ascii"].cpu().pin_memory()) for s in inputs_dev]
+    h2d = int(sum(s["ascii"].numel() for s in host) + sum(16 * len(s["starts"]) for s in resident))
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup):
+        out = None
+        for _ in range(warmup):
+            out = fn()
+        barrier()
+        eng.ctx.stage_times(reset=True)
+        l0 = eng.ctx.launches
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(steps):
+            out = fn()
+        e1.record(stream)
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if dist is not None:
+            t = torch.tensor([ms], device=f"cuda:{local}", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms / steps, out, eng.ctx.stage_times(reset=True), (eng.ctx.launches - l0) / steps
+
+    sampler = ClockSampler(local)
+    sampler.start()
+    ms_dev, res, stages, launches = timed(lambda: eng.all_vs_all(resident, labels, None, dist=dist), a.steps, a.warmup)
+    ms_e2e, res2, _, _ = timed(lambda: eng.all_vs_all(host, labels, a.top, dist=dist), a.steps, 1)
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+    assert np.array_equal(res["matrix"], res2["matrix"])
+
+    lengths = res["lengths"]
+    cells_eq = equiv_cells(lengths)
+    stats = res["stats"]
+    agg = {k: float(v) for k, v in stats.items()}
+    if dist is not None:
+        keys = sorted(agg)
+        t = torch.tensor([agg[k] for k in keys], device=f"cuda:{local}", dtype=torch.float64)
+        dist.all_reduce(t)
+        agg = dict(zip(keys, t.tolist()))
+    out = None
+    if rank == 0:
+        n_pairs_local = max(res["n_local_pairs"], 1)
+        dp_ms = stages["gapped_dp"]["ms"] / a.steps           # this rank, per step
+        dp_calls = max(stages["gapped_dp"]["calls"] / a.steps, 1)
+        dp_cells_rank = stats.get("dp_cells", 0)
+        clocks = sampler.summary()
+        mhz = clocks["sm_max_mhz"] or 1965
+        int_ops_peak = SMS * INT32_LANES_PER_SM * mhz * 1e6
+        OPS_PER_CELL = 12   # minimum int32 instructions of one cell of this recurrence
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:  # noqa: BLE001
+            pass
+        hbm_peak = peaks.get("hbm_gbs", 6650.0)
+        seed_ms = stages["seed_join"]["ms"] / max(stages["seed_join"]["calls"], 1)
+        n_index = float(np.mean(lengths)) * 0.15   # measured density of indexed positions, see DESIGN.md
+        seed_bytes = 20.0 * n_index
+        out = {
+            "metric": "all_vs_all_alignment_gcups_equiv", "value": cells_eq / (ms_dev * 1e-3) / 1e9, "unit": "GCUPS",
+            "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms_dev,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
+            "config": {"workload": workload_name(a), "pairs": len(res["pairs"]), "ordered_searches": 2 * len(res["pairs"]),
+                       "nt_per_sample": int(np.mean(lengths)), "l2": "inputs larger than L2 (1 GB of ASCII per step)",
+                       "parallelism": f"pairs sharded over {world} rank(s)"},
+            "seconds_to_matrix": {"hbm_resident": ms_dev * 1e-3, "from_host_buffers": ms_e2e * 1e-3},
+            "gcups_actual": agg.get("dp_cells", 0) / (ms_dev * 1e-3) / 1e9,
+            "e2e": {"value": cells_eq / (ms_e2e * 1e-3) / 1e9, "unit": "GCUPS", "ms_per_step": ms_e2e,
+                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": int(16 * len(res["pairs"]) + 64)},
+            "gpu_launches": launches,
+            "clocks": clocks,
+            "roofline": {"kernel": "k_gapped", "bound": "int_alu", "achieved": dp_cells_rank / max(dp_ms * 1e-3, 1e-9) / 1e9,
+                         "peak": int_ops_peak / OPS_PER_CELL / 1e9, "unit": "GCUPS (DP cells/s)",
+                         "frac": (dp_cells_rank / max(dp_ms * 1e-3, 1e-9)) / (int_ops_peak / OPS_PER_CELL),
+                         "traffic": None, "launch_ms": dp_ms / dp_calls, "share_of_step": dp_ms / ms_dev,
+                         "peak_source": f"148 SMs x 128 int32 lanes x {mhz} MHz / {OPS_PER_CELL} ops per cell (nominal; no measured int peak in MEASURED_PEAKS.json)"},
+            "roofline_hbm": {"kernel": "k_seed_join", "bound": "hbm", "achieved": seed_bytes / max(seed_ms * 1e-3, 1e-9) / 1e9,
+                             "peak": hbm_peak, "unit": "GB/s", "frac": seed_bytes / max(seed_ms * 1e-3, 1e-9) / 1e9 / hbm_peak,
+                             "traffic": None, "launch_ms": seed_ms,
+                             "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s"},
+            "stages_ms_per_step": {k: v["ms"] / a.steps for k, v in stages.items()},
+            "search_stats_per_step": agg,
+            "phase2_counts": res["counts"],
+        }
+    if dist is not None:
+        dist.barrier()
+    if rank == 0:
+        if not a.no_cpu_baseline and world == 1:
+            t, cores, desc, gcups = run_cpu_leg(inputs_dev, a, lengths, 1, 0)
+            out["cpu_baseline"] = {"value": gcups, "unit": "GCUPS", "cores": cores, "kind": "port", "sample": desc,
+                                   "seconds_sample": t}
+        else:
+            out["cpu_baseline"] = None
+        print(json.dumps(out))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -41,15 +41,20 @@ int rcq_ctx_sync(rcq_ctx* ctx);
 void* rcq_ctx_stream(rcq_ctx* ctx);
 /* number of kernels this library launched on ctx since creation (bench.py's gpu_launches) */
 int64_t rcq_ctx_launches(rcq_ctx* ctx);
+/* device time per stage, measured with CUDA events on the context's stream and accumulated over
+ * calls: 0 pack+index, 1 seed join, 2 ungapped, 3 sort/group, 4 gapped DP, 5 selection+table,
+ * 6 phase 2 (7 unused).  reset != 0 clears the accumulators after reading. */
+int rcq_ctx_stage_times(rcq_ctx* ctx, double ms[8], int64_t calls[8], int reset);
 
 /* ---- kernels (1)+(2): pack + seed index.  Replaces makeblastdb per sample
  * (find_all_pairs.py:120-159 make_one_db/make_all_dbs -> BlastDBCache.makedb).
- * ascii: concatenated nucleotide letters of the sample's top-gene transcripts (no newlines);
- * offsets[n_seq+1]: start of each transcript in ascii; gene/iso: parsed FASTA ids
- * (transcripts.py:60-126).  ascii_on_device!=0 means `ascii` is a device pointer. */
-int rcq_sample_create(rcq_ctx* ctx, const uint8_t* ascii, int ascii_on_device,
-                      const int64_t* offsets, const int32_t* gene, const int32_t* iso,
-                      int32_t n_seq, rcq_sample** out);
+ * ascii[ascii_len]: nucleotide letters (no newlines) holding at least the selected transcripts;
+ * transcript t is ascii[starts[t] .. starts[t]+lengths[t]) — transcripts need not be contiguous,
+ * so a top-gene selection is passed as (starts, lengths) without gathering.  gene/iso: parsed
+ * FASTA ids (transcripts.py:60-126).  ascii_on_device != 0 means `ascii` is a device pointer. */
+int rcq_sample_create(rcq_ctx* ctx, const uint8_t* ascii, int64_t ascii_len, int ascii_on_device,
+                      const int64_t* starts, const int32_t* lengths, const int32_t* gene,
+                      const int32_t* iso, int32_t n_seq, rcq_sample** out);
 void rcq_sample_free(rcq_sample* s);
 /* info[0]=n_seq, [1]=total bases, [2]=arena bases (padded), [3]=#index entries, [4]=#masked bases */
 int rcq_sample_info(const rcq_sample* s, int64_t info[5]);

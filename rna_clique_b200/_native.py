@@ -19,7 +19,7 @@ HSP_COLS = ["tx1", "tx2", "minus", "a0", "a1", "b0", "b1", "score2", "mismatch",
 # every symbol include/rcq.h declares (checked by tests/test_abi.py)
 SYMBOLS = [
     "rcq_last_error", "rcq_version", "rcq_ctx_create", "rcq_ctx_destroy", "rcq_ctx_sync", "rcq_ctx_stream",
-    "rcq_ctx_launches", "rcq_sample_create", "rcq_sample_free", "rcq_sample_info", "rcq_sample_download",
+    "rcq_ctx_launches", "rcq_ctx_stage_times", "rcq_sample_create", "rcq_sample_free", "rcq_sample_info", "rcq_sample_download",
     "rcq_search_pair", "rcq_table_rows", "rcq_table_download", "rcq_table_free", "rcq_debug_last_hsps",
     "rcq_length_adjustment", "rcq_evalue", "rcq_bitscore", "rcq_phase2_host", "rcq_phase2_tables",
     "rcq_table_flat_words", "rcq_table_flatten", "rcq_table_from_flat",
@@ -68,7 +68,8 @@ def lib():
         L.rcq_ctx_stream.restype = vp
         L.rcq_ctx_launches.argtypes = [vp]
         L.rcq_ctx_launches.restype = i64
-        L.rcq_sample_create.argtypes = [vp, vp, C.c_int, vp, vp, vp, i32, C.POINTER(vp)]
+        L.rcq_ctx_stage_times.argtypes = [vp, vp, vp, C.c_int]
+        L.rcq_sample_create.argtypes = [vp, vp, i64, C.c_int, vp, vp, vp, vp, i32, C.POINTER(vp)]
         L.rcq_sample_free.argtypes = [vp]
         L.rcq_sample_free.restype = None
         L.rcq_sample_info.argtypes = [vp, vp]
@@ -129,6 +130,14 @@ class Context:
     def launches(self) -> int:
         return lib().rcq_ctx_launches(self.h)
 
+    STAGES = ["pack_index", "seed_join", "ungapped", "sort_group", "gapped_dp", "select_table", "phase2"]
+
+    def stage_times(self, reset: bool = False) -> dict:
+        ms = np.zeros(8, dtype=np.float64)
+        calls = np.zeros(8, dtype=np.int64)
+        check(lib().rcq_ctx_stage_times(self.h, ms.ctypes.data, calls.ctypes.data, int(reset)))
+        return {n: dict(ms=float(ms[i]), calls=int(calls[i])) for i, n in enumerate(self.STAGES)}
+
     def close(self):
         if self.h:
             lib().rcq_ctx_destroy(self.h)
@@ -144,28 +153,39 @@ class Context:
 class Sample:
     """Device-resident packed sample + seed index (rcq_sample)."""
 
-    def __init__(self, ctx: Context, ascii_, offsets, gene, iso, name: str = ""):
+    def __init__(self, ctx: Context, ascii_, offsets, gene, iso, name: str = "", lengths=None):
+        """ascii_: uint8 numpy array or torch tensor (CPU or CUDA).  offsets: int64 [n+1] boundaries of
+        contiguous transcripts, or — when `lengths` is given — int64 [n] start positions."""
         self.ctx = ctx
         self.name = name
         offsets = np.ascontiguousarray(offsets, dtype=np.int64)
         gene = np.ascontiguousarray(gene, dtype=np.int32)
         iso = np.ascontiguousarray(iso, dtype=np.int32)
         n = len(gene)
-        assert len(offsets) == n + 1 and len(iso) == n
+        if lengths is None:
+            assert len(offsets) == n + 1
+            starts = np.ascontiguousarray(offsets[:-1])
+            lengths = np.diff(offsets).astype(np.int32)
+        else:
+            starts = offsets
+            lengths = np.ascontiguousarray(lengths, dtype=np.int32)
+        assert len(starts) == n and len(lengths) == n and len(iso) == n
         on_device = 0
         if hasattr(ascii_, "data_ptr"):  # torch tensor
+            alen = int(ascii_.numel())
             if ascii_.is_cuda:
                 on_device, p = 1, ascii_.data_ptr()
-                self._keep = ascii_
+                keep = ascii_
             else:
-                a = ascii_.numpy()
-                p, self._keep = a.ctypes.data, a
+                keep = ascii_.numpy()
+                p = keep.ctypes.data
         else:
-            a = np.ascontiguousarray(ascii_, dtype=np.uint8)
-            p, self._keep = a.ctypes.data, a
+            keep = np.ascontiguousarray(ascii_, dtype=np.uint8)
+            p, alen = keep.ctypes.data, len(keep)
         h = C.c_void_p()
-        check(lib().rcq_sample_create(ctx.h, p, on_device, offsets.ctypes.data, gene.ctypes.data,
-                                      iso.ctypes.data, n, C.byref(h)))
+        check(lib().rcq_sample_create(ctx.h, p, alen, on_device, starts.ctypes.data, lengths.ctypes.data,
+                                      gene.ctypes.data, iso.ctypes.data, n, C.byref(h)))
+        del keep
         self.h = h
         self._keep = None
         info = np.zeros(5, dtype=np.int64)
@@ -239,3 +259,49 @@ def debug_last_hsps(ctx: Context) -> np.ndarray:
     if n:
         lib().rcq_debug_last_hsps(ctx.h, out.ctypes.data, n)
     return out
+
+
+def phase2_host(ctx: Context, n_samples: int, stride: int, row_off, t_s, t_q, sgene, qgene, nident, length,
+                gaps, sample_count=None, want_valid: bool = True):
+    """rcq_phase2_host: concatenated host tables -> (nident_sum, denom_sum, valid, counts).
+    Raises NoIdealComponents (after filling the sums) like the reference's NoIdealComponentsError."""
+    row_off = np.ascontiguousarray(row_off, dtype=np.int64)
+    n_tables = len(row_off) - 1
+    arrs = [np.ascontiguousarray(a, dtype=np.int32) for a in (t_s, t_q, sgene, qgene, nident, length, gaps)]
+    ni = np.zeros(max(n_tables, 1), dtype=np.int64)
+    de = np.zeros(max(n_tables, 1), dtype=np.int64)
+    valid = np.zeros(n_samples * stride, dtype=np.uint8) if want_valid else None
+    counts = np.zeros(5, dtype=np.int64)
+    code = lib().rcq_phase2_host(ctx.h, n_samples, stride, n_tables, row_off.ctypes.data, *[a.ctypes.data for a in arrs],
+                                 int(sample_count or 0), ni.ctypes.data, de.ctypes.data, _ptr(valid), counts.ctypes.data)
+    res = dict(nident_sum=ni[:n_tables], denom_sum=de[:n_tables], valid=valid,
+               counts=dict(zip(["components", "ideal", "sample_count", "nodes", "edges"], counts.tolist())))
+    if code == -4:
+        res["no_ideal"] = True
+        return res
+    check(code)
+    res["no_ideal"] = False
+    return res
+
+
+def phase2_tables(ctx: Context, n_samples: int, stride: int, tables, t_s, t_q, sample_count=None,
+                  want_valid: bool = True):
+    """rcq_phase2_tables: device-resident tables straight from search_pair."""
+    n_tables = len(tables)
+    hs = (C.c_void_p * max(n_tables, 1))(*[t.h for t in tables])
+    t_s = np.ascontiguousarray(t_s, dtype=np.int32)
+    t_q = np.ascontiguousarray(t_q, dtype=np.int32)
+    ni = np.zeros(max(n_tables, 1), dtype=np.int64)
+    de = np.zeros(max(n_tables, 1), dtype=np.int64)
+    valid = np.zeros(n_samples * stride, dtype=np.uint8) if want_valid else None
+    counts = np.zeros(5, dtype=np.int64)
+    code = lib().rcq_phase2_tables(ctx.h, n_samples, stride, n_tables, hs, t_s.ctypes.data, t_q.ctypes.data,
+                                   int(sample_count or 0), ni.ctypes.data, de.ctypes.data, _ptr(valid), counts.ctypes.data)
+    res = dict(nident_sum=ni[:n_tables], denom_sum=de[:n_tables], valid=valid,
+               counts=dict(zip(["components", "ideal", "sample_count", "nodes", "edges"], counts.tolist())))
+    if code == -4:
+        res["no_ideal"] = True
+        return res
+    check(code)
+    res["no_ideal"] = False
+    return res

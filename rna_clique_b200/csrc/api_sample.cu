@@ -5,7 +5,7 @@
 thread_local std::string g_rcq_err;
 
 int rcq_sample_build(rcq_ctx* ctx, rcq_sample* s, const uint8_t* d_ascii, int64_t ascii_len,
-                     const int64_t* d_offsets);  // sample.cu
+                     const int64_t* d_starts);  // sample.cu
 
 extern "C" {
 
@@ -23,6 +23,7 @@ int rcq_ctx_create(int device, rcq_ctx** out) {
     CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     CU(cudaMallocHost((void**)&c->h_pin, 64 * sizeof(int64_t)));
     CU(cudaMalloc((void**)&c->d_ctr, 64 * sizeof(int64_t)));
+    for (int i = 0; i < 16; i++) CU(cudaEventCreate(&c->ev[i]));
     cudaMemPool_t pool;
     CU(cudaDeviceGetDefaultMemPool(&pool, device));
     uint64_t thr = UINT64_MAX;  // keep freed blocks in the pool: no OS round trips per pair
@@ -36,6 +37,7 @@ void rcq_ctx_destroy(rcq_ctx* c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     if (c->dbg_hsp) cudaFree(c->dbg_hsp);
+    for (int i = 0; i < 16; i++) cudaEventDestroy(c->ev[i]);
     cudaFreeHost(c->h_pin);
     cudaFree(c->d_ctr);
     cudaStreamDestroy(c->stream);
@@ -48,11 +50,21 @@ int rcq_ctx_sync(rcq_ctx* c) {
 }
 void* rcq_ctx_stream(rcq_ctx* c) { return (void*)c->stream; }
 int64_t rcq_ctx_launches(rcq_ctx* c) { return c->launches; }
+int rcq_ctx_stage_times(rcq_ctx* c, double ms[8], int64_t calls[8], int reset) {
+    CU(cudaStreamSynchronize(c->stream));
+    stage_collect(c);
+    for (int i = 0; i < 8; i++) {
+        if (ms) ms[i] = c->stage_ms[i];
+        if (calls) calls[i] = c->stage_calls[i];
+        if (reset) { c->stage_ms[i] = 0; c->stage_calls[i] = 0; }
+    }
+    return 0;
+}
 
-int rcq_sample_create(rcq_ctx* ctx, const uint8_t* ascii, int ascii_on_device,
-                      const int64_t* offsets, const int32_t* gene, const int32_t* iso,
-                      int32_t n_seq, rcq_sample** out) {
-    if (!ctx || !out || n_seq < 0 || (n_seq > 0 && (!ascii || !offsets || !gene || !iso)))
+int rcq_sample_create(rcq_ctx* ctx, const uint8_t* ascii, int64_t ascii_len, int ascii_on_device,
+                      const int64_t* starts, const int32_t* lengths, const int32_t* gene,
+                      const int32_t* iso, int32_t n_seq, rcq_sample** out) {
+    if (!ctx || !out || n_seq < 0 || ascii_len < 0 || (n_seq > 0 && (!ascii || !starts || !lengths || !gene || !iso)))
         return rcq_fail(RCQ_ERR_ARG, "rcq_sample_create: bad argument");
     CU(cudaSetDevice(ctx->device));
     rcq_sample* s = new rcq_sample();
@@ -63,8 +75,11 @@ int rcq_sample_create(rcq_ctx* ctx, const uint8_t* ascii, int ascii_on_device,
     int64_t pos = 64, total = 0;
     int32_t max_len = 0;
     for (int32_t t = 0; t < n_seq; t++) {
-        int64_t l = offsets[t + 1] - offsets[t];
-        if (l < 0 || l > 0x3fffffff) { delete s; return rcq_fail(RCQ_ERR_ARG, "rcq_sample_create: bad offsets"); }
+        int64_t l = lengths[t];
+        if (l < 0 || l > 1000000 || starts[t] < 0 || starts[t] + l > ascii_len) {
+            delete s;
+            return rcq_fail(RCQ_ERR_ARG, "rcq_sample_create: transcript outside ascii[] or longer than 1,000,000 bases");
+        }
         aoff[t] = (int32_t)pos;
         len[t] = (int32_t)l;
         if (l > max_len) max_len = (int32_t)l;
@@ -75,18 +90,16 @@ int rcq_sample_create(rcq_ctx* ctx, const uint8_t* ascii, int ascii_on_device,
     s->total = total;
     s->max_len = max_len;
     s->arena = ((pos + 63) & ~63ll) + 128;
-    int64_t ascii_len = n_seq ? offsets[n_seq] : 0;
-    int64_t base0 = n_seq ? offsets[0] : 0;
     const uint8_t* d_ascii = ascii;
     uint8_t* own_ascii = nullptr;
-    int64_t* d_offsets = nullptr;
-    RC(dalloc(ctx, &d_offsets, n_seq + 1));
+    int64_t* d_starts = nullptr;
+    RC(dalloc(ctx, &d_starts, n_seq));
     if (!ascii_on_device && n_seq) {
-        RC(dalloc(ctx, &own_ascii, ascii_len - base0 + 64));
-        CU(cudaMemcpyAsync(own_ascii, ascii + base0, ascii_len - base0, cudaMemcpyHostToDevice, ctx->stream));
-        d_ascii = own_ascii - base0;  // so that offsets index it directly
+        RC(dalloc(ctx, &own_ascii, ascii_len + 64));
+        CU(cudaMemcpyAsync(own_ascii, ascii, ascii_len, cudaMemcpyHostToDevice, ctx->stream));
+        d_ascii = own_ascii;
     }
-    if (n_seq) CU(cudaMemcpyAsync(d_offsets, offsets, (n_seq + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, ctx->stream));
+    if (n_seq) CU(cudaMemcpyAsync(d_starts, starts, n_seq * sizeof(int64_t), cudaMemcpyHostToDevice, ctx->stream));
     RC(dalloc(ctx, &s->off, n_seq));
     RC(dalloc(ctx, &s->len, n_seq));
     RC(dalloc(ctx, &s->gene, n_seq));
@@ -108,11 +121,14 @@ int rcq_sample_create(rcq_ctx* ctx, const uint8_t* ascii, int ascii_on_device,
         CU(cudaMemcpyAsync(s->gene, gene, n_seq * 4, cudaMemcpyHostToDevice, ctx->stream));
         CU(cudaMemcpyAsync(s->iso, iso, n_seq * 4, cudaMemcpyHostToDevice, ctx->stream));
     }
-    int rc = rcq_sample_build(ctx, s, d_ascii, ascii_len, d_offsets);
+    stage_tic(ctx, 0);
+    int rc = rcq_sample_build(ctx, s, d_ascii, ascii_len, d_starts);
+    stage_toc(ctx, 0);
     // the host staging vectors (aoff, len) must outlive the async copies
     cudaStreamSynchronize(ctx->stream);
+    stage_collect(ctx);
     dfree(ctx, own_ascii);
-    dfree(ctx, d_offsets);
+    dfree(ctx, d_starts);
     if (rc) { rcq_sample_free(s); return rc; }
     *out = s;
     return 0;

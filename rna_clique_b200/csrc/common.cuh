@@ -46,7 +46,28 @@ struct rcq_ctx {
     // debug: gapped HSPs of the last search (device, 12 int32 each)
     int32_t* dbg_hsp = nullptr;
     int64_t dbg_n = 0;
+    // per-stage device time (CUDA events on this stream), accumulated across calls:
+    // 0 pack+index, 1 seed join, 2 ungapped, 3 sort/group, 4 gapped DP, 5 selection+table, 6 phase 2
+    double stage_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    int64_t stage_calls[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    cudaEvent_t ev[16] = {};
+    int pending[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 };
+
+// stage timers: tic/toc record events; collect() folds every pending pair after a stream sync
+static inline void stage_tic(rcq_ctx* c, int st) { cudaEventRecord(c->ev[2 * st], c->stream); }
+static inline void stage_toc(rcq_ctx* c, int st) { cudaEventRecord(c->ev[2 * st + 1], c->stream); c->pending[st] = 1; }
+static inline void stage_collect(rcq_ctx* c) {
+    for (int st = 0; st < 8; st++)
+        if (c->pending[st]) {
+            float ms = 0;
+            if (cudaEventElapsedTime(&ms, c->ev[2 * st], c->ev[2 * st + 1]) == cudaSuccess) {
+                c->stage_ms[st] += ms;
+                c->stage_calls[st]++;
+            }
+            c->pending[st] = 0;
+        }
+}
 
 // stream-ordered device allocation (pool keeps memory; no OS round trips in steady state)
 template <typename T>

@@ -164,6 +164,7 @@ static int phase2_run(rcq_ctx* ctx, P2View V, int32_t sample_count, int64_t* nid
     CU(cudaMemsetAsync(d_ni, 0, (size_t)std::max(V.n_tables, 1) * 8, ctx->stream));
     CU(cudaMemsetAsync(d_de, 0, (size_t)std::max(V.n_tables, 1) * 8, ctx->stream));
     CU(cudaMemsetAsync(ctr, 0, 16 * sizeof(int64_t), ctx->stream));
+    stage_tic(ctx, 6);
     LAUNCH(ctx, k_p2_init, grid_for(n_nodes, 256), 256, 0, V.parent, n_nodes);
     if (V.n_rows) LAUNCH(ctx, k_p2_union, grid_for(V.n_rows, 256), 256, 0, V);
     LAUNCH(ctx, k_p2_flatten, grid_for(n_nodes, 256), 256, 0, V, n_nodes, ctr, spresent);
@@ -177,6 +178,7 @@ static int phase2_run(rcq_ctx* ctx, P2View V, int32_t sample_count, int64_t* nid
     }
     LAUNCH(ctx, k_p2_valid, grid_for(n_nodes, 256), 256, 0, V, n_nodes, sample_count, valid, ctr);
     if (V.n_rows) LAUNCH(ctx, k_p2_reduce, grid_for(V.n_rows, 256), 256, 0, V, valid, d_ni, d_de);
+    stage_toc(ctx, 6);
     if (V.n_tables) {
         CU(cudaMemcpyAsync(nident_sum, d_ni, (size_t)V.n_tables * 8, cudaMemcpyDeviceToHost, ctx->stream));
         CU(cudaMemcpyAsync(denom_sum, d_de, (size_t)V.n_tables * 8, cudaMemcpyDeviceToHost, ctx->stream));
@@ -184,6 +186,7 @@ static int phase2_run(rcq_ctx* ctx, P2View V, int32_t sample_count, int64_t* nid
     if (valid_out) CU(cudaMemcpyAsync(valid_out, valid, n_nodes, cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaMemcpyAsync(ctx->h_pin, ctr, 8 * sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
+    stage_collect(ctx);
     if (counts) {
         counts[0] = ctx->h_pin[0]; counts[1] = ctx->h_pin[1]; counts[2] = sample_count;
         counts[3] = ctx->h_pin[3]; counts[4] = ctx->h_pin[4];

@@ -18,14 +18,14 @@ __device__ __forceinline__ uint32_t base_code(uint32_t c) {  // 0..3, or 4 = not
 // letters come from two aligned 16-byte vector loads funnel-shifted to the transcript's byte
 // alignment (coalesced: a warp iteration reads one contiguous 512(+16)-byte span).
 __global__ void k_pack(const uint8_t* __restrict__ ascii, int64_t ascii_len,
-                       const int64_t* __restrict__ offsets, const int32_t* __restrict__ aoff,
-                       int32_t n_seq, uint32_t* __restrict__ fwd, uint32_t* __restrict__ mask,
+                       const int64_t* __restrict__ starts, const int32_t* __restrict__ aoff,
+                       const int32_t* __restrict__ len, int32_t n_seq, uint32_t* __restrict__ fwd, uint32_t* __restrict__ mask,
                        unsigned long long* __restrict__ n_masked) {
     int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     int nwarps = (gridDim.x * blockDim.x) >> 5;
     for (int t = warp; t < n_seq; t += nwarps) {
-        int64_t src = offsets[t];
-        int32_t n = (int32_t)(offsets[t + 1] - src);
+        int64_t src = starts[t];
+        int32_t n = len[t];
         int64_t dst = aoff[t];
         unsigned long long masked = 0;
         for (int32_t c = 0; c < n; c += 512) {
@@ -219,7 +219,7 @@ int rcq_sort_u64(rcq_ctx* ctx, uint64_t* keys, int64_t n) { return sort_u64(ctx,
 
 // Pack + reverse complement + minimizer index for one sample (stream-ordered).
 int rcq_sample_build(rcq_ctx* ctx, rcq_sample* s, const uint8_t* d_ascii, int64_t ascii_len,
-                     const int64_t* d_offsets) {
+                     const int64_t* d_starts) {
     int64_t words = s->arena / 16, mwords = s->arena / 32;
     RC(dalloc(ctx, &s->fwd, words));
     RC(dalloc(ctx, &s->rc, words));
@@ -236,7 +236,7 @@ int rcq_sample_build(rcq_ctx* ctx, rcq_sample* s, const uint8_t* d_ascii, int64_
     CU(cudaMemsetAsync(ctr, 0, 2 * sizeof(unsigned long long), ctx->stream));
     int blocks = RCQ_SMS * 8;
     if (s->n_seq) {
-        LAUNCH(ctx, k_pack, blocks, 256, 0, d_ascii, ascii_len, d_offsets, s->off, s->n_seq, s->fwd,
+        LAUNCH(ctx, k_pack, blocks, 256, 0, d_ascii, ascii_len, d_starts, s->off, s->len, s->n_seq, s->fwd,
                s->mask, ctr);
         LAUNCH(ctx, k_revcomp, blocks, 256, 0, s->fwd, s->mask, s->off, s->len, s->n_seq, s->rc,
                s->mask_rc);

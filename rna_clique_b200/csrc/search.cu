@@ -69,9 +69,12 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
     for (int attempt = 0; attempt < 2 && s1->n_index && s2->n_index; attempt++) {
         RC(dalloc(ctx, &seeds, cap));
         CU(cudaMemsetAsync(ctr, 0, 16 * sizeof(int64_t), ctx->stream));
+        stage_tic(ctx, 1);
         LAUNCH(ctx, k_seed_join, grid_for(s1->n_index, 256), 256, 0, s1->index, s1->n_index, s2->index,
                s2->dir, P, seeds, cap, ctr);
+        stage_toc(ctx, 1);
         RC(read_counters(ctx, 2));
+        stage_collect(ctx);
         n_seeds = ctx->h_pin[0];
         st.n_candidates = ctx->h_pin[1];
         if (n_seeds <= cap) break;
@@ -87,7 +90,10 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
         Ungapped* U = nullptr;
         RC(dalloc(ctx, &U, n_seeds));
         CU(cudaMemsetAsync(ctr, 0, 16 * sizeof(int64_t), ctx->stream));
+        stage_tic(ctx, 2);
         LAUNCH(ctx, k_ungapped, grid_for(n_seeds, 256), 256, 0, seeds, n_seeds, P, U, ctr + 4);
+        stage_toc(ctx, 2);
+        stage_tic(ctx, 3);
         dfree(ctx, seeds); seeds = nullptr;
         uint64_t* keys = nullptr; uint32_t* order = nullptr; uint32_t* heads = nullptr;
         RC(dalloc(ctx, &keys, n_seeds));
@@ -96,7 +102,9 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
         LAUNCH(ctx, k_group_keys, grid_for(n_seeds, 256), 256, 0, U, n_seeds, keys, order);
         RC(sort_pairs_u64_u32(ctx, &keys, &order, n_seeds, 64));
         LAUNCH(ctx, k_group_heads, grid_for(n_seeds, 256), 256, 0, keys, n_seeds, heads, ctr + 5);
+        stage_toc(ctx, 3);
         RC(read_counters(ctx, 6));
+        stage_collect(ctx);
         st.ungapped_cells = ctx->h_pin[4];
         int64_t n_groups = ctx->h_pin[5];
         st.n_ungapped = n_seeds;
@@ -109,8 +117,10 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
         int32_t* scratch = nullptr;
         RC(dalloc(ctx, &scratch, per_warp * blocks * (threads / 32)));
         CU(cudaMemsetAsync(ctr, 0, 16 * sizeof(int64_t), ctx->stream));
+        stage_tic(ctx, 4);
         if (has_n) LAUNCH(ctx, k_gapped<true>, blocks, threads, 0, U, order, keys, n_seeds, heads, n_groups, P, G, scratch, per_warp, ctr);
         else LAUNCH(ctx, k_gapped<false>, blocks, threads, 0, U, order, keys, n_seeds, heads, n_groups, P, G, scratch, per_warp, ctr);
+        stage_toc(ctx, 4);
         dfree(ctx, scratch); dfree(ctx, U); dfree(ctx, keys); dfree(ctx, order); dfree(ctx, heads);
         // ---- compact (stable: group order, then processing order inside the group)
         RC(dalloc(ctx, &Gd, n_seeds));
@@ -169,6 +179,7 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
         RC(dalloc(ctx, &rkeys, 2 * n_gapped));
         RC(dalloc(ctx, &rdesc, 2 * n_gapped));
         int g = grid_for(n_gapped, 256);
+        stage_tic(ctx, 5);
         LAUNCH(ctx, k_sel_best, g, 256, 0, V);
         LAUNCH(ctx, k_sel_pairs, g, 256, 0, V);
         LAUNCH(ctx, k_sel_pairbest, g, 256, 0, V);
@@ -185,6 +196,7 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
             LAUNCH(ctx, k_sel_fill, grid_for(n_rows, 256), 256, 0, Gd, rdesc, n_rows, s1->len, s2->len,
                    s1->gene, s1->iso, s2->gene, s2->iso, T->cols);
         }
+        stage_toc(ctx, 5);
         dfree(ctx, rkeys); dfree(ctx, rdesc);
         dfree(ctx, V.pass); dfree(ctx, V.bestF); dfree(ctx, V.bestB); dfree(ctx, V.bestQ);
         dfree(ctx, V.firstkey); dfree(ctx, V.hkeys); dfree(ctx, V.hflags); dfree(ctx, V.hbest);
@@ -192,6 +204,8 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
     dfree(ctx, Gd);
     T->n = n_rows;
     st.n_rows = n_rows;
+    CU(cudaStreamSynchronize(ctx->stream));
+    stage_collect(ctx);
     if (stats) *stats = st;
     return 0;
 }

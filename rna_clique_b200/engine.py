@@ -1,0 +1,142 @@
+"""In-memory all-vs-all engine: the device-resident form of the reference's phase 1 + phase 2.
+
+  select_top_genes()  host, bit-exact restatement target of select_top_genes.py:108-127
+  Engine.upload()     kernels (1)+(2)            (replaces makeblastdb, find_all_pairs.py:120-159)
+  Engine.search()     kernel (3) per unordered pair (replaces 2x blastn + find_homologs.py:215-302)
+  Engine.distances()  kernel (4) on the device-resident tables + exact Fractions on the host
+                      (build_graph.py, filtered_distance.py, similarity_computer.py)
+
+Multi-GPU (one process per GPU): pairs are sharded round-robin by estimated cost; the only
+collective is an all-gather of the flat hit tables (torch.distributed, NCCL) before phase 2.
+"""
+from __future__ import annotations
+
+import itertools
+from fractions import Fraction
+from typing import Optional, Sequence
+
+import numpy as np
+
+from . import _native
+
+
+class NoIdealComponentsError(Exception):
+    """Reference: filtered_distance.py:126-127."""
+
+
+def select_top_genes(coverage: np.ndarray, gene: np.ndarray, top: int) -> np.ndarray:
+    """Indices (file order) of every transcript whose gene is among the `top` genes by
+    max-isoform coverage.  Ties: heapq.nlargest over (coverage, gene) tuples => larger gene id
+    wins (select_top_genes.py:108-127).  Coverage starts from 0.0 (defaultdict(float))."""
+    coverage = np.asarray(coverage, dtype=np.float64)
+    gene = np.asarray(gene)
+    ug, inv = np.unique(gene, return_inverse=True)
+    best = np.zeros(len(ug), dtype=np.float64)
+    np.maximum.at(best, inv, coverage)
+    if top >= len(ug):
+        keep_gene = np.ones(len(ug), dtype=bool)
+    elif top <= 0:
+        keep_gene = np.zeros(len(ug), dtype=bool)
+    else:
+        order = np.lexsort((ug, best))            # ascending by coverage, then gene
+        keep_gene = np.zeros(len(ug), dtype=bool)
+        keep_gene[order[len(ug) - top:]] = True
+    return np.flatnonzero(keep_gene[inv])
+
+
+def schedule_pairs(n: int, totals: Sequence[int], world: int):
+    """All unordered pairs in itertools.combinations order, and the rank that owns each:
+    greedy longest-processing-time assignment by estimated cost L_i + L_j."""
+    pairs = list(itertools.combinations(range(n), 2))
+    cost = [totals[i] + totals[j] for i, j in pairs]
+    owner = [0] * len(pairs)
+    load = [0] * world
+    for k in sorted(range(len(pairs)), key=lambda k: (-cost[k], k)):
+        r = min(range(world), key=lambda r: (load[r], r))
+        owner[k] = r
+        load[r] += cost[k]
+    return pairs, owner
+
+
+class Engine:
+    def __init__(self, device: int = 0):
+        self.ctx = _native.Context(device)
+        self.device = device
+
+    # ---- kernels (1)+(2)
+    def upload(self, ascii_, starts, lengths, gene, iso, name: str = "") -> _native.Sample:
+        return _native.Sample(self.ctx, ascii_, starts, gene, iso, name=name, lengths=lengths)
+
+    # ---- kernel (3)
+    def search(self, samples, pairs=None, evalue: float = 1e-99, top_n: int = 1, keep_all: bool = True):
+        """Returns (pairs, tables): tables[k] joins samples pairs[k] = (i, j), i = transcripts1."""
+        if pairs is None:
+            pairs = list(itertools.combinations(range(len(samples)), 2))
+        tables = [_native.search_pair(self.ctx, samples[i], samples[j], evalue, top_n, keep_all) for i, j in pairs]
+        return pairs, tables
+
+    # ---- kernel (4)
+    def phase2(self, n_samples: int, pairs, tables, stride: int, sample_count: Optional[int] = None,
+               want_valid: bool = False):
+        return _native.phase2_tables(self.ctx, n_samples, stride, tables, [p[0] for p in pairs],
+                                     [p[1] for p in pairs], sample_count, want_valid)
+
+    @staticmethod
+    def matrix_from_sums(labels: Sequence[str], pairs, nident_sum, denom_sum):
+        """Exact rational similarity per pair, d = 1 - sim, float() last; rows/cols sorted by label
+        (similarity_computer.py:216-251,285-312).  Raises NoIdealComponentsError on an empty table."""
+        present = sorted({labels[i] for p in pairs for i in p})
+        pos = {s: k for k, s in enumerate(present)}
+        m = np.zeros((len(present), len(present)), dtype=np.float64)
+        for (i, j), ni, de in zip(pairs, nident_sum, denom_sum):
+            if int(de) == 0:
+                raise NoIdealComponentsError()
+            d = float(1 - Fraction(int(ni), int(de)))
+            m[pos[labels[i]], pos[labels[j]]] = d
+            m[pos[labels[j]], pos[labels[i]]] = d
+        return present, m
+
+    def all_vs_all(self, inputs, labels, top_genes: Optional[int] = None, evalue: float = 1e-99,
+                   top_n: int = 1, keep_all: bool = True, dist=None, keep_tables: bool = False):
+        """inputs[k] = dict(ascii=uint8 array/tensor, starts, lengths, coverage, gene, iso) for sample k.
+        Returns dict(labels, matrix, sums, pairs, stats[, tables, samples])."""
+        world = dist.get_world_size() if dist is not None else 1
+        rank = dist.get_rank() if dist is not None else 0
+        samples = []
+        for k, s in enumerate(inputs):
+            starts, lengths, gene, iso = (np.asarray(s[c]) for c in ("starts", "lengths", "gene", "iso"))
+            if top_genes is not None:
+                keep = select_top_genes(s["coverage"], gene, top_genes)
+                starts, lengths, gene, iso = starts[keep], lengths[keep], gene[keep], iso[keep]
+            samples.append(self.upload(s["ascii"], starts, lengths, gene, iso, name=labels[k]))
+        n = len(samples)
+        pairs, owner = schedule_pairs(n, [s.total for s in samples], world)
+        mine = [k for k in range(len(pairs)) if owner[k] == rank]
+        _, my_tables = self.search(samples, [pairs[k] for k in mine], evalue, top_n, keep_all)
+        stats = {}
+        for t in my_tables:
+            for key, v in t.stats.items():
+                stats[key] = stats.get(key, 0) + v
+        if world > 1:
+            from .exchange import allgather_tables
+            tables = allgather_tables(self.ctx, dist, pairs, owner, mine, my_tables)
+        else:
+            tables = my_tables
+        stride = 1 + max([0] + [int(np.max(s["gene"], initial=0)) for s in inputs])
+        res = self.phase2(n, pairs, tables, stride)
+        out = dict(pairs=pairs, nident_sum=res["nident_sum"], denom_sum=res["denom_sum"], counts=res["counts"],
+                   stats=stats, no_ideal=res["no_ideal"], n_local_pairs=len(mine),
+                   lengths=[s.total for s in samples])
+        if not res["no_ideal"]:
+            out["labels"], out["matrix"] = self.matrix_from_sums(labels, pairs, res["nident_sum"], res["denom_sum"])
+        if keep_tables:
+            out["tables"], out["samples"] = tables, samples
+        else:
+            for t in tables:
+                t.close()
+            for s in samples:
+                s.close()
+        return out
+
+    def close(self):
+        self.ctx.close()
