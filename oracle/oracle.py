@@ -49,6 +49,8 @@ def lib():
         L.orc_evalue.argtypes = [C.c_int32, C.c_int64, C.c_int64, C.c_int64]
         L.orc_bitscore.restype = C.c_double
         L.orc_bitscore.argtypes = [C.c_int32]
+        L.orc_set_gapped_mode.argtypes = [C.c_int]
+        L.orc_extend.argtypes = [C.c_char_p, C.c_int32, C.c_char_p, C.c_int32, C.c_int, C.c_void_p]
         _lib = L
     return _lib
 
@@ -105,3 +107,17 @@ def match_table_from_rows(fwd: np.ndarray, bwd: np.ndarray, top_n: int = 1, keep
     lib().orc_result_counts(r.h, c.ctypes.data)
     r.counts = dict(zip(["gapped", "fwd", "bwd", "rows", "seeds", "ungapped", "dp_cells"], c.tolist()))
     return r
+
+
+def set_gapped_mode(greedy: bool) -> None:
+    """True (default): greedy X-drop waves, the canonical gapped stage.  False: the anti-diagonal
+    X-drop DP kept as a cross-check (same scores and end points; it splits ties between two
+    mismatches and an insertion+deletion pair differently)."""
+    lib().orc_set_gapped_mode(int(bool(greedy)))
+
+
+def extend(q: bytes, s: bytes, greedy: bool = True) -> dict:
+    """One gapped extension of ASCII q against ASCII s from (0, 0)."""
+    out = np.zeros(6, dtype=np.int32)
+    lib().orc_extend(q, len(q), s, len(s), int(bool(greedy)), out.ctypes.data)
+    return dict(zip(["score2", "qi", "sj", "mismatch", "gaps", "gapopen"], out.tolist()))

@@ -253,6 +253,112 @@ static ext_t xdrop_extend(const uint8_t* q, int32_t qn, int qstep, const uint8_t
 }
 int64_t orc_dp_cells(void) { return g_dp_cells; }
 
+/* Greedy X-drop extension — the algorithm megablast itself uses for linear gap
+ * costs (Zhang, Schwartz, Wagner, Miller 2000; NCBI BLAST_GreedyAlign).  With reward 1, penalty
+ * -2 and gap cost 2.5 a path that ends on anti-diagonal t = i + j after d differences
+ * (mismatches + gap characters) scores exactly t - 6d in doubled units, so the search keeps, per
+ * difference count d and diagonal k = j - i, only the furthest row R(d, k) reachable.
+ *   wave 0     : slide from (0, 0) along diagonal 0 while bases match.
+ *   wave d >= 1: for every diagonal k in [L-1, U+1] (L..U = valid diagonals of wave d-1) the
+ *                entry row is the largest of   R(d-1, k) + 1   mismatch  (needs i<=qn, j<=sn)
+ *                                              R(d-1, k+1) + 1 consume q (U; needs i<=qn)
+ *                                              R(d-1, k-1)     consume s (L; needs j<=sn)
+ *                ties: mismatch, then U, then L.  The entry is dropped when its score
+ *                t - 6d < T(d - 19) - 108, T(x) = best score of waves <= x (0 for x < 0):
+ *                19 = floor((108 + 1) / 6) + 1 is BLAST's xdrop_offset.  Then slide.
+ *   stop       : when a wave has no valid diagonal.
+ * Best end point: highest score; ties -> smaller d, then smaller k.  Mismatch / gap / gap-opening
+ * counts travel with every (d, k) point: a gap character opens a new gap unless the point it
+ * comes from was entered by the same kind of gap and slid over no match. */
+static int64_t g_greedy_steps = 0;
+static ext_t greedy_extend(const uint8_t* q, int32_t qn, int qstep, const uint8_t* s, int32_t sn,
+                           int sstep) {
+    int32_t nd = qn + sn + 3;
+    int32_t* R[2]; int32_t* MM[2]; int32_t* GP[2]; int32_t* GO[2]; uint8_t* OP[2];
+    for (int x = 0; x < 2; x++) {
+        R[x] = malloc(sizeof(int32_t) * nd); MM[x] = calloc(nd, sizeof(int32_t));
+        GP[x] = calloc(nd, sizeof(int32_t)); GO[x] = calloc(nd, sizeof(int32_t)); OP[x] = calloc(nd, 1);
+    }
+    int32_t tcap = 64, *T = malloc(sizeof(int32_t) * tcap);
+#define IX(k) ((k) + qn + 1)
+#define QB(i) q[(int64_t)(i) * qstep]
+#define SB(j) s[(int64_t)(j) * sstep]
+    int32_t i = 0;
+    while (i < qn && i < sn && is_match(QB(i), SB(i))) i++;
+    g_greedy_steps += i + 1;
+    ext_t best = {2 * i, i, i, 0, 0, 0};
+    R[0][IX(0)] = i; OP[0][IX(0)] = 0;   /* op: bit0-1 entry op (0 D, 1 U, 2 L), bit2 = slid */
+    T[0] = 2 * i;
+    int32_t L = 0, U = 0;
+    for (int32_t d = 1; d <= qn + sn; d++) {
+        const int p = (d - 1) & 1, c = d & 1;
+        int32_t tref = d >= 19 ? T[d - 19] : 0;
+        int32_t nL = 1, nU = 0, wbest = NEG;
+        int32_t klo = L - 1 < -qn ? -qn : L - 1, khi = U + 1 > sn ? sn : U + 1;
+        for (int32_t k = klo; k <= khi; k++) {
+            int32_t bi = -1, mm = 0, gp = 0, go = 0; uint8_t op = 0;
+            if (k >= L && k <= U && R[p][IX(k)] >= 0) {
+                int32_t ci = R[p][IX(k)] + 1;
+                if (ci <= qn && ci + k <= sn) { bi = ci; mm = MM[p][IX(k)] + 1; gp = GP[p][IX(k)]; go = GO[p][IX(k)]; op = 0; }
+            }
+            if (k + 1 >= L && k + 1 <= U && R[p][IX(k + 1)] >= 0) {
+                int32_t ci = R[p][IX(k + 1)] + 1;
+                if (ci <= qn && ci > bi) {
+                    bi = ci; mm = MM[p][IX(k + 1)]; gp = GP[p][IX(k + 1)] + 1;
+                    go = GO[p][IX(k + 1)] + (OP[p][IX(k + 1)] != 1); op = 1;
+                }
+            }
+            if (k - 1 >= L && k - 1 <= U && R[p][IX(k - 1)] >= 0) {
+                int32_t ci = R[p][IX(k - 1)];
+                if (ci + k <= sn && ci > bi) {
+                    bi = ci; mm = MM[p][IX(k - 1)]; gp = GP[p][IX(k - 1)] + 1;
+                    go = GO[p][IX(k - 1)] + (OP[p][IX(k - 1)] != 2); op = 2;
+                }
+            }
+            R[c][IX(k)] = -1;
+            if (bi < 0) continue;
+            if (2 * bi + k - 6 * d < tref - XG2) continue;
+            int32_t e = bi;
+            while (e < qn && e + k < sn && is_match(QB(e), SB(e + k))) e++;
+            g_greedy_steps += e - bi + 1;
+            if (e > bi) op |= 4;
+            R[c][IX(k)] = e; MM[c][IX(k)] = mm; GP[c][IX(k)] = gp; GO[c][IX(k)] = go; OP[c][IX(k)] = op;
+            if (nL > nU) nL = k;
+            nU = k;
+            int32_t sc = 2 * e + k - 6 * d;
+            if (sc > wbest) wbest = sc;
+            if (sc > best.score2) { best.score2 = sc; best.qi = e; best.sj = e + k; best.mism = mm; best.gaps = gp; best.gapopen = go; }
+        }
+        if (d >= tcap) { tcap *= 2; T = realloc(T, sizeof(int32_t) * tcap); }
+        T[d] = wbest > T[d - 1] ? wbest : T[d - 1];
+        /* wave d-1's cells outside the new range must not be read as wave d+1's predecessors */
+        L = nL; U = nU;
+        if (L > U) break;
+    }
+#undef IX
+#undef QB
+#undef SB
+    for (int x = 0; x < 2; x++) { free(R[x]); free(MM[x]); free(GP[x]); free(GO[x]); free(OP[x]); }
+    free(T);
+    return best;
+}
+int64_t orc_greedy_steps(void) { return g_greedy_steps; }
+static int g_gapped_mode = 1;   /* 1 = greedy (canonical), 0 = anti-diagonal X-drop DP (cross-check) */
+void orc_set_gapped_mode(int m) { g_gapped_mode = m; }
+static ext_t gapped_extend(const uint8_t* q, int32_t qn, int qstep, const uint8_t* s, int32_t sn, int sstep) {
+    return g_gapped_mode ? greedy_extend(q, qn, qstep, s, sn, sstep) : xdrop_extend(q, qn, qstep, s, sn, sstep);
+}
+
+/* test hook: one extension of ASCII q against ASCII s (both forward); out = score2 qi sj mism gaps gapopen */
+void orc_extend(const uint8_t* q, int32_t qn, const uint8_t* s, int32_t sn, int mode, int32_t* out) {
+    uint8_t* a = malloc(qn + 1); uint8_t* b = malloc(sn + 1);
+    for (int32_t i = 0; i < qn; i++) a[i] = code_of(q[i]);
+    for (int32_t i = 0; i < sn; i++) b[i] = code_of(s[i]);
+    ext_t r = mode ? greedy_extend(a, qn, 1, b, sn, 1) : xdrop_extend(a, qn, 1, b, sn, 1);
+    out[0] = r.score2; out[1] = r.qi; out[2] = r.sj; out[3] = r.mism; out[4] = r.gaps; out[5] = r.gapopen;
+    free(a); free(b);
+}
+
 /* ------------------------------- seeds -> ungapped HSPs ------------------------------- */
 typedef struct { uint64_t key; int32_t tb, pos; int32_t minus; } kent_t;
 static int cmp_kent(const void* x, const void* y) {
@@ -373,8 +479,8 @@ static gapped_t gapped_from(const orc_sample* s1, const orc_sample* s2, const un
     int32_t lb = (int32_t)(s2->off[u->tb + 1] - s2->off[u->tb]);
     int32_t i0 = gapped_start(a, b, u), j0 = i0 + u->diag;
     /* left part consumes the anchor pair (i0, j0) first, walking backwards */
-    ext_t L = xdrop_extend(a + i0, i0 + 1, -1, b + j0, j0 + 1, -1);
-    ext_t R = xdrop_extend(a + i0 + 1, la - i0 - 1, 1, b + j0 + 1, lb - j0 - 1, 1);
+    ext_t L = gapped_extend(a + i0, i0 + 1, -1, b + j0, j0 + 1, -1);
+    ext_t R = gapped_extend(a + i0 + 1, la - i0 - 1, 1, b + j0 + 1, lb - j0 - 1, 1);
     gapped_t g;
     g.ta = u->ta; g.tb = u->tb; g.minus = u->minus;
     g.a0 = i0 + 1 - L.qi; g.a1 = i0 + 1 + R.qi;

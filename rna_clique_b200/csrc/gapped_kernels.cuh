@@ -1,225 +1,181 @@
-// gapped_kernels.cuh — kernel (3b): X-drop gapped extension with linear gap cost (megablast scoring:
-// +1/-2, gap 2.5 per position; kept doubled: +2/-4/-5; X-drop 100 bits = 54 -> 108 doubled).
+// gapped_kernels.cuh — kernel (3b): greedy X-drop gapped extension (megablast's own algorithm for
+// linear gap costs: Zhang, Schwartz, Wagner, Miller 2000; NCBI BLAST_GreedyAlign), scoring +1/-2,
+// gap 2.5 per position.  In doubled units a path that ends on anti-diagonal t = i + j after d
+// differences (mismatches + gap characters) scores exactly t - 6d, so per difference count d and
+// diagonal k = j - i only the furthest row R(d, k) is kept ("wave" d).  X-drop 100 bits = 54 raw
+// = 108 doubled, applied BLAST's way: an entry of wave d is dropped when its score is more than
+// 108 below the best score of waves <= d - 19 (19 = floor((108 + 1) / 6) + 1).
 //
-// One warp per (transcript of A, transcript of B, strand) group.  The DP runs in anti-diagonal
-// order: lane l owns the two diagonals k = -32+2l and k+1 of a 64-diagonal band, so every
-// anti-diagonal step computes one cell per lane from its own registers plus ONE neighbour value
-// moved with a warp shuffle (anti-diagonal propagation); the best score so far is shared with
-// redux.sync (__reduce_max_sync).  Score and alignment statistics (mismatches, gap characters,
-// gap openings, last operation) travel with the cell, so no traceback pass is needed.
-// The band is exact as long as no live cell touches its edge; otherwise the extension is redone
-// by the unbounded routine below, whose per-diagonal state lives in a global scratch row.
+// One warp per (transcript of A, transcript of B, strand) group.  A wave is processed 32 diagonals
+// at a time, one per lane: the three candidate entries come from the previous wave's row (a
+// shared-memory ring of 128 diagonals per warp; global scratch rows when a wave is wider), the
+// slide over matching bases is word-parallel (32 bases per XOR/compare of 2-bit words), and a
+// slide that survives its first 32 bases is finished by the whole warp together (1024 bases per
+// round).  Mismatch / gap / gap-opening counts travel with every (d, k) point, so there is no
+// traceback pass.  The wave loop stops early once no live diagonal can still beat the best score
+// (upper bound 2*min(qn, sn-k) + k - 6d), which ends a full-length extension the moment it
+// reaches the transcript ends.
 //
-// Roofline: integer-ALU bound (no HBM traffic to speak of: sequence words are re-read from L2
-// once per 31 cells).  Work unit: DP cells; reported as GCUPS.
+// Roofline: instruction-issue bound (L2-resident 2-bit words; no HBM traffic to speak of).
+// Work unit: base comparisons ("extension steps"), reported per search.
 #pragma once
 #include "search.cuh"
 
 #define NEG (-(1 << 29))
 #define FULL 0xffffffffu
+#define RCQ_RING 128            // diagonals per shared-memory row
+#define RCQ_XDROP_OFFSET 19     // floor((108 + 1) / 6) + 1
 
-struct ExtRes { int32_t score2, qi, sj, mism, gw; };  // gw = gaps<<16 | gapopen<<2 | lastop
+struct ExtRes { int32_t score2, qi, sj, mism, gw; };  // gw = gaps<<17 | gapopen<<3 | slid<<2 | entry op
 
-__device__ __forceinline__ int32_t gw_gap(int32_t gw, int32_t op) {  // op 1 = U, 2 = L
-    return ((gw & ~3) | op) + (1 << 16) + (((gw & 3) != op) ? 4 : 0);
-}
-
-__device__ __forceinline__ uint32_t base_at(const uint32_t* bits, int64_t p) {
-    return (__ldg(bits + (p >> 4)) >> ((p & 15) * 2)) & 3u;
-}
-__device__ __forceinline__ uint32_t mask_at(const uint32_t* mask, int64_t p) {
-    return mask ? ((__ldg(mask + (p >> 5)) >> (p & 31)) & 1u) : 0u;
-}
-
-// ---- fast path: 64-diagonal register band -------------------------------------------------
-// q bases at arena positions qpos + i (i in [0, qn)), s bases at spos + j.  Returns false when a
-// live cell reached the band edge (result invalid, caller falls back).
-template <bool HAS_N>
-__device__ bool xdrop_band64(const SeqArena Q, int64_t qpos, int32_t qn, const SeqArena S, int64_t spos,
-                             int32_t sn, ExtRes* res, unsigned long long* cells) {
+// number of matching base pairs from (qp, sp), at most lim (lim >= 0), computed by the whole warp
+__device__ __forceinline__ int32_t coop_slide(const SeqArena& Q, int64_t qp, const SeqArena& S, int64_t sp,
+                                              int32_t lim) {
     const int lane = threadIdx.x & 31;
-    const int32_t kA = -32 + 2 * lane;
-    int32_t hA = (lane == 16) ? 0 : NEG, hB = NEG, mA = 0, mB = 0, gA = 0, gB = 0;
-    int32_t bH = (lane == 16) ? 0 : NEG, bI = 0, bJ = 0, bM = 0, bG = 0;
-    int32_t gbest = 0;
-    uint64_t qw = 0, sw = 0;
-    uint32_t qm = 0, sm = 0;
-    unsigned long long ncell = 0;
-    const int32_t tmax_all = qn + sn;
+    int32_t base = 0;
+    while (base < lim) {
+        int32_t o = base + 32 * lane, z = 32;
+        if (o < lim) {
+            uint32_t m = match32(Q, qp + o, S, sp + o);
+            if (m != 0xFFFFFFFFu) z = __ffs(~m) - 1;
+            if (z > lim - o) z = lim - o;
+        } else z = 0;
+        unsigned stop = __ballot_sync(FULL, z < 32);
+        if (stop) {
+            int src = __ffs(stop) - 1;
+            return base + 32 * src + __shfl_sync(FULL, z, src);
+        }
+        base += 1024;
+    }
+    return lim;
+}
+
+// One extension by one warp.  rows: 6 arrays of rowlen int32 (R[2], M[2], G[2]); RING: index
+// k & (RCQ_RING-1) (returns false when a wave is wider than the ring), else index k + qn + 1.
+template <bool RING>
+__device__ bool greedy_extend(const SeqArena Q, int64_t qpos, int32_t qn, const SeqArena S, int64_t spos,
+                              int32_t sn, int32_t* rows, int32_t rowlen, ExtRes* res,
+                              unsigned long long* steps) {
+    const int lane = threadIdx.x & 31;
+    int32_t* Rr = rows; int32_t* Mr = rows + 2 * rowlen; int32_t* Gr = rows + 4 * rowlen;
+#define IX(k) (RING ? ((k) & (RCQ_RING - 1)) : ((k) + qn + 1))
+    // wave 0
+    int32_t i0 = coop_slide(Q, qpos, S, spos, min(qn, sn));
+    unsigned long long nstep = (lane == 0) ? (unsigned long long)(i0 + 1) : 0ull;
+    if (lane == 0) { Rr[IX(0)] = i0; Mr[IX(0)] = 0; Gr[IX(0)] = 0; }
+    int32_t bS = (lane == 0) ? 2 * i0 : NEG, bD = 0, bK = 0, bI = i0, bM = 0, bG = 0;
+    int32_t gb = 2 * i0;                 // best score so far (uniform)
+    int32_t Tl = (lane == 0) ? gb : 0;   // lane (d & 31) holds T[d]
+    int32_t Tprev = gb, L = 0, U = 0;
     bool ok = true;
-    for (int32_t p = 0; 2 * p + 1 <= tmax_all; p++) {
-        const int32_t c = p - lane + 16;      // iB; iA = c + 1
-        const int32_t jB = c + kA + 1;        // = jA
-        if (p % 31 == 0) {
-            qw = fetch32(Q.bits, qpos + c - 1);
-            sw = fetch32(S.bits, spos + jB - 1);
-            if (HAS_N) {
-                qm = Q.mask ? fetchmask32(Q.mask, qpos + c - 1) : 0u;
-                sm = S.mask ? fetchmask32(S.mask, spos + jB - 1) : 0u;
-            }
-        }
-        uint32_t q0 = (uint32_t)qw & 3u, q1 = (uint32_t)(qw >> 2) & 3u, s0 = (uint32_t)sw & 3u;
-        bool n0 = false, n1 = false;
-        if (HAS_N) { n0 = ((qm | sm) & 1u) != 0; n1 = (((qm >> 1) | sm) & 1u) != 0; }
-        qw >>= 2; sw >>= 2;
-        if (HAS_N) { qm >>= 1; sm >>= 1; }
-        // ---- sub-step 1: t = 2p+1, cells on diagonal kB = kA+1 at (iB, jB) = (c, jB)
-        bool any1;
-        {
-            int32_t hU = __shfl_down_sync(FULL, hA, 1), mU = __shfl_down_sync(FULL, mA, 1),
-                    gU = __shfl_down_sync(FULL, gA, 1);
-            if (lane == 31) hU = NEG;
-            bool valid = c >= 0 && jB >= 0 && c <= qn && jB <= sn;
-            int32_t h = NEG, m = 0, g = 0;
-            if (valid) {
-                ncell++;
-                if (c >= 1 && jB >= 1 && hB > NEG) {
-                    bool mt = (q0 == s0) && !n0;
-                    h = hB + (mt ? RCQ_MATCH2 : RCQ_MISMATCH2); m = mB + (mt ? 0 : 1); g = gB & ~3;
+    __syncwarp();
+    for (int32_t d = 1; d <= qn + sn; d++) {
+        const int32_t p = ((d - 1) & 1) * rowlen, c = (d & 1) * rowlen;
+        int32_t tref = __shfl_sync(FULL, Tl, (d - RCQ_XDROP_OFFSET) & 31);
+        if (d < RCQ_XDROP_OFFSET) tref = 0;
+        const int32_t klo = max(L - 1, -qn), khi = min(U + 1, sn);
+        if (RING && khi - klo + 1 > RCQ_RING) { ok = false; break; }
+        int32_t nL = 1 << 28, nU = -(1 << 28), wbest = NEG, ubmax = NEG;
+        for (int32_t kb = klo; kb <= khi; kb += 32) {
+            const int32_t k = kb + lane;
+            int32_t bi = -1, src = 0, op = 0;
+            if (k <= khi) {
+                if (k >= L && k <= U) {
+                    int32_t r = Rr[p + IX(k)];
+                    if (r >= 0 && r + 1 <= qn && r + 1 + k <= sn) { bi = r + 1; src = k; op = 0; }
                 }
-                if (c >= 1 && hU > NEG && hU + RCQ_GAP2 > h) { h = hU + RCQ_GAP2; m = mU; g = gw_gap(gU, 1); }
-                if (jB >= 1 && hA > NEG && hA + RCQ_GAP2 > h) { h = hA + RCQ_GAP2; m = mA; g = gw_gap(gA, 2); }
-                if (h < gbest - RCQ_XDROP_GAPPED2) h = NEG;
-            }
-            hB = h; mB = m; gB = g;
-            bool alive = h > NEG;
-            if (alive && h > bH) { bH = h; bI = c; bJ = jB; bM = m; bG = g; }
-            int32_t tm = __reduce_max_sync(FULL, alive ? h : NEG);
-            any1 = tm > NEG;
-            if (tm > gbest) gbest = tm;
-            if (__any_sync(FULL, alive && lane == 31)) ok = false;
-        }
-        // ---- sub-step 2: t = 2p+2, cells on diagonal kA at (c+1, jB)
-        bool any2 = false;
-        if (2 * p + 2 <= tmax_all) {
-            int32_t hL = __shfl_up_sync(FULL, hB, 1), mL = __shfl_up_sync(FULL, mB, 1),
-                    gL = __shfl_up_sync(FULL, gB, 1);
-            if (lane == 0) hL = NEG;
-            const int32_t iA = c + 1;
-            bool valid = iA >= 0 && jB >= 0 && iA <= qn && jB <= sn;
-            int32_t h = NEG, m = 0, g = 0;
-            if (valid) {
-                ncell++;
-                if (iA >= 1 && jB >= 1 && hA > NEG) {
-                    bool mt = (q1 == s0) && !n1;
-                    h = hA + (mt ? RCQ_MATCH2 : RCQ_MISMATCH2); m = mA + (mt ? 0 : 1); g = gA & ~3;
+                if (k + 1 >= L && k + 1 <= U) {
+                    int32_t r = Rr[p + IX(k + 1)];
+                    if (r >= 0 && r + 1 <= qn && r + 1 > bi) { bi = r + 1; src = k + 1; op = 1; }
                 }
-                if (iA >= 1 && hB > NEG && hB + RCQ_GAP2 > h) { h = hB + RCQ_GAP2; m = mB; g = gw_gap(gB, 1); }
-                if (jB >= 1 && hL > NEG && hL + RCQ_GAP2 > h) { h = hL + RCQ_GAP2; m = mL; g = gw_gap(gL, 2); }
-                if (h < gbest - RCQ_XDROP_GAPPED2) h = NEG;
+                if (k - 1 >= L && k - 1 <= U) {
+                    int32_t r = Rr[p + IX(k - 1)];
+                    if (r >= 0 && r + k <= sn && r > bi) { bi = r; src = k - 1; op = 2; }
+                }
+                if (bi >= 0 && 2 * bi + k - 6 * d < tref - RCQ_XDROP_GAPPED2) bi = -1;
             }
-            hA = h; mA = m; gA = g;
-            bool alive = h > NEG;
-            if (alive && h > bH) { bH = h; bI = iA; bJ = jB; bM = m; bG = g; }
-            int32_t tm = __reduce_max_sync(FULL, alive ? h : NEG);
-            any2 = tm > NEG;
-            if (tm > gbest) gbest = tm;
-            if (__any_sync(FULL, alive && lane == 0)) ok = false;
+            int32_t e = bi, mm = 0, gw = 0, lim = 0;
+            bool cont = false;
+            if (bi >= 0) {
+                mm = Mr[p + IX(src)];
+                int32_t g = Gr[p + IX(src)];
+                if (op == 0) { mm++; gw = g & ~7; }
+                else gw = ((g & ~7) | op) + (1 << 17) + (((g & 7) != op) ? 8 : 0);
+                lim = min(qn - bi, sn - bi - k);
+                int32_t z = 0;
+                if (lim > 0) {
+                    uint32_t m = match32(Q, qpos + bi, S, spos + bi + k);
+                    z = (m == 0xFFFFFFFFu) ? 32 : (__ffs(~m) - 1);
+                    if (z > lim) z = lim;
+                }
+                nstep += z + 1;
+                e = bi + z;
+                cont = (z == 32 && lim > 32);
+            }
+            unsigned more = __ballot_sync(FULL, cont);
+            while (more) {
+                int sl = __ffs(more) - 1;
+                more &= more - 1;
+                int32_t e2 = __shfl_sync(FULL, e, sl), k2 = __shfl_sync(FULL, k, sl), l2 = __shfl_sync(FULL, lim, sl);
+                int32_t extra = coop_slide(Q, qpos + e2, S, spos + e2 + k2, l2 - 32);
+                if (lane == sl) { e += extra; nstep += extra; }
+            }
+            if (k <= khi) {
+                if (bi >= 0) {
+                    if (e > bi) gw |= 4;
+                    Rr[c + IX(k)] = e; Mr[c + IX(k)] = mm; Gr[c + IX(k)] = gw;
+                    int32_t sc = 2 * e + k - 6 * d;
+                    wbest = max(wbest, sc);
+                    nL = min(nL, k); nU = max(nU, k);
+                    ubmax = max(ubmax, 2 * min(qn, sn - k) + k - 6 * d);
+                    if (sc > bS) { bS = sc; bD = d; bK = k; bI = e; bM = mm; bG = gw; }
+                } else {
+                    Rr[c + IX(k)] = -1;
+                }
+            }
         }
-        if (!ok) break;
-        if (!any1 && !any2) break;
+        wbest = __reduce_max_sync(FULL, wbest);
+        nL = __reduce_min_sync(FULL, nL);
+        nU = __reduce_max_sync(FULL, nU);
+        ubmax = __reduce_max_sync(FULL, ubmax);
+        Tprev = max(Tprev, wbest);
+        if (lane == (d & 31)) Tl = Tprev;
+        gb = max(gb, wbest);
+        L = nL; U = nU;
+        __syncwarp();
+        if (L > U) break;
+        if (ubmax <= gb) break;      // nothing still alive can beat the best end point
     }
-    for (int o = 16; o; o >>= 1) ncell += __shfl_down_sync(FULL, ncell, o);
-    if (lane == 0) *cells += ncell;
+#undef IX
+    for (int o = 16; o; o >>= 1) nstep += __shfl_down_sync(FULL, nstep, o);
+    if (lane == 0) *steps += nstep;
     if (!ok) return false;
-    // best end point: score desc, then t asc, then k asc
+    // best end point: score desc, then d asc, then k asc
     uint64_t key = 0;
-    if (bH > NEG) {
-        int32_t t = bI + bJ, k = bJ - bI;
-        key = ((uint64_t)(uint32_t)(bH + (1 << 20)) << 42) | ((uint64_t)((1 << 22) - 1 - t) << 20) |
-              (uint64_t)((1 << 20) - 1 - (k + (1 << 19)));
-    }
+    if (bS > NEG)
+        key = ((uint64_t)(uint32_t)(bS + (1 << 20)) << 42) | ((uint64_t)((1 << 21) - 1 - bD) << 21) |
+              (uint64_t)((1 << 21) - 1 - (bK + (1 << 20)));
     uint64_t best = key;
     for (int o = 16; o; o >>= 1) { uint64_t x = __shfl_xor_sync(FULL, best, o); if (x > best) best = x; }
     int src = __ffs(__ballot_sync(FULL, key == best)) - 1;
-    res->score2 = __shfl_sync(FULL, bH, src);
+    res->score2 = __shfl_sync(FULL, bS, src);
     res->qi = __shfl_sync(FULL, bI, src);
-    res->sj = __shfl_sync(FULL, bJ, src);
+    res->sj = res->qi + __shfl_sync(FULL, bK, src);
     res->mism = __shfl_sync(FULL, bM, src);
     res->gw = __shfl_sync(FULL, bG, src);
     return true;
 }
 
-// ---- general path: unbounded live window, per-diagonal state in a global scratch row -------
-// scratch: 3 * (qn + sn + 3) int32.  Same recurrence, same tie rules, same pruning.
-__device__ void xdrop_wide(const SeqArena Q, int64_t qpos, int32_t qn, const SeqArena S, int64_t spos,
-                           int32_t sn, int32_t* scratch, ExtRes* res, unsigned long long* cells) {
-    const int lane = threadIdx.x & 31;
-    const int32_t nd = qn + sn + 3;
-    int32_t *H = scratch, *MM = scratch + nd, *GW = scratch + 2 * nd;
-    for (int32_t x = lane; x < nd; x += 32) { H[x] = NEG; MM[x] = 0; GW[x] = 0; }
-    __syncwarp();
-#define IX(k) ((k) + qn + 1)
-    if (lane == 0) H[IX(0)] = 0;
-    __syncwarp();
-    int32_t bH = (lane == 0) ? 0 : NEG, bI = 0, bJ = 0, bM = 0, bG = 0;
-    int32_t gbest = 0, lo1 = 0, hi1 = 0, lo2 = 1, hi2 = 0;
-    unsigned long long ncell = 0;
-    for (int32_t t = 1; t <= qn + sn; t++) {
-        if (lo1 > hi1 && lo2 > hi2) break;
-        int32_t lo, hi;
-        if (lo1 > hi1) { lo = lo2; hi = hi2; }
-        else if (lo2 > hi2) { lo = lo1; hi = hi1; }
-        else { lo = min(lo1, lo2); hi = max(hi1, hi2); }
-        lo = max(lo - 1, -qn); hi = min(hi + 1, sn);
-        int32_t nlo = 1 << 28, nhi = -(1 << 28), tm = NEG;
-        int32_t k0 = lo + ((t - lo) & 1);
-        for (int32_t k = k0 + 2 * lane; k <= hi; k += 64) {
-            int32_t i = (t - k) >> 1, j = (t + k) >> 1;
-            if (i < 0 || j < 0 || i > qn || j > sn) continue;
-            ncell++;
-            int32_t h = NEG, m = 0, g = 0;
-            int32_t hd = H[IX(k)], hu = H[IX(k + 1)], hl = H[IX(k - 1)];
-            if (i >= 1 && j >= 1 && hd > NEG) {
-                bool mt = base_at(Q.bits, qpos + i - 1) == base_at(S.bits, spos + j - 1) &&
-                          !mask_at(Q.mask, qpos + i - 1) && !mask_at(S.mask, spos + j - 1);
-                h = hd + (mt ? RCQ_MATCH2 : RCQ_MISMATCH2); m = MM[IX(k)] + (mt ? 0 : 1); g = GW[IX(k)] & ~3;
-            }
-            if (i >= 1 && hu > NEG && hu + RCQ_GAP2 > h) { h = hu + RCQ_GAP2; m = MM[IX(k + 1)]; g = gw_gap(GW[IX(k + 1)], 1); }
-            if (j >= 1 && hl > NEG && hl + RCQ_GAP2 > h) { h = hl + RCQ_GAP2; m = MM[IX(k - 1)]; g = gw_gap(GW[IX(k - 1)], 2); }
-            if (h > NEG && h < gbest - RCQ_XDROP_GAPPED2) h = NEG;
-            H[IX(k)] = h; MM[IX(k)] = m; GW[IX(k)] = g;
-            if (h > NEG) {
-                nlo = min(nlo, k); nhi = max(nhi, k); tm = max(tm, h);
-                if (h > bH) { bH = h; bI = i; bJ = j; bM = m; bG = g; }
-            }
-        }
-        __syncwarp();
-        tm = __reduce_max_sync(FULL, tm);
-        nlo = __reduce_min_sync(FULL, nlo);
-        nhi = __reduce_max_sync(FULL, nhi);
-        if (tm > gbest) gbest = tm;
-        lo2 = lo1; hi2 = hi1;
-        if (tm > NEG) { lo1 = nlo; hi1 = nhi; } else { lo1 = 1; hi1 = 0; }
-    }
-#undef IX
-    for (int o = 16; o; o >>= 1) ncell += __shfl_down_sync(FULL, ncell, o);
-    if (lane == 0) *cells += ncell;
-    uint64_t key = 0;
-    if (bH > NEG) {
-        int32_t t = bI + bJ, k = bJ - bI;
-        key = ((uint64_t)(uint32_t)(bH + (1 << 20)) << 42) | ((uint64_t)((1 << 22) - 1 - t) << 20) |
-              (uint64_t)((1 << 20) - 1 - (k + (1 << 19)));
-    }
-    uint64_t best = key;
-    for (int o = 16; o; o >>= 1) { uint64_t x = __shfl_xor_sync(FULL, best, o); if (x > best) best = x; }
-    int src = __ffs(__ballot_sync(FULL, key == best)) - 1;
-    res->score2 = __shfl_sync(FULL, bH, src);
-    res->qi = __shfl_sync(FULL, bI, src);
-    res->sj = __shfl_sync(FULL, bJ, src);
-    res->mism = __shfl_sync(FULL, bM, src);
-    res->gw = __shfl_sync(FULL, bG, src);
-}
-
-// ---- one extension, fast path with fallback -------------------------------------------------
-template <bool HAS_N>
+// ---- one extension: shared-memory ring first, global rows when a wave outgrows it ------------
 __device__ __forceinline__ void extend(const SeqArena Q, int64_t qpos, int32_t qn, const SeqArena S,
-                                       int64_t spos, int32_t sn, int32_t* scratch, ExtRes* r,
-                                       unsigned long long* cells, unsigned long long* retries) {
-    if (!xdrop_band64<HAS_N>(Q, qpos, qn, S, spos, sn, r, cells)) {
+                                       int64_t spos, int32_t sn, int32_t* ring, int32_t* scratch, ExtRes* r,
+                                       unsigned long long* steps, unsigned long long* retries) {
+    if (!greedy_extend<true>(Q, qpos, qn, S, spos, sn, ring, RCQ_RING, r, steps)) {
         if ((threadIdx.x & 31) == 0) (*retries)++;
-        xdrop_wide(Q, qpos, qn, S, spos, sn, scratch, r, cells);
+        __syncwarp();
+        greedy_extend<false>(Q, qpos, qn, S, spos, sn, scratch, qn + sn + 3, r, steps);
     }
+    __syncwarp();
 }
 
 // canonical processing order inside a group: score desc, diag asc, a0 asc, a1 asc
@@ -234,7 +190,6 @@ __device__ __forceinline__ bool ung_before(const Ungapped& x, const Ungapped& y)
 // order; one contained in an earlier gapped HSP of the group is skipped; identical results are
 // dropped; at most RCQ_MAX_GAPPED_PER_GROUP gapped HSPs are kept.  Group g writes its results
 // to out[head .. head+count), the remaining slots of its range keep ta = -1.
-template <bool HAS_N>
 __global__ void __launch_bounds__(128) k_gapped(const Ungapped* __restrict__ U, const uint32_t* __restrict__ order,
                                                 const uint64_t* __restrict__ keys, int64_t n,
                                                 const uint32_t* __restrict__ heads, int64_t n_groups,
@@ -244,6 +199,8 @@ __global__ void __launch_bounds__(128) k_gapped(const Ungapped* __restrict__ U, 
     const int lane = threadIdx.x & 31;
     const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     int32_t* my_scratch = scratch + (int64_t)warp_global * scratch_per_warp;
+    __shared__ int32_t ring_all[4][6 * RCQ_RING];
+    int32_t* ring = ring_all[threadIdx.x >> 5];
     unsigned long long cells = 0, retries = 0, produced = 0;
     while (true) {
         unsigned long long g = 0;
@@ -296,16 +253,16 @@ __global__ void __launch_bounds__(128) k_gapped(const Ungapped* __restrict__ U, 
             if (__any_sync(FULL, contained)) continue;
             const int32_t i0 = cur.i0, j0 = i0 + cur.diag;
             ExtRes L, R;
-            extend<HAS_N>(P.Ar, oa + (la - 1 - i0), i0 + 1, Bo, ob + (lb - 1 - j0), j0 + 1, my_scratch, &L, &cells, &retries);
-            extend<HAS_N>(P.Af, oa + i0 + 1, la - i0 - 1, Bs, ob + j0 + 1, lb - j0 - 1, my_scratch, &R, &cells, &retries);
+            extend(P.Ar, oa + (la - 1 - i0), i0 + 1, Bo, ob + (lb - 1 - j0), j0 + 1, ring, my_scratch, &L, &cells, &retries);
+            extend(P.Af, oa + i0 + 1, la - i0 - 1, Bs, ob + j0 + 1, lb - j0 - 1, ring, my_scratch, &R, &cells, &retries);
             Gapped gp;
             gp.ta = ta; gp.tb = tb; gp.minus = minus;
             gp.a0 = i0 + 1 - L.qi; gp.a1 = i0 + 1 + R.qi;
             gp.b0 = j0 + 1 - L.sj; gp.b1 = j0 + 1 + R.sj;
             gp.score2 = L.score2 + R.score2;
             gp.mism = L.mism + R.mism;
-            gp.gaps = (L.gw >> 16) + (R.gw >> 16);
-            gp.gapopen = ((L.gw >> 2) & 0x3fff) + ((R.gw >> 2) & 0x3fff);
+            gp.gaps = (L.gw >> 17) + (R.gw >> 17);
+            gp.gapopen = ((L.gw >> 3) & 0x3fff) + ((R.gw >> 3) & 0x3fff);
             gp.nident = ((gp.a1 - gp.a0) + (gp.b1 - gp.b0) - gp.gaps) / 2 - gp.mism;
             bool dup = false;
             if (lane < count) {

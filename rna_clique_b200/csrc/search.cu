@@ -50,7 +50,6 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
     CU(cudaSetDevice(ctx->device));
     rcq_search_stats st;
     memset(&st, 0, sizeof st);
-    const bool has_n = s1->n_masked > 0 || s2->n_masked > 0;
     PairView P;
     P.Af = {s1->fwd, s1->n_masked ? s1->mask : nullptr};
     P.Ar = {s1->rc, s1->n_masked ? s1->mask_rc : nullptr};
@@ -113,13 +112,12 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
         RC(dalloc(ctx, &G, n_seeds));
         CU(cudaMemsetAsync(G, 0xFF, n_seeds * sizeof(Gapped), ctx->stream));
         const int blocks = RCQ_SMS * 8, threads = 128;
-        int64_t per_warp = 3ll * ((int64_t)s1->max_len + s2->max_len + 8);
+        int64_t per_warp = 6ll * ((int64_t)s1->max_len + s2->max_len + 8);
         int32_t* scratch = nullptr;
         RC(dalloc(ctx, &scratch, per_warp * blocks * (threads / 32)));
         CU(cudaMemsetAsync(ctr, 0, 16 * sizeof(int64_t), ctx->stream));
         stage_tic(ctx, 4);
-        if (has_n) LAUNCH(ctx, k_gapped<true>, blocks, threads, 0, U, order, keys, n_seeds, heads, n_groups, P, G, scratch, per_warp, ctr);
-        else LAUNCH(ctx, k_gapped<false>, blocks, threads, 0, U, order, keys, n_seeds, heads, n_groups, P, G, scratch, per_warp, ctr);
+        LAUNCH(ctx, k_gapped, blocks, threads, 0, U, order, keys, n_seeds, heads, n_groups, P, G, scratch, per_warp, ctr);
         stage_toc(ctx, 4);
         dfree(ctx, scratch); dfree(ctx, U); dfree(ctx, keys); dfree(ctx, order); dfree(ctx, heads);
         // ---- compact (stable: group order, then processing order inside the group)

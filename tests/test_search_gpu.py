@@ -63,6 +63,9 @@ def test_index_covers_every_28mer_window(ctx):
     dict(taxa=2, count=150, seed=1),
     dict(taxa=2, count=60, seed=2, mutation_rate=0.08),
     dict(taxa=2, count=60, seed=3, mutation_rate=0.03, indel_rate=0.004),
+    dict(taxa=2, count=120, seed=4, mutation_rate=0.15, indel_rate=0.01),
+    dict(taxa=2, count=80, seed=5, mutation_rate=0.05, indel_rate=0.03),
+    dict(taxa=2, count=40, seed=6, mutation_rate=0.02, indel_rate=0.002, len_loc=9000, len_n=4000),
 ])
 def test_search_pair_matches_oracle(ctx, kw):
     from rna_clique_b200 import _native
