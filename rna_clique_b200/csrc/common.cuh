@@ -116,3 +116,5 @@ __host__ __device__ static inline uint32_t rcq_mix32(uint32_t x) {
     x ^= x >> 16; x *= 0x85ebca6bu; x ^= x >> 13; x *= 0xc2b2ae35u; x ^= x >> 16;
     return x;
 }
+// index sort key of a minimizer hash (bijective, so equal keys <=> equal canonical 16-mers)
+__host__ __device__ static inline uint32_t rcq_index_key(uint32_t h) { return rcq_mix32(h ^ 0x9E3779B9u); }

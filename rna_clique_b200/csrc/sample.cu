@@ -179,12 +179,24 @@ __global__ void k_minimizers(const uint32_t* __restrict__ fwd, const uint32_t* _
                     if (FILL && sel) {
                         unsigned long long pos = (unsigned long long)(off + p);
                         out[base + __popc(m & ((1u << lane) - 1u))] =
-                            ((unsigned long long)h << 32) | (pos << 1) | so[wib][i + H];
+                            ((unsigned long long)rcq_index_key(h) << 32) | (pos << 1) | so[wib][i + H];
                         atomicOr(selmap + (pos >> 5), 1u << (pos & 31));
                     }
                 }
             }
         }
+    }
+}
+
+// blk2tx / ol tables: warp per transcript
+__global__ void k_tx_tables(const int32_t* __restrict__ aoff, const int32_t* __restrict__ len, int32_t n_seq,
+                            int32_t* __restrict__ blk2tx, int2* __restrict__ ol) {
+    int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    int nwarps = (gridDim.x * blockDim.x) >> 5;
+    for (int t = warp; t < n_seq; t += nwarps) {
+        int32_t o = aoff[t], n = len[t];
+        if (lane == 0) ol[t] = make_int2(o, n);
+        for (int32_t b = lane; b < ((n + 31) >> 5); b += 32) blk2tx[(o >> 5) + b] = t;
     }
 }
 
@@ -231,6 +243,9 @@ int rcq_sample_build(rcq_ctx* ctx, rcq_sample* s, const uint8_t* d_ascii, int64_
     CU(cudaMemsetAsync(s->mask, 0xFF, mwords * 4, ctx->stream));
     CU(cudaMemsetAsync(s->mask_rc, 0xFF, mwords * 4, ctx->stream));
     RC(dalloc(ctx, &s->sel, mwords));
+    RC(dalloc(ctx, &s->blk2tx, mwords));
+    RC(dalloc(ctx, &s->ol, s->n_seq));
+    CU(cudaMemsetAsync(s->blk2tx, 0, mwords * 4, ctx->stream));
     CU(cudaMemsetAsync(s->sel, 0, mwords * 4, ctx->stream));
     unsigned long long* ctr = (unsigned long long*)ctx->d_ctr;
     CU(cudaMemsetAsync(ctr, 0, 2 * sizeof(unsigned long long), ctx->stream));
@@ -238,6 +253,7 @@ int rcq_sample_build(rcq_ctx* ctx, rcq_sample* s, const uint8_t* d_ascii, int64_
     if (s->n_seq) {
         LAUNCH(ctx, k_pack, blocks, 256, 0, d_ascii, ascii_len, d_starts, s->off, s->len, s->n_seq, s->fwd,
                s->mask, ctr);
+        LAUNCH(ctx, k_tx_tables, blocks, 256, 0, s->off, s->len, s->n_seq, s->blk2tx, s->ol);
         LAUNCH(ctx, k_revcomp, blocks, 256, 0, s->fwd, s->mask, s->off, s->len, s->n_seq, s->rc,
                s->mask_rc);
         LAUNCH(ctx, k_minimizers<false>, blocks, 256, 0, s->fwd, s->mask, s->off, s->len, s->n_seq,

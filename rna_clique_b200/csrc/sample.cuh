@@ -7,9 +7,13 @@
 //                   it mismatches everything in extension)
 //   off[n_seq]      int32   arena offset of transcript t (multiple of 32 bases), len[n_seq]
 //   gene/iso[n_seq] int32
-//   index[n_index]  uint64  sorted minimizer entries  hash(canonical 16-mer)<<32 | pos<<1 | orient
+//   index[n_index]  uint64  sorted minimizer entries  key<<32 | pos<<1 | orient, key = a second
+//                   bijective mix of the canonical 16-mer hash: minimizer hashes crowd towards 0, the
+//                   remix spreads them evenly over the directory buckets
 //   dir[2^DIRBITS+1] uint32 first index entry of each hash-prefix bucket
 //   sel[arena/32]   uint32  bitmap of indexed positions;  gidx[n_seq] dense gene index
+//   blk2tx[arena/32] int32  transcript owning each 32-base block (transcripts start on block
+//                   boundaries);  ol[n_seq] int2 {off, len} for one-load transcript bounds
 #pragma once
 #include "common.cuh"
 
@@ -29,6 +33,8 @@ struct rcq_sample {
     uint32_t* dir = nullptr;
     uint32_t* sel = nullptr;   // arena/32 words: bit p set = position p holds an index entry
     int32_t* gidx = nullptr;   // dense index of gene[t] among the sample's sorted distinct genes
+    int32_t* blk2tx = nullptr; // arena/32 entries
+    int2* ol = nullptr;        // {off, len} per transcript
     int32_t n_genes = 0;
 };
 

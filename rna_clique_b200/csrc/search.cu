@@ -57,28 +57,36 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
     P.Br = {s2->rc, s2->n_masked ? s2->mask_rc : nullptr};
     P.offA = s1->off; P.lenA = s1->len; P.offB = s2->off; P.lenB = s2->len;
     P.nA = s1->n_seq; P.nB = s2->n_seq; P.selA = s1->sel; P.selB = s2->sel;
+    P.blkA = s1->blk2tx; P.blkB = s2->blk2tx; P.olA = s1->ol; P.olB = s2->ol;
     unsigned long long* ctr = (unsigned long long*)ctx->d_ctr;
     rcq_table* T = new rcq_table();
     T->ctx = ctx;
     *out = T;
 
-    // ---- seeds
+    // ---- seeds: probe (index join) -> candidate list -> verify
     Seed* seeds = nullptr;
+    uint2* cand = nullptr;
     int64_t n_seeds = 0, cap = std::max<int64_t>(1 << 20, 48ll * std::max(s1->n_seq, s2->n_seq));
-    for (int attempt = 0; attempt < 2 && s1->n_index && s2->n_index; attempt++) {
+    int64_t ccap = std::max<int64_t>(1 << 20, 2 * s1->n_index);
+    for (int attempt = 0; attempt < 3 && s1->n_index && s2->n_index; attempt++) {
         RC(dalloc(ctx, &seeds, cap));
+        RC(dalloc(ctx, &cand, ccap));
         CU(cudaMemsetAsync(ctr, 0, 16 * sizeof(int64_t), ctx->stream));
         stage_tic(ctx, 1);
-        LAUNCH(ctx, k_seed_join, grid_for(s1->n_index, 256), 256, 0, s1->index, s1->n_index, s2->index,
-               s2->dir, P, seeds, cap, ctr);
+        LAUNCH(ctx, k_seed_probe, grid_for(s1->n_index, 256), 256, 0, s1->index, s1->n_index, s2->index,
+               s2->dir, cand, ccap, ctr);
+        LAUNCH(ctx, k_seed_verify, RCQ_SMS * 16, 256, 0, cand, ccap, P, seeds, cap, ctr);
         stage_toc(ctx, 1);
         RC(read_counters(ctx, 2));
         stage_collect(ctx);
         n_seeds = ctx->h_pin[0];
         st.n_candidates = ctx->h_pin[1];
-        if (n_seeds <= cap) break;
+        dfree(ctx, cand); cand = nullptr;
+        if (n_seeds <= cap && st.n_candidates <= ccap) break;
         dfree(ctx, seeds); seeds = nullptr;
-        cap = n_seeds;
+        cap = std::max(cap, n_seeds);
+        ccap = std::max(ccap, st.n_candidates);
+        n_seeds = 0;
     }
     st.n_seeds = n_seeds;
     if (n_seeds >= (1ll << 31)) return rcq_fail(RCQ_ERR_CAPACITY, "rcq_search_pair: too many seeds");

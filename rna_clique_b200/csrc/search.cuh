@@ -12,6 +12,8 @@ struct PairView {
     const int32_t *offA, *lenA, *offB, *lenB;
     int32_t nA, nB;
     const uint32_t *selA, *selB;
+    const int32_t *blkA, *blkB;   // 32-base block -> transcript
+    const int2 *olA, *olB;        // {off, len} per transcript
 };
 
 struct rcq_table {

@@ -5,7 +5,7 @@
 // transcript of B (the megablast seed condition, blastn word_size 28) and extend each run without
 // gaps under an X-drop of 10 (20 bits).  Any 28-mer window contains the window minimum of its 13
 // canonical 16-mers, and both samples index every position that is a window minimum, so joining
-// the two sorted minimizer lists on the hash finds at least one anchor inside every such run.
+// the two sorted minimizer lists on the key finds at least one anchor inside every such run.
 // Exactly one anchor per run survives (the leftmost position indexed on both sides).
 //
 // Roofline: HBM/L2-bound.  Algorithmic bytes per pair: 8 B per index entry of A streamed +
@@ -52,91 +52,122 @@ __device__ __forceinline__ int32_t run_back(const SeqArena& A, int64_t pa, const
     return n;
 }
 
-// Try one (A position, B position, strand) anchor; on success append a seed record.
-__device__ __forceinline__ bool try_anchor(const PairView& P, int32_t pA, int32_t pB, int minus,
-                                           Seed* out) {
-    int32_t ta = find_tx(P.offA, P.nA, pA), tb = find_tx(P.offB, P.nB, pB);
-    int32_t oa = __ldg(P.offA + ta), ob = __ldg(P.offB + tb);
-    int32_t la = __ldg(P.lenA + ta), lb = __ldg(P.lenB + tb);
-    int32_t ia = pA - oa, jf = pB - ob;
-    int32_t j = minus ? lb - jf - RCQ_KMER : jf;
+// ---- phase 1: probe.  Thread per index entry of A; both indexes are sorted by the same key, so
+// neighbouring threads read neighbouring directory buckets and entries of B (coalesced, L2
+// friendly).  Every key match becomes a candidate (entry of A, entry of B), written with one
+// atomic per warp.  counters[1] = #candidates (may exceed cap: the host re-runs with a larger list).
+__global__ void __launch_bounds__(256) k_seed_probe(
+    const uint64_t* __restrict__ idxA, int64_t nIdxA, const uint64_t* __restrict__ idxB,
+    const uint32_t* __restrict__ dirB, uint2* __restrict__ cand, int64_t cap,
+    unsigned long long* __restrict__ counters) {
+    const int lane = threadIdx.x & 31;
+    int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t first = 0, cnt = 0, lowA = 0;
+    if (e < nIdxA) {
+        uint64_t ka = __ldg(idxA + e);
+        uint32_t key = (uint32_t)(ka >> 32);
+        lowA = (uint32_t)ka;
+        uint32_t b = key >> (32 - RCQ_DIRBITS);
+        uint32_t lo = __ldg(dirB + b), hi = __ldg(dirB + b + 1);
+        for (uint32_t k = lo; k < hi; k++) {
+            uint32_t kb = (uint32_t)(__ldg(idxB + k) >> 32);
+            if (kb < key) continue;
+            if (kb > key) break;
+            if (!cnt) first = k;
+            cnt++;
+        }
+    }
+    // warp prefix sum of cnt
+    uint32_t incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+    if (!total) return;
+    unsigned long long base = 0;
+    if (lane == 31) base = atomicAdd(counters + 1, (unsigned long long)total);
+    base = __shfl_sync(0xffffffffu, base, 31) + (incl - cnt);
+    for (uint32_t c = 0; c < cnt; c++)
+        if ((int64_t)(base + c) < cap) cand[base + c] = make_uint2(lowA, (uint32_t)__ldg(idxB + first + c));
+}
+
+// ---- phase 2: verify.  Thread per candidate (grid-stride).  A candidate survives when the two
+// 16-mers are equal on the implied strand, the exact run through them is >= 28 long, and it is
+// the leftmost position of that run indexed in BOTH samples.  Every window of 13 consecutive
+// 16-mers lying inside a shared exact run has the same minimum in both samples, so a run that
+// reaches 13 or more bases to the left of the anchor always holds an earlier joint position: such
+// candidates are rejected after one 32-base compare, the others check the two index bitmaps over
+// the (< 13) bases to the left.
+__device__ __forceinline__ bool verify_anchor(const PairView& P, int32_t pA, int32_t pB, int minus, Seed* out) {
+    const int32_t ta = __ldg(P.blkA + (pA >> 5)), tb = __ldg(P.blkB + (pB >> 5));
+    const int2 a = __ldg(P.olA + ta), b = __ldg(P.olB + tb);
+    const int32_t oa = a.x, la = a.y, ob = b.x, lb = b.y;
+    const int32_t ia = pA - oa, jf = pB - ob;
+    const int32_t j = minus ? lb - jf - RCQ_KMER : jf;
     const SeqArena& B = minus ? P.Br : P.Bf;
-    int64_t ba = oa, bb = ob;
+    const int64_t ba = oa, bb = ob;
     if ((match32(P.Af, ba + ia, B, bb + j) & 0xFFFFu) != 0xFFFFu) return false;
-    int32_t right = run_fwd(P.Af, ba + ia + RCQ_KMER, B, bb + j + RCQ_KMER,
-                            min(la - ia - RCQ_KMER, lb - j - RCQ_KMER));
-    int32_t left = (ia > 0 && j > 0) ? run_back(P.Af, ba + ia - 1, B, bb + j - 1, min(ia, j)) : 0;
-    int32_t rs = ia - left, re = ia + RCQ_KMER + right, d = j - ia;
-    if (re - rs < RCQ_WORD) return false;
-    // leftmost jointly indexed position of the run wins
-    for (int32_t p0 = rs; p0 < ia; p0 += 32) {
+    // left: at most 13 bases matter
+    int32_t left = 0;
+    const int32_t llim = min(ia, j);
+    if (llim > 0) {
+        uint32_t m = match32_back(P.Af, ba + ia - 1, B, bb + j - 1);
+        left = (m == 0xFFFFFFFFu) ? 32 : (__ffs(~m) - 1);
+        if (left > llim) left = llim;
+        if (left >= RCQ_WIN) return false;
+    }
+    const int32_t d = j - ia;
+    if (left > 0) {
+        const int32_t p0 = ia - left;      // bits for positions [p0, ia)
         uint32_t wa = fetchmask32(P.selA, ba + p0), wb;
         if (!minus) wb = fetchmask32(P.selB, bb + p0 + d);
         else wb = __brev(fetchmask32(P.selB, bb + lb - d - RCQ_KMER - p0 - 31));
-        uint32_t both = wa & wb;
-        int32_t v = ia - p0;
-        if (v < 32) both &= (1u << v) - 1u;
-        if (both) return false;
+        if (wa & wb & ((1u << left) - 1u)) return false;
     }
+    const int32_t right = run_fwd(P.Af, ba + ia + RCQ_KMER, B, bb + j + RCQ_KMER,
+                                  min(la - ia - RCQ_KMER, lb - j - RCQ_KMER));
+    const int32_t rs = ia - left, re = ia + RCQ_KMER + right;
+    if (re - rs < RCQ_WORD) return false;
     out->ta = ta; out->tb = tb; out->minus = minus; out->rs = rs; out->re = re; out->diag = d;
     return true;
 }
 
-// Thread per index entry of A.  Seeds are staged in shared memory and flushed with one global
-// atomic per block.
-__global__ void __launch_bounds__(256) k_seed_join(
-    const uint64_t* __restrict__ idxA, int64_t nIdxA, const uint64_t* __restrict__ idxB,
-    const uint32_t* __restrict__ dirB, PairView P, Seed* __restrict__ seeds, int64_t cap,
-    unsigned long long* __restrict__ counters /* [0]=seeds [1]=candidates */) {
-    __shared__ Seed stage[512];
-    __shared__ int n_stage;
-    __shared__ unsigned long long base;
-    if (threadIdx.x == 0) n_stage = 0;
-    __syncthreads();
-    int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    unsigned cand = 0;
-    if (e < nIdxA) {
-        uint64_t ka = idxA[e];
-        uint32_t h = (uint32_t)(ka >> 32);
-        int32_t pA = (int32_t)((ka & 0xFFFFFFFFu) >> 1);
-        int oA = (int)(ka & 1);
-        uint32_t b = h >> (32 - RCQ_DIRBITS);
-        uint32_t lo = __ldg(dirB + b), hi = __ldg(dirB + b + 1);
-        // palindromic 16-mers match on both strands
-        uint32_t f = (uint32_t)fetch32(P.Af.bits, pA);
-        uint32_t x = ~f;
-        x = __brev(x);
-        x = ((x >> 1) & 0x55555555u) | ((x & 0x55555555u) << 1);
-        bool pal = (x == f);
-        for (uint32_t k = lo; k < hi; k++) {
-            uint64_t kb = __ldg(idxB + k);
-            uint32_t hb = (uint32_t)(kb >> 32);
-            if (hb < h) continue;
-            if (hb > h) break;
-            int32_t pB = (int32_t)((kb & 0xFFFFFFFFu) >> 1);
-            int minus = oA ^ (int)(kb & 1);
-            for (int rep = 0; rep < (pal ? 2 : 1); rep++) {
-                cand++;
-                Seed s;
-                if (try_anchor(P, pA, pB, minus ^ rep, &s)) {
-                    int slot = atomicAdd(&n_stage, 1);
-                    if (slot < 512) stage[slot] = s;
-                    else {  // rare: staging full, go straight to global
-                        unsigned long long g = atomicAdd(counters, 1ull);
-                        if ((int64_t)g < cap) seeds[g] = s;
-                    }
-                }
-            }
+__global__ void __launch_bounds__(256) k_seed_verify(const uint2* __restrict__ cand, int64_t cand_cap, PairView P,
+                                                     Seed* __restrict__ seeds, int64_t cap,
+                                                     unsigned long long* __restrict__ counters /* [0]=seeds */) {
+    const int lane = threadIdx.x & 31;
+    // the candidate count is read from device memory: no host round trip between probe and verify
+    const int64_t n_cand = min((int64_t)counters[1], cand_cap);
+    for (int64_t base = (int64_t)blockIdx.x * blockDim.x; base < n_cand; base += (int64_t)gridDim.x * blockDim.x) {
+        int64_t x = base + threadIdx.x;
+        Seed s[2];
+        int ns = 0;
+        if (x < n_cand) {
+            const uint2 c = __ldg(cand + x);
+            const int32_t pA = (int32_t)(c.x >> 1), pB = (int32_t)(c.y >> 1);
+            const int minus = (int)((c.x ^ c.y) & 1u);
+            // palindromic 16-mers match on both strands
+            uint32_t f = (uint32_t)fetch32(P.Af.bits, pA);
+            uint32_t r = __brev(~f);
+            r = ((r >> 1) & 0x55555555u) | ((r & 0x55555555u) << 1);
+            const int reps = (r == f) ? 2 : 1;
+            for (int rep = 0; rep < reps; rep++)
+                if (verify_anchor(P, pA, pB, minus ^ rep, &s[ns])) ns++;
+        }
+        // warp-aggregated append
+        unsigned m1 = __ballot_sync(0xffffffffu, ns >= 1), m2 = __ballot_sync(0xffffffffu, ns >= 2);
+        int tot = __popc(m1) + __popc(m2);
+        if (tot) {
+            unsigned long long g = 0;
+            if (lane == 0) g = atomicAdd(counters, (unsigned long long)tot);
+            g = __shfl_sync(0xffffffffu, g, 0);
+            unsigned below = (1u << lane) - 1u;
+            if (ns >= 1) { int64_t slot = (int64_t)g + __popc(m1 & below); if (slot < cap) seeds[slot] = s[0]; }
+            if (ns >= 2) { int64_t slot = (int64_t)g + __popc(m1) + __popc(m2 & below); if (slot < cap) seeds[slot] = s[1]; }
         }
     }
-    for (int o = 16; o; o >>= 1) cand += __shfl_down_sync(0xffffffffu, cand, o);
-    if ((threadIdx.x & 31) == 0 && cand) atomicAdd(counters + 1, (unsigned long long)cand);
-    __syncthreads();
-    int ns = min(n_stage, 512);
-    if (threadIdx.x == 0 && ns) base = atomicAdd(counters, (unsigned long long)ns);
-    __syncthreads();
-    for (int i = threadIdx.x; i < ns; i += blockDim.x)
-        if ((int64_t)(base + i) < cap) seeds[base + i] = stage[i];
 }
 
 // X-drop ungapped extension (thread per seed) + start point of the gapped extension.
