@@ -203,6 +203,8 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    step_walls = []
+
     def timed(fn, steps, warmup):
         out = None
         for _ in range(warmup):
@@ -212,9 +214,13 @@ def main():
         l0 = eng.ctx.launches
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
+        walls = []
         for _ in range(steps):
+            t0 = time.perf_counter()
             out = fn()
+            walls.append((time.perf_counter() - t0) * 1e3)
         e1.record(stream)
+        step_walls.append(walls)
         barrier()
         ms = e0.elapsed_time(e1)
         if dist is not None:
@@ -283,7 +289,7 @@ def main():
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s"},
             "stages_ms_per_step": {k: v["ms"] / a.steps for k, v in stages.items()},
             "search_stats_per_step": agg,
-            "phase2_counts": res["counts"],
+            "phase2_counts": res["counts"], "host_wall_ms_per_step": step_walls,
         }
     if dist is not None:
         dist.barrier()

@@ -110,17 +110,21 @@ double rcq_bitscore(int32_t score);
  * Replaces build_graph.py:40-68, filtered_distance.py:25-39,171-210,234-247 and
  * similarity_computer.py:21-42.  Node id = sample_index*stride + gene.
  * Rows of all tables are concatenated; table k owns rows [row_off[k], row_off[k+1]) and
- * joins samples t_s[k] (ssample) and t_q[k] (qsample).  sample_count<=0 => count the samples
- * present in the graph (filtered_distance.py:171-182).
+ * joins samples t_s[k] (ssample) and t_q[k] (qsample).  t_flags (may be NULL = 3 for every table):
+ * bit0 = the table's rows are edges of the graph, bit1 = its rows are summed — SampleSimilarity
+ * takes the graph and the tables as separate arguments (filtered_distance.py:162-169), so a graph
+ * that is not the union of the tables is passed as edge-only pseudo-tables.  sample_count<=0 =>
+ * count the samples present in the graph (filtered_distance.py:171-182).
  * Outputs: nident_sum/denom_sum int64[n_tables] (denom = sum(length) - sum(gaps) over
  * restricted rows); valid uint8[n_samples*stride] (may be NULL); counts[0]=#components,
  * [1]=#ideal components, [2]=sample_count used, [3]=#nodes, [4]=#unique edges.
- * Returns RCQ_ERR_NO_IDEAL when some denom_sum is 0 (sums are still filled in). */
+ * Returns RCQ_ERR_NO_IDEAL when some summed table's denom_sum is 0 (sums are still filled in). */
 int rcq_phase2_host(rcq_ctx* ctx, int32_t n_samples, int64_t stride, int32_t n_tables,
                     const int64_t* row_off, const int32_t* t_s, const int32_t* t_q,
                     const int32_t* sgene, const int32_t* qgene, const int32_t* nident,
-                    const int32_t* length, const int32_t* gaps, int32_t sample_count,
-                    int64_t* nident_sum, int64_t* denom_sum, uint8_t* valid, int64_t counts[5]);
+                    const int32_t* length, const int32_t* gaps, const uint8_t* t_flags,
+                    int32_t sample_count, int64_t* nident_sum, int64_t* denom_sum, uint8_t* valid,
+                    int64_t counts[5]);
 /* Same, fed from device-resident tables produced by rcq_search_pair (no host round trip). */
 int rcq_phase2_tables(rcq_ctx* ctx, int32_t n_samples, int64_t stride, int32_t n_tables,
                       const rcq_table* const* tables, const int32_t* t_s, const int32_t* t_q,

@@ -88,7 +88,7 @@ def lib():
         L.rcq_evalue.restype = dbl
         L.rcq_bitscore.argtypes = [i32]
         L.rcq_bitscore.restype = dbl
-        L.rcq_phase2_host.argtypes = [vp, i32, i64, i32, vp, vp, vp, vp, vp, vp, vp, vp, i32, vp, vp, vp, vp]
+        L.rcq_phase2_host.argtypes = [vp, i32, i64, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, vp, vp, vp, vp]
         L.rcq_phase2_tables.argtypes = [vp, i32, i64, i32, vp, vp, vp, i32, vp, vp, vp, vp]
         L.rcq_table_flat_words.argtypes = [vp]
         L.rcq_table_flat_words.restype = i64
@@ -262,7 +262,7 @@ def debug_last_hsps(ctx: Context) -> np.ndarray:
 
 
 def phase2_host(ctx: Context, n_samples: int, stride: int, row_off, t_s, t_q, sgene, qgene, nident, length,
-                gaps, sample_count=None, want_valid: bool = True):
+                gaps, sample_count=None, want_valid: bool = True, t_flags=None):
     """rcq_phase2_host: concatenated host tables -> (nident_sum, denom_sum, valid, counts).
     Raises NoIdealComponents (after filling the sums) like the reference's NoIdealComponentsError."""
     row_off = np.ascontiguousarray(row_off, dtype=np.int64)
@@ -272,8 +272,11 @@ def phase2_host(ctx: Context, n_samples: int, stride: int, row_off, t_s, t_q, sg
     de = np.zeros(max(n_tables, 1), dtype=np.int64)
     valid = np.zeros(n_samples * stride, dtype=np.uint8) if want_valid else None
     counts = np.zeros(5, dtype=np.int64)
+    if t_flags is not None:
+        t_flags = np.ascontiguousarray(t_flags, dtype=np.uint8)
+        assert len(t_flags) == n_tables
     code = lib().rcq_phase2_host(ctx.h, n_samples, stride, n_tables, row_off.ctypes.data, *[a.ctypes.data for a in arrs],
-                                 int(sample_count or 0), ni.ctypes.data, de.ctypes.data, _ptr(valid), counts.ctypes.data)
+                                 _ptr(t_flags), int(sample_count or 0), ni.ctypes.data, de.ctypes.data, _ptr(valid), counts.ctypes.data)
     res = dict(nident_sum=ni[:n_tables], denom_sum=de[:n_tables], valid=valid,
                counts=dict(zip(["components", "ideal", "sample_count", "nodes", "edges"], counts.tolist())))
     if code == -4:

@@ -1,0 +1,91 @@
+"""Gene-matches graph.  Mirrors the reference's build_graph.py:40-68: nodes are (sample path string,
+gene id) tuples, one undirected edge per table row (repeated rows collapse).
+
+The hot path never needs the networkx object — connected components and the ideal-component test
+run on the device from flat (sample index, gene) arrays — so `EdgeArrays` keeps the flat form and
+materialises / pickles as the reference's nx.Graph only on demand."""
+from __future__ import annotations
+
+from typing import Iterable
+
+import networkx as nx
+import numpy as np
+import pandas as pd
+
+
+class EdgeArrays:
+    """Edges grouped per (ssample, qsample): lists of (ssample str, qsample str, sgene int32[], qgene int32[])."""
+
+    def __init__(self):
+        self.groups = []
+
+    def add(self, ssample: str, qsample: str, sgene, qgene):
+        self.groups.append((str(ssample), str(qsample), np.asarray(sgene, dtype=np.int32), np.asarray(qgene, dtype=np.int32)))
+
+    def add_frame(self, df: pd.DataFrame):
+        if len(df) == 0:
+            return
+        ss, qs = df["ssample"].astype(str).to_numpy(), df["qsample"].astype(str).to_numpy()
+        if (ss == ss[0]).all() and (qs == qs[0]).all():
+            self.add(ss[0], qs[0], df["sgene"].to_numpy(), df["qgene"].to_numpy())
+        else:  # a frame mixing sample pairs: split
+            for (s, q), part in df.groupby([ss, qs], sort=False):
+                self.add(s, q, part["sgene"].to_numpy(), part["qgene"].to_numpy())
+
+    def to_networkx(self) -> nx.Graph:
+        g = nx.Graph()
+        for s, q, sg, qg in self.groups:
+            g.add_edges_from(zip(zip([s] * len(sg), sg.tolist()), zip([q] * len(qg), qg.tolist())))
+        return g
+
+    @classmethod
+    def from_networkx(cls, g: nx.Graph) -> "EdgeArrays":
+        buckets = {}
+        for (s1, g1), (s2, g2) in g.edges():
+            b = buckets.setdefault((s1, s2), ([], []))
+            b[0].append(g1)
+            b[1].append(g2)
+        out = cls()
+        for (s1, s2), (a, b) in buckets.items():
+            out.add(s1, s2, a, b)
+        out.isolated = [n for n in g.nodes if g.degree(n) == 0]
+        return out
+
+
+class GeneMatchGraph(nx.Graph):
+    """nx.Graph that is filled lazily from EdgeArrays the first time networkx looks at it; it
+    pickles as a plain networkx Graph (filtering_step.py:158-159 writes graph.pkl)."""
+
+    def __init__(self, edges: EdgeArrays = None):
+        super().__init__()
+        self._rcq_edges = edges
+        self._rcq_built = edges is None
+
+    def _materialise(self):
+        if not self._rcq_built:
+            self._rcq_built = True
+            for s, q, sg, qg in self._rcq_edges.groups:
+                super().add_edges_from(zip(zip([s] * len(sg), sg.tolist()), zip([q] * len(qg), qg.tolist())))
+        return self
+
+    @property
+    def rcq_edges(self):
+        return self._rcq_edges
+
+    def __reduce__(self):
+        self._materialise()
+        return (nx.Graph, (), {"graph": self.graph, "_node": self._node, "_adj": self._adj, "__networkx_cache__": {}})
+
+    def __getattribute__(self, name):
+        if name in ("_node", "_adj", "nodes", "edges", "adj", "degree") and not object.__getattribute__(self, "__dict__").get("_rcq_built", True):
+            object.__getattribute__(self, "_materialise")()
+        return object.__getattribute__(self, name)
+
+
+def build_graph(dfs: Iterable[pd.DataFrame]) -> nx.Graph:
+    """build_graph(dfs) -> nx.Graph (build_graph.py:40-68).  Consumes the iterable (it is the
+    unordered generator of find_all_pairs in the pipeline, filtering_step.py:157)."""
+    e = EdgeArrays()
+    for df in dfs:
+        e.add_frame(df)
+    return GeneMatchGraph(e)

@@ -16,6 +16,7 @@ struct P2View {
     int64_t stride, n_rows;
     const int64_t* row_off;           // [n_tables+1]
     const int32_t *t_s, *t_q;         // [n_tables]
+    const uint8_t* t_flags;           // [n_tables] or NULL: bit0 rows are graph edges, bit1 rows are summed
     const int32_t *sgene, *qgene, *nident, *length, *gaps;  // [n_rows]
     int32_t* parent;                  // [n_samples*stride]
     uint8_t* present;                 // [n_samples*stride]
@@ -60,6 +61,7 @@ __global__ void k_p2_union(P2View V) {
     int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= V.n_rows) return;
     int32_t t = table_of(V.row_off, V.n_tables, r);
+    if (V.t_flags && !(V.t_flags[t] & 1)) return;
     int32_t u = (int32_t)(V.t_s[t] * V.stride + V.sgene[r]);
     int32_t v = (int32_t)(V.t_q[t] * V.stride + V.qgene[r]);
     V.present[u] = 1; V.present[v] = 1;
@@ -121,7 +123,7 @@ __global__ void k_p2_reduce(P2View V, const uint8_t* __restrict__ valid, unsigne
     if (r < V.n_rows) {
         t = table_of(V.row_off, V.n_tables, r);
         int64_t u = V.t_s[t] * V.stride + V.sgene[r], v = V.t_q[t] * V.stride + V.qgene[r];
-        if (valid[u] && valid[v]) { a = (unsigned long long)V.nident[r]; b = (unsigned long long)(V.length[r] - V.gaps[r]); }
+        if ((!V.t_flags || (V.t_flags[t] & 2)) && valid[u] && valid[v]) { a = (unsigned long long)V.nident[r]; b = (unsigned long long)(V.length[r] - V.gaps[r]); }
     }
     // warp-level segmented add: rows of a table are contiguous, so the lanes of one table form a
     // contiguous run and a shuffle-down tree restricted to equal table ids is exact
@@ -138,7 +140,7 @@ __global__ void k_p2_reduce(P2View V, const uint8_t* __restrict__ valid, unsigne
 
 // ---------------------------------------------------------------------------------------------
 static int phase2_run(rcq_ctx* ctx, P2View V, int32_t sample_count, int64_t* nident_sum, int64_t* denom_sum,
-                      uint8_t* valid_out, int64_t counts[5]) {
+                      uint8_t* valid_out, int64_t counts[5], const uint8_t* h_flags = nullptr) {
     const int64_t n_nodes = (int64_t)V.n_samples * V.stride;
     if (n_nodes >= (1ll << 31)) return rcq_fail(RCQ_ERR_CAPACITY, "rcq_phase2: n_samples*stride exceeds 2^31 nodes");
     unsigned long long* ctr = (unsigned long long*)ctx->d_ctr;
@@ -194,15 +196,16 @@ static int phase2_run(rcq_ctx* ctx, P2View V, int32_t sample_count, int64_t* nid
     dfree(ctx, V.parent); dfree(ctx, V.present); dfree(ctx, V.vcount); dfree(ctx, V.ecount);
     dfree(ctx, V.ekeys); dfree(ctx, valid); dfree(ctx, spresent); dfree(ctx, d_ni); dfree(ctx, d_de);
     for (int32_t t = 0; t < V.n_tables; t++)
-        if (denom_sum[t] == 0) return rcq_fail(RCQ_ERR_NO_IDEAL, "rcq_phase2: a table has no row inside ideal components");
+        if (denom_sum[t] == 0 && (!h_flags || (h_flags[t] & 2))) return rcq_fail(RCQ_ERR_NO_IDEAL, "rcq_phase2: a table has no row inside ideal components");
     return 0;
 }
 
 extern "C" int rcq_phase2_host(rcq_ctx* ctx, int32_t n_samples, int64_t stride, int32_t n_tables,
                                const int64_t* row_off, const int32_t* t_s, const int32_t* t_q,
                                const int32_t* sgene, const int32_t* qgene, const int32_t* nident,
-                               const int32_t* length, const int32_t* gaps, int32_t sample_count,
-                               int64_t* nident_sum, int64_t* denom_sum, uint8_t* valid, int64_t counts[5]) {
+                               const int32_t* length, const int32_t* gaps, const uint8_t* t_flags,
+                               int32_t sample_count, int64_t* nident_sum, int64_t* denom_sum, uint8_t* valid,
+                               int64_t counts[5]) {
     if (!ctx || n_samples < 0 || stride < 1 || n_tables < 0 || (n_tables && (!row_off || !t_s || !t_q || !nident_sum || !denom_sum)))
         return rcq_fail(RCQ_ERR_ARG, "rcq_phase2_host: bad argument");
     CU(cudaSetDevice(ctx->device));
@@ -216,6 +219,12 @@ extern "C" int rcq_phase2_host(rcq_ctx* ctx, int32_t n_samples, int64_t stride, 
     RC(dalloc(ctx, &d_ts, n_tables));
     RC(dalloc(ctx, &d_tq, n_tables));
     RC(dalloc(ctx, &d_cols, 5 * n));
+    uint8_t* d_flags = nullptr;
+    if (t_flags && n_tables) {
+        RC(dalloc(ctx, &d_flags, n_tables));
+        CU(cudaMemcpyAsync(d_flags, t_flags, (size_t)n_tables, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    V.t_flags = d_flags;
     if (n_tables) {
         CU(cudaMemcpyAsync(d_off, row_off, (size_t)(n_tables + 1) * 8, cudaMemcpyHostToDevice, ctx->stream));
         CU(cudaMemcpyAsync(d_ts, t_s, (size_t)n_tables * 4, cudaMemcpyHostToDevice, ctx->stream));
@@ -226,8 +235,8 @@ extern "C" int rcq_phase2_host(rcq_ctx* ctx, int32_t n_samples, int64_t stride, 
         CU(cudaMemcpyAsync(d_cols + c * n, src[c], (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
     V.row_off = d_off; V.t_s = d_ts; V.t_q = d_tq;
     V.sgene = d_cols; V.qgene = d_cols + n; V.nident = d_cols + 2 * n; V.length = d_cols + 3 * n; V.gaps = d_cols + 4 * n;
-    int rc = phase2_run(ctx, V, sample_count, nident_sum, denom_sum, valid, counts);
-    dfree(ctx, d_off); dfree(ctx, d_ts); dfree(ctx, d_tq); dfree(ctx, d_cols);
+    int rc = phase2_run(ctx, V, sample_count, nident_sum, denom_sum, valid, counts, d_flags ? t_flags : nullptr);
+    dfree(ctx, d_off); dfree(ctx, d_ts); dfree(ctx, d_tq); dfree(ctx, d_cols); dfree(ctx, d_flags);
     return rc;
 }
 

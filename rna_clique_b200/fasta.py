@@ -1,0 +1,64 @@
+"""FASTA ingest for the hot path: one pass over the file bytes with numpy, no per-record Python
+objects for the sequence data.  Replaces the Bio.SeqIO.parse passes of select_top_genes.py:110-127
+on the host side; the letters go to the device as one flat uint8 buffer + (start, length)."""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from pathlib import Path
+
+import numpy as np
+
+
+@dataclass
+class Fasta:
+    headers: list          # header lines without '>' (id = first whitespace-separated token)
+    ascii: np.ndarray      # uint8, all sequence letters concatenated, newlines removed
+    offsets: np.ndarray    # int64 [n+1]
+
+    @property
+    def ids(self):
+        return [h.split(None, 1)[0] if h else "" for h in self.headers]
+
+    def __len__(self):
+        return len(self.headers)
+
+
+def read_fasta(path: Path) -> Fasta:
+    raw = np.fromfile(str(path), dtype=np.uint8)
+    if raw.size == 0:
+        return Fasta([], np.zeros(0, np.uint8), np.zeros(1, np.int64))
+    nl = np.flatnonzero(raw == 10)
+    line_start = np.concatenate([[0], nl + 1])
+    line_start = line_start[line_start < raw.size]
+    is_hdr = raw[line_start] == ord(">")
+    hdr_start = line_start[is_hdr]
+    # end of each header line
+    ends = np.append(nl, raw.size)
+    hdr_end = ends[np.searchsorted(ends, hdr_start)]
+    headers = [raw[a + 1:b].tobytes().decode().rstrip("\r") for a, b in zip(hdr_start, hdr_end)]
+    # keep = sequence letters: not newline / CR / space, and not inside a header line
+    keep = (raw != 10) & (raw != 13) & (raw != 32)
+    delta = np.zeros(raw.size + 1, dtype=np.int32)
+    np.add.at(delta, hdr_start, 1)
+    np.add.at(delta, np.minimum(hdr_end, raw.size), -1)
+    keep &= np.cumsum(delta[:-1]) == 0
+    csum = np.concatenate([[0], np.cumsum(keep, dtype=np.int64)])
+    offsets = np.append(csum[hdr_start], csum[-1]).astype(np.int64)
+    return Fasta(headers, np.ascontiguousarray(raw[keep]), offsets)
+
+
+def write_fasta(path: Path, headers, ascii_: np.ndarray, starts, lengths, width: int = 60) -> None:
+    """Biopython-style output (SeqIO.write(..., "fasta"): '>' + header, 60 letters per line), as
+    select_top_genes_all.py:37-45 writes od1/<sample>_top.fasta."""
+    with open(path, "wb") as f:
+        for h, s, n in zip(headers, starts, lengths):
+            seq = ascii_[int(s):int(s) + int(n)]
+            f.write(b">" + h.encode() + b"\n")
+            full = (len(seq) // width) * width
+            if full:
+                body = np.empty((full // width, width + 1), dtype=np.uint8)
+                body[:, :width] = seq[:full].reshape(-1, width)
+                body[:, width] = 10
+                f.write(body.tobytes())
+            if len(seq) > full:
+                f.write(seq[full:].tobytes() + b"\n")

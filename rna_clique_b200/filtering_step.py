@@ -1,0 +1,30 @@
+"""Phase 1 driver.  Mirrors the reference's filtering_step.py:61-164: top genes per sample ->
+all-pairs tables -> gene-matches graph -> graph pickle; returns lazy table readers."""
+from __future__ import annotations
+
+import itertools
+import os
+import pickle
+from pathlib import Path
+from typing import Callable, Iterable
+
+from .build_graph import build_graph
+from .filtered_distance import SampleSimilarity
+from .find_all_pairs import find_all_pairs
+from .select_top_genes import select_top_and_save
+from .transcripts import default_parser
+
+
+def filtering_step(dirs: Iterable[Path], out_dir_1: Path, out_dir_2: Path, cache_dir: Path, output_graph: Path,
+                   top_genes: int, transcripts: str = "transcripts.fasta", top_matches: int = 1,
+                   id_parser: Callable = default_parser, evalue: float = 1e-99, keep_all: bool = True,
+                   jobs: int = max((os.cpu_count() or 2) - 1, 1)):
+    path_to_sample = dict(select_top_and_save(Path(out_dir_1), transcripts, Path(x), top_genes, id_parser) for x in dirs)
+    tables, table_paths, num_tables = find_all_pairs(path_to_sample, out_dir_2, cache_dir, path_to_sample.__getitem__,
+                                                     hf_args=[id_parser, top_matches, evalue, keep_all], jobs=jobs)
+    graph = build_graph(tables)
+    if output_graph is not None:
+        with open(output_graph, "wb") as f:
+            pickle.dump(graph, f, pickle.HIGHEST_PROTOCOL)
+    p1, p2 = itertools.tee(table_paths)
+    return map(SampleSimilarity._read_table, p1), p2, graph, num_tables, path_to_sample

@@ -1,0 +1,127 @@
+"""One sample pair -> gene-matches table.  Mirrors the reference's find_homologs.py:176-302
+(HomologFinder) with the two `blastn` subprocesses (find_homologs.py:124) and the pandas
+reductions (:130, :215-302) replaced by ONE call into the CUDA library: rcq_search_pair.
+
+Table contract (docs/formats.md:231-252): transcripts1 is the `ssample` side, so
+`sgene/siso` name a transcript of transcripts1 and `qgene/qiso` one of transcripts2 in every row;
+`reverse` marks rows that came from the search transcripts1 -> transcripts2, whose
+qstart/qend/sstart/send/sstrand keep that search's own query/subject orientation."""
+from __future__ import annotations
+
+from pathlib import Path
+from typing import Callable, Optional
+
+import numpy as np
+import pandas as pd
+
+from . import _native
+from .fasta import read_fasta
+from .transcripts import default_parser, parse_ids
+
+COLUMNS = ["pident", "length", "mismatch", "gapopen", "qstart", "qend", "sstart", "send", "evalue", "bitscore",
+           "gaps", "nident", "sstrand", "qgene", "qiso", "sgene", "siso", "reverse"]
+KA_LAMBDA, KA_K = 1.28, 0.46   # blastn 1/-2 with linear gaps (csrc/common.cuh)
+_INT_COLS = ["length", "mismatch", "gapopen", "qstart", "qend", "sstart", "send", "gaps", "nident",
+             "qgene", "qiso", "sgene", "siso"]
+
+
+def shrink_df(df: pd.DataFrame) -> pd.DataFrame:
+    """Down-cast integer columns to the smallest width holding their values
+    (reference shrink_df, find_homologs.py:58-80)."""
+    for c in _INT_COLS:
+        if c in df and len(df):
+            df[c] = pd.to_numeric(df[c], downcast="unsigned" if df[c].min() >= 0 else "signed")
+    return df
+
+
+class SampleCache:
+    """Device-resident samples keyed by FASTA path (the role of BlastDBCache, find_all_pairs.py:120-159)."""
+
+    def __init__(self, ctx: Optional[_native.Context] = None, device: int = 0):
+        self.ctx = ctx or _native.Context(device)
+        self._samples = {}
+
+    def get(self, path: Path, parser=default_parser) -> _native.Sample:
+        path = Path(path)
+        st = path.stat()
+        key = (str(path.resolve()), st.st_mtime_ns, st.st_size, id(parser))
+        s = self._samples.get(key)
+        if s is None:
+            fa = read_fasta(path)
+            _, gene, iso = parse_ids(fa.ids, parser)
+            s = _native.Sample(self.ctx, fa.ascii, fa.offsets, gene, iso, name=str(path))
+            self._samples[key] = s
+        return s
+
+    def close(self):
+        for s in self._samples.values():
+            s.close()
+        self._samples.clear()
+
+
+_default_cache: Optional[SampleCache] = None
+
+
+def default_cache() -> SampleCache:
+    global _default_cache
+    if _default_cache is None:
+        _default_cache = SampleCache()
+    return _default_cache
+
+
+def table_to_frame(cols: dict, n_db_bases_fwd: int, n_db_seqs_fwd: int, n_db_bases_bwd: int,
+                   n_db_seqs_bwd: int) -> pd.DataFrame:
+    """Device columns -> the reference's DataFrame.  pident / evalue / bitscore are derived here in
+    fp64 from the integer columns (blastn tabular semantics: pident = 100 nident / length;
+    bitscore printed as an integer above 99.9 bits)."""
+    n = len(cols["length"])
+    L = _native.lib()
+    rev = cols["reverse"].astype(bool)
+    score, qlen = cols["score"], cols["qlen"]
+    # Karlin-Altschul statistics; the length adjustment depends only on
+    # (query length, direction), so it is evaluated once per distinct value
+    key = qlen.astype(np.int64) * 2 + rev
+    uk, inv = np.unique(key, return_inverse=True)
+    la = np.array([L.rcq_length_adjustment(int(k >> 1), *((n_db_bases_bwd, n_db_seqs_bwd) if k & 1 else
+                                                         (n_db_bases_fwd, n_db_seqs_fwd))) for k in uk], dtype=np.float64)[inv] \
+        if n else np.zeros(0)
+    nb = np.where(rev, n_db_bases_bwd, n_db_bases_fwd).astype(np.float64)
+    ns = np.where(rev, n_db_seqs_bwd, n_db_seqs_fwd).astype(np.float64)
+    evalue = KA_K * np.maximum(qlen - la, 1.0) * np.maximum(nb - ns * la, 1.0) * np.exp(-KA_LAMBDA * score.astype(np.float64))
+    b = (KA_LAMBDA * score - np.log(KA_K)) / np.log(2.0)
+    bits = np.where(b > 99.9, np.round(b), np.round(b, 1))
+    df = pd.DataFrame({
+        "pident": np.round(100.0 * cols["nident"] / np.maximum(cols["length"], 1), 3),
+        "length": cols["length"], "mismatch": cols["mismatch"], "gapopen": cols["gapopen"],
+        "qstart": cols["qstart"], "qend": cols["qend"], "sstart": cols["sstart"], "send": cols["send"],
+        "evalue": evalue, "bitscore": bits, "gaps": cols["gaps"], "nident": cols["nident"],
+        "sstrand": np.where(cols["minus"].astype(bool), "minus", "plus"),
+        "qgene": cols["qgene"], "qiso": cols["qiso"], "sgene": cols["sgene"], "siso": cols["siso"],
+        "reverse": rev,
+    }, columns=COLUMNS)
+    return shrink_df(df)
+
+
+class HomologFinder:
+    """HomologFinder(parse_transcript_id, top_n, evalue, keep_all, debug=False, **blast_kwargs)
+    (find_homologs.py:176-213).  blast_kwargs are accepted for signature compatibility; `db_cache`
+    may carry a SampleCache (what find_all_pairs passes), everything else is ignored."""
+
+    def __init__(self, parse_transcript_id: Callable = default_parser, top_n: int = 1, evalue: float = 1e-99,
+                 keep_all: bool = True, debug: bool = False, **blast_kwargs):
+        self.parse, self.top_n, self.evalue, self.keep_all, self.debug = parse_transcript_id, top_n, evalue, keep_all, debug
+        cache = blast_kwargs.get("db_cache")
+        self.cache = cache if isinstance(cache, SampleCache) else default_cache()
+        self.last_table: Optional[_native.Table] = None
+
+    def get_device_table(self, transcripts1: Path, transcripts2: Path) -> _native.Table:
+        s1, s2 = self.cache.get(transcripts1, self.parse), self.cache.get(transcripts2, self.parse)
+        t = _native.search_pair(self.cache.ctx, s1, s2, self.evalue, self.top_n, self.keep_all)
+        t.db = (s1.total, s1.n_seq, s2.total, s2.n_seq)
+        return t
+
+    def get_match_table(self, transcripts1: Path, transcripts2: Path) -> pd.DataFrame:
+        t = self.get_device_table(transcripts1, transcripts2)
+        self.last_table = t
+        # forward search: query transcripts2 vs database transcripts1; backward: the other way round
+        return table_to_frame(t.download(), t.db[0], t.db[1], t.db[2], t.db[3])

@@ -1,0 +1,70 @@
+"""Top-n genes by k-mer coverage.  Mirrors the reference's select_top_genes.py:36-137 and
+select_top_genes_all.py:12-46: a gene's coverage is the maximum over its isoforms (starting from
+0.0), the top n genes are heapq.nlargest over (coverage, gene) — so equal coverage resolves to the
+LARGER gene id — and every isoform of a selected gene is emitted in input-file order."""
+from __future__ import annotations
+
+from pathlib import Path
+from typing import Callable, Iterator
+
+import numpy as np
+
+from .fasta import Fasta, read_fasta, write_fasta
+from .transcripts import default_parser, parse_ids
+
+
+def top_gene_mask(coverage: np.ndarray, gene: np.ndarray, top: int) -> np.ndarray:
+    """Indices (file order) of every transcript whose gene is among the `top` genes
+    (select_top_genes.py:108-127)."""
+    coverage = np.asarray(coverage, dtype=np.float64)
+    gene = np.asarray(gene)
+    ug, inv = np.unique(gene, return_inverse=True)
+    best = np.zeros(len(ug), dtype=np.float64)       # defaultdict(float): starts at 0.0
+    np.maximum.at(best, inv, coverage)
+    if top >= len(ug):
+        keep_gene = np.ones(len(ug), dtype=bool)
+    elif top <= 0:
+        keep_gene = np.zeros(len(ug), dtype=bool)
+    else:
+        order = np.lexsort((ug, best))               # ascending by coverage, then gene id
+        keep_gene = np.zeros(len(ug), dtype=bool)
+        keep_gene[order[len(ug) - top:]] = True
+    return np.flatnonzero(keep_gene[inv])
+
+
+class TopGeneSelector:
+    """seqs_fun() -> Fasta (or a path-bound reader); top = number of genes; parser = id parser."""
+
+    def __init__(self, seqs_fun: Callable[[], Fasta], top: int, parser=default_parser):
+        self.seqs_fun, self.top, self.parser = seqs_fun, top, parser
+        self._fa = None
+
+    def _load(self):
+        if self._fa is None:
+            self._fa = self.seqs_fun()
+            self._cov, self._gene, self._iso = parse_ids(self._fa.ids, self.parser)
+            self._keep = top_gene_mask(self._cov, self._gene, self.top)
+        return self._fa
+
+    def get_top_genes(self) -> Iterator[int]:
+        self._load()
+        return iter(sorted({int(g) for g in self._gene[self._keep]}))
+
+    def get_top_gene_seqs(self):
+        """(Fasta, kept transcript indices in file order, coverage, gene, isoform of the kept ones)."""
+        fa = self._load()
+        k = self._keep
+        return fa, k, self._cov[k], self._gene[k], self._iso[k]
+
+    @classmethod
+    def from_path(cls, path: Path, *args, **kwargs):
+        return cls(lambda: read_fasta(Path(path)), *args, **kwargs)
+
+
+def select_top_and_save(out_dir: Path, transcripts: str, x: Path, *args) -> tuple[Path, str]:
+    """Writes out_dir/<x.stem>_top.fasta and returns (path, x.stem) (select_top_genes_all.py:12-46)."""
+    x = Path(x)
+    out = Path(out_dir) / (x.stem + "_top.fasta")
+    fa, keep, _, _, _ = TopGeneSelector.from_path(x / transcripts, *args).get_top_gene_seqs()
+    write_fasta(out, [fa.headers[i] for i in keep], fa.ascii, fa.offsets[:-1][keep], np.diff(fa.offsets)[keep])
+    return out, x.stem

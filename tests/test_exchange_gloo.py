@@ -1,0 +1,51 @@
+"""CPU, world size 2 (gloo): the table exchange (exchange.allgather_flat) and the pair schedule —
+the host logic of the N > 1 path."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from rna_clique_b200.engine import schedule_pairs
+        from rna_clique_b200.exchange import allgather_flat
+        totals = [1000, 900, 800, 700, 50]
+        pairs, owner = schedule_pairs(len(totals), totals, world)
+        mine = [k for k in range(len(pairs)) if owner[k] == rank]
+        # item k: a ragged int32 "table" whose content encodes k (item 3 is empty)
+        make = lambda k: torch.arange(17 * ((k * 7) % 5 if k != 3 else 0), dtype=torch.int32) + 1000 * k
+        got = allgather_flat(dist, mine, [make(k) for k in mine], len(pairs), torch.device("cpu"))
+        ok = all(torch.equal(got[k], make(k)) for k in range(len(pairs)))
+        q.put((rank, ok, mine))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_allgather_flat_world2():
+    world, port = 2, _free_port()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert all(ok for _, ok, _ in res)
+    owned = sorted(k for _, _, mine in res for k in mine)
+    assert owned == list(range(10))           # every pair owned exactly once
+    assert all(len(mine) >= 3 for _, _, mine in res)
