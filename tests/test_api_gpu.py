@@ -1,0 +1,119 @@
+"""GPU: the reference-facing Python API (rna_clique(), SampleSimilarity, HomologFinder, find_all_pairs)
+end to end through the C ABI, against the oracle and the reference-generated fixtures."""
+import pickle
+
+import networkx as nx
+import numpy as np
+import pandas as pd
+import pytest
+
+from test_phase2_oracle import CASES, load_case
+
+pytestmark = pytest.mark.gpu
+
+
+def _frames(names, tables):
+    out = []
+    for t in tables:
+        df = pd.DataFrame({c: t[c] for c in ("sgene", "qgene", "nident", "length", "gaps")})
+        df["ssample"], df["qsample"] = names[t["s"]], names[t["q"]]
+        out.append(df)
+    return out
+
+
+@pytest.mark.parametrize("name", CASES)
+@pytest.mark.parametrize("graph_kind", ["lazy", "networkx"])
+def test_sample_similarity_against_reference_fixtures(ctx, name, graph_kind):
+    from rna_clique_b200.build_graph import build_graph
+    from rna_clique_b200.filtered_distance import NoIdealComponentsError, SampleSimilarity
+    rec, names, tables = load_case(name)
+    exp = rec["expect"]
+    dfs = _frames(names, tables)
+    graph = build_graph(dfs)
+    if graph_kind == "networkx":
+        graph = pickle.loads(pickle.dumps(graph))
+        assert type(graph) is nx.Graph
+    sim = SampleSimilarity(graph, SampleSimilarity.mapping_from_dfs(iter(dfs)), rec.get("sample_count"), ctx=ctx)
+    assert sim.sample_count == exp["sample_count"]
+    assert sorted([s, int(g)] for s, g in sim.valid.itertuples(index=False)) == exp["valid"]
+    if exp["error"]:
+        with pytest.raises(NoIdealComponentsError):
+            sim.get_dissimilarity_df()
+        return
+    df = sim.get_dissimilarity_df()
+    assert list(df.index) == exp["samples"] and list(df.columns) == exp["samples"]
+    assert np.array_equal(df.to_numpy(), np.asarray(exp["matrix"]))       # fp64, bit for bit
+    # restricted(): same rows the two validity probes keep
+    v = {(s, int(g)) for s, g in sim.valid.itertuples(index=False)}
+    for d in dfs[:3]:
+        keep = [(s, g) in v and (q, h) in v for s, g, q, h in zip(d["ssample"], d["sgene"], d["qsample"], d["qgene"])]
+        assert sim.restricted(d).equals(d[np.asarray(keep, dtype=bool)])
+
+
+def test_graph_that_is_not_the_union_of_the_tables(ctx):
+    """SampleSimilarity takes graph and tables separately (filtered_distance.py:162-169): the valid set
+    comes from the graph alone."""
+    from rna_clique_b200.filtered_distance import SampleSimilarity
+    mk = lambda s, q, sg, qg: pd.DataFrame(dict(ssample=s, qsample=q, sgene=sg, qgene=qg, nident=[90] * len(sg),
+                                                 length=[100] * len(sg), gaps=[0] * len(sg)))
+    dfs = [mk("a", "b", [1, 2], [1, 2]), mk("a", "c", [1, 2], [1, 2]), mk("b", "c", [1, 2], [1, 2])]
+    g = nx.Graph()
+    for d in dfs:
+        for s, q, sg, qg in zip(d["ssample"], d["qsample"], d["sgene"], d["qgene"]):
+            if sg == 1:                      # the graph only knows gene 1
+                g.add_edge((s, int(sg)), (q, int(qg)))
+    sim = SampleSimilarity(g, SampleSimilarity.mapping_from_dfs(iter(dfs)), ctx=ctx)
+    assert sorted(sim.valid.itertuples(index=False, name=None)) == [("a", 1), ("b", 1), ("c", 1)]
+    assert sim.get_dissimilarity_df().loc["a", "b"] == 0.1      # float(1 - Fraction(90, 100))
+
+
+def test_rna_clique_end_to_end(tmp_path):
+    from oracle import oracle as O
+    from oracle import phase2_ref
+    from rna_clique_b200.fasta import read_fasta
+    from rna_clique_b200.filtered_distance import SampleSimilarity
+    from rna_clique_b200.gene_matches_tables import default_extension, get_table_files, read_table
+    from rna_clique_b200.rna_clique import rna_clique
+    from rna_clique_b200.simulate import simulate, write_dataset
+    from rna_clique_b200.transcripts import parse_ids
+    _, ts = simulate(3, 150, seed=21, mutation_rate=0.03, indel_rate=0.002)
+    dirs = write_dataset(tmp_path / "in", ts)
+    od1, od2 = tmp_path / "od1", tmp_path / "od2"
+    od1.mkdir(); od2.mkdir()
+    sim, pts = rna_clique(dirs, od1, od2, tmp_path / "db", tmp_path / "graph.pkl", tmp_path / "matrix.pkl", 100)
+    assert sorted(pts.values()) == ["T0", "T1", "T2"] and all(p.exists() for p in pts)
+    ext = default_extension()
+    assert sorted(p.name for p in get_table_files(od2)) == [f"T0--T1.{ext}", f"T0--T2.{ext}", f"T1--T2.{ext}"]
+    mat = pd.read_pickle(tmp_path / "matrix.pkl")
+    labels = sorted(str(p) for p in pts)
+    assert list(mat.index) == labels and (np.diag(mat.to_numpy()) == 0).all()
+    # oracle: same top-gene files, oracle search, reference-pinned phase 2
+    osamples, paths = [], list(pts)
+    for p in paths:
+        fa = read_fasta(p)
+        assert len(fa) == 100
+        _, gene, iso = parse_ids(fa.ids)
+        osamples.append(O.Sample(fa.ascii, fa.offsets, gene, iso))
+    otables = []
+    for i in range(3):
+        for j in range(i + 1, 3):
+            want = O.search_pair(osamples[i], osamples[j]).rows(2)
+            got = read_table(od2 / f"T{i}--T{j}.{ext}")
+            assert got["ssample"][0] == str(paths[i]) and got["qsample"][0] == str(paths[j])
+            for col, k in (("length", 0), ("mismatch", 1), ("gapopen", 2), ("qstart", 3), ("qend", 4), ("sstart", 5),
+                           ("send", 6), ("gaps", 8), ("nident", 9), ("qgene", 10), ("qiso", 11), ("sgene", 12), ("siso", 13)):
+                assert np.array_equal(got[col].to_numpy().astype(np.int64), want[:, k]), col
+            assert np.array_equal(got["reverse"].to_numpy(), want[:, 16].astype(bool))
+            assert np.array_equal(got["sstrand"].to_numpy() == "minus", want[:, 15].astype(bool))
+            assert (got["evalue"] <= 1e-99).all() and (got["bitscore"] > 300).all()
+            otables.append(dict(s=i, q=j, sgene=want[:, 12], qgene=want[:, 10], nident=want[:, 9], length=want[:, 0], gaps=want[:, 8]))
+    exp = phase2_ref.phase2(3, otables)
+    _, m = phase2_ref.distance_matrix([str(p) for p in paths], otables, exp["sums"])
+    assert np.array_equal(mat.to_numpy(), m)
+    assert sim.ideal_component_count == exp["n_ideal"] > 50
+    with open(tmp_path / "graph.pkl", "rb") as f:
+        g = pickle.load(f)
+    assert type(g) is nx.Graph and g.number_of_edges() == exp["n_edges"]
+    # phase-2-only entry on the files just written
+    again = SampleSimilarity.from_filenames(tmp_path / "graph.pkl", sorted(get_table_files(od2)))
+    assert np.array_equal(again.get_dissimilarity_df().to_numpy(), m)
