@@ -409,7 +409,7 @@ static void upush(uvec_t* u, ungapped_t x) {
 
 static int64_t g_seeds = 0;
 /* All maximal exact runs >= WORD between transcripts of s1 (plus) and s2 (both strands),
- * each extended without gaps; duplicates removed. */
+ * extended without gaps under BLAST's diagonal rule (below); duplicates removed. */
 static uvec_t find_ungapped(const orc_sample* s1, const orc_sample* s2) {
     int64_t cap = 2 * s2->total + 1, nk = 0;
     kent_t* idx = malloc(cap * sizeof(kent_t));
@@ -429,7 +429,8 @@ static uvec_t find_ungapped(const orc_sample* s1, const orc_sample* s2) {
         }
     }
     qsort(idx, nk, sizeof(kent_t), cmp_kent);
-    uvec_t out = {0, 0, 0};
+    /* pass 1: every seed = maximal exact run >= WORD, as (ta, tb, minus, diag, [rs, re)) */
+    uvec_t seeds = {0, 0, 0};
     for (int ta = 0; ta < s1->n_seq; ta++) {
         const uint8_t* a = s1->fwd + s1->off[ta];
         int32_t la = (int32_t)(s1->off[ta + 1] - s1->off[ta]);
@@ -447,13 +448,33 @@ static uvec_t find_ungapped(const orc_sample* s1, const orc_sample* s2) {
                 int32_t re = i + WORD;
                 while (re < la && re + (j - i) < lb && is_match(a[re], b[re + (j - i)])) re++;
                 g_seeds++;
-                ungapped_t u = ungapped_extend(a, la, b, lb, i, re, j - i);
-                u.ta = ta; u.tb = tb; u.minus = minus;
-                upush(&out, u);
+                ungapped_t u;
+                u.ta = ta; u.tb = tb; u.minus = minus; u.diag = j - i; u.a0 = i; u.a1 = re; u.score = 0;
+                upush(&seeds, u);
             }
         }
     }
     free(idx); free(key); free(valid);
+    /* pass 2 (BLAST's diagonal rule): along each diagonal, seeds in ascending position; a seed that
+     * starts inside the ungapped HSP extended from an earlier seed of the diagonal is skipped */
+    uvec_t out = {0, 0, 0};
+    if (seeds.n) qsort(seeds.v, seeds.n, sizeof(ungapped_t), cmp_ungapped_id);
+    int32_t last_end = -1;
+    for (int64_t r = 0; r < seeds.n; r++) {
+        const ungapped_t* sd = &seeds.v[r];
+        if (r == 0 || sd->ta != seeds.v[r - 1].ta || sd->tb != seeds.v[r - 1].tb ||
+            sd->minus != seeds.v[r - 1].minus || sd->diag != seeds.v[r - 1].diag) last_end = -1;
+        if (sd->a0 < last_end) continue;
+        const uint8_t* a = s1->fwd + s1->off[sd->ta];
+        const uint8_t* b = (sd->minus ? s2->rc : s2->fwd) + s2->off[sd->tb];
+        int32_t la = (int32_t)(s1->off[sd->ta + 1] - s1->off[sd->ta]);
+        int32_t lb = (int32_t)(s2->off[sd->tb + 1] - s2->off[sd->tb]);
+        ungapped_t u = ungapped_extend(a, la, b, lb, sd->a0, sd->a1, sd->diag);
+        u.ta = sd->ta; u.tb = sd->tb; u.minus = sd->minus;
+        last_end = u.a1;
+        upush(&out, u);
+    }
+    free(seeds.v);
     if (out.n) {
         qsort(out.v, out.n, sizeof(ungapped_t), cmp_ungapped_id);
         int64_t w = 1;

@@ -190,7 +190,9 @@ __device__ __forceinline__ bool ung_before(const Ungapped& x, const Ungapped& y)
 // order; one contained in an earlier gapped HSP of the group is skipped; identical results are
 // dropped; at most RCQ_MAX_GAPPED_PER_GROUP gapped HSPs are kept.  Group g writes its results
 // to out[head .. head+count), the remaining slots of its range keep ta = -1.
-__global__ void __launch_bounds__(128) k_gapped(const Ungapped* __restrict__ U, const uint32_t* __restrict__ order,
+// U is indexed like the sorted seed list (slots of seeds the diagonal rule skipped have score < 0);
+// keys[] are the seed sort keys: group = key >> 21.
+__global__ void __launch_bounds__(128) k_gapped(const Ungapped* __restrict__ U,
                                                 const uint64_t* __restrict__ keys, int64_t n,
                                                 const uint32_t* __restrict__ heads, int64_t n_groups,
                                                 PairView P, Gapped* __restrict__ out,
@@ -209,11 +211,10 @@ __global__ void __launch_bounds__(128) k_gapped(const Ungapped* __restrict__ U, 
         if ((int64_t)g >= n_groups) break;
         const int64_t h = heads[g];
         int64_t e = h + 1;
-        const uint64_t key = keys[h];
-        while (e < n && keys[e] == key) e++;
+        const uint64_t key = keys[h] >> 21;
+        while (e < n && (keys[e] >> 21) == key) e++;
         const int32_t gsize = (int32_t)(e - h);
-        const Ungapped first = U[order[h]];
-        const int32_t ta = first.ta, tb = first.tb, minus = first.minus;
+        const int32_t ta = (int32_t)(key >> 22), tb = (int32_t)((key >> 1) & 0x1FFFFF), minus = (int32_t)(key & 1);
         const int64_t oa = __ldg(P.offA + ta), ob = __ldg(P.offB + tb);
         const int32_t la = __ldg(P.lenA + ta), lb = __ldg(P.lenB + tb);
         const SeqArena Bs = minus ? P.Br : P.Bf, Bo = minus ? P.Bf : P.Br;
@@ -223,12 +224,11 @@ __global__ void __launch_bounds__(128) k_gapped(const Ungapped* __restrict__ U, 
         for (int32_t it = 0; it < gsize && count < RCQ_MAX_GAPPED_PER_GROUP; it++) {
             // next ungapped HSP strictly after `last` in canonical order (duplicates collapse)
             Ungapped cur;
-            if (gsize == 1) {
-                cur = first;
-            } else {
+            {
                 Ungapped bestu; bool found = false;
                 for (int64_t x = h + lane; x < e; x += 32) {
-                    Ungapped u = U[order[x]];
+                    Ungapped u = U[x];
+                    if (u.score < 0) continue;
                     if (have_last && !ung_before(last, u)) continue;
                     if (!found || ung_before(u, bestu)) { bestu = u; found = true; }
                 }

@@ -93,28 +93,35 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
     int64_t n_gapped = 0;
     Gapped* Gd = nullptr;
     if (n_seeds > 0) {
-        // ---- ungapped HSPs, grouped by (tx1, tx2, strand)
+        // ---- seeds sorted by (tx1, tx2, strand, diagonal); ungapped HSPs under the diagonal rule
+        if (s1->n_seq >= (1 << 21) || s2->n_seq >= (1 << 21))
+            return rcq_fail(RCQ_ERR_CAPACITY, "rcq_search_pair: more than 2^21 transcripts in a sample");
         Ungapped* U = nullptr;
         RC(dalloc(ctx, &U, n_seeds));
+        CU(cudaMemsetAsync(U, 0xFF, n_seeds * sizeof(Ungapped), ctx->stream));
         CU(cudaMemsetAsync(ctr, 0, 16 * sizeof(int64_t), ctx->stream));
-        stage_tic(ctx, 2);
-        LAUNCH(ctx, k_ungapped, grid_for(n_seeds, 256), 256, 0, seeds, n_seeds, P, U, ctr + 4);
-        stage_toc(ctx, 2);
         stage_tic(ctx, 3);
-        dfree(ctx, seeds); seeds = nullptr;
-        uint64_t* keys = nullptr; uint32_t* order = nullptr; uint32_t* heads = nullptr;
+        uint64_t* keys = nullptr; uint32_t* order = nullptr; uint32_t* heads = nullptr; uint32_t* dheads = nullptr;
         RC(dalloc(ctx, &keys, n_seeds));
         RC(dalloc(ctx, &order, n_seeds));
         RC(dalloc(ctx, &heads, n_seeds));
-        LAUNCH(ctx, k_group_keys, grid_for(n_seeds, 256), 256, 0, U, n_seeds, keys, order);
+        RC(dalloc(ctx, &dheads, n_seeds));
+        LAUNCH(ctx, k_seed_keys, grid_for(n_seeds, 256), 256, 0, seeds, n_seeds, keys, order);
         RC(sort_pairs_u64_u32(ctx, &keys, &order, n_seeds, 64));
-        LAUNCH(ctx, k_group_heads, grid_for(n_seeds, 256), 256, 0, keys, n_seeds, heads, ctr + 5);
+        LAUNCH(ctx, k_seed_heads, grid_for(n_seeds, 256), 256, 0, keys, n_seeds, dheads, heads, ctr);
         stage_toc(ctx, 3);
-        RC(read_counters(ctx, 6));
+        RC(read_counters(ctx, 7));
+        stage_collect(ctx);
+        int64_t n_groups = ctx->h_pin[5], n_diag = ctx->h_pin[6];
+        stage_tic(ctx, 2);
+        LAUNCH(ctx, k_ungapped_diag, grid_for(n_diag, 128), 128, 0, seeds, order, keys, n_seeds, dheads, n_diag, P, U, ctr);
+        stage_toc(ctx, 2);
+        RC(read_counters(ctx, 8));
         stage_collect(ctx);
         st.ungapped_cells = ctx->h_pin[4];
-        int64_t n_groups = ctx->h_pin[5];
-        st.n_ungapped = n_seeds;
+        st.n_ungapped = ctx->h_pin[7];
+        dfree(ctx, seeds); seeds = nullptr;
+        dfree(ctx, order); dfree(ctx, dheads);
         // ---- gapped extension, warp per group
         Gapped* G = nullptr;
         RC(dalloc(ctx, &G, n_seeds));
@@ -125,9 +132,9 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
         RC(dalloc(ctx, &scratch, per_warp * blocks * (threads / 32)));
         CU(cudaMemsetAsync(ctr, 0, 16 * sizeof(int64_t), ctx->stream));
         stage_tic(ctx, 4);
-        LAUNCH(ctx, k_gapped, blocks, threads, 0, U, order, keys, n_seeds, heads, n_groups, P, G, scratch, per_warp, ctr);
+        LAUNCH(ctx, k_gapped, blocks, threads, 0, U, keys, n_seeds, heads, n_groups, P, G, scratch, per_warp, ctr);
         stage_toc(ctx, 4);
-        dfree(ctx, scratch); dfree(ctx, U); dfree(ctx, keys); dfree(ctx, order); dfree(ctx, heads);
+        dfree(ctx, scratch); dfree(ctx, U); dfree(ctx, keys); dfree(ctx, heads);
         // ---- compact (stable: group order, then processing order inside the group)
         RC(dalloc(ctx, &Gd, n_seeds));
         size_t bytes = 0;

@@ -170,15 +170,12 @@ __global__ void __launch_bounds__(256) k_seed_verify(const uint2* __restrict__ c
     }
 }
 
-// X-drop ungapped extension (thread per seed) + start point of the gapped extension.
+// X-drop ungapped extension of one seed + start point of the gapped extension.
 // Word-parallel: 32 base pairs per match mask; a run of matches is consumed in one step.
-__global__ void __launch_bounds__(256) k_ungapped(const Seed* __restrict__ seeds, int64_t n, PairView P,
-                                                  Ungapped* __restrict__ out,
-                                                  unsigned long long* __restrict__ cells) {
-    int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    unsigned long long work = 0;
-    if (e < n) {
-        Seed s = seeds[e];
+__device__ __forceinline__ Ungapped ungapped_one(const Seed& s, const PairView& P, unsigned long long& work) {
+    Ungapped u;
+    {
+
         const SeqArena& B = s.minus ? P.Br : P.Bf;
         int64_t ba = __ldg(P.offA + s.ta), bb = __ldg(P.offB + s.tb);
         int32_t la = __ldg(P.lenA + s.ta), lb = __ldg(P.lenB + s.tb), d = s.diag;
@@ -240,35 +237,68 @@ __global__ void __launch_bounds__(256) k_ungapped(const Seed* __restrict__ seeds
         }
         if (run > best_len) { best_len = run; best_s = a1 - run; }
         work += a1 - a0;
-        Ungapped u;
         u.ta = s.ta; u.tb = s.tb; u.minus = s.minus; u.diag = d; u.a0 = a0; u.a1 = a1;
         u.score = score; u.i0 = best_s + best_len / 2;
-        out[e] = u;
     }
-    for (int o = 16; o; o >>= 1) work += __shfl_down_sync(0xffffffffu, work, o);
-    if ((threadIdx.x & 31) == 0 && work) atomicAdd(cells, work);
+    return u;
 }
 
-// group key of each ungapped HSP for the sort: (ta, tb, strand)
-__global__ void k_group_keys(const Ungapped* __restrict__ u, int64_t n, uint64_t* __restrict__ keys,
-                             uint32_t* __restrict__ vals) {
+// sort key of a seed: (ta, tb, strand, diagonal); seeds of one diagonal end up adjacent, and so do
+// the diagonals of one (ta, tb, strand) group
+#define RCQ_DIAG_BITS 21
+__global__ void k_seed_keys(const Seed* __restrict__ seeds, int64_t n, uint64_t* __restrict__ keys,
+                            uint32_t* __restrict__ vals) {
     int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= n) return;
-    keys[e] = ((uint64_t)(uint32_t)u[e].ta << 32) | ((uint64_t)(uint32_t)u[e].tb << 1) | (uint64_t)u[e].minus;
+    const Seed s = seeds[e];
+    keys[e] = ((uint64_t)(uint32_t)s.ta << 43) | ((uint64_t)(uint32_t)s.tb << 22) | ((uint64_t)s.minus << 21) |
+              (uint64_t)(uint32_t)(s.diag + (1 << 20));
     vals[e] = (uint32_t)e;
 }
-// group heads after the sort: heads[g] = first sorted slot of group g
-__global__ void k_group_heads(const uint64_t* __restrict__ keys, int64_t n, uint32_t* __restrict__ heads,
-                              unsigned long long* __restrict__ n_groups) {
+// heads of diagonals and of (ta, tb, strand) groups in the sorted order (list order is irrelevant)
+__global__ void k_seed_heads(const uint64_t* __restrict__ keys, int64_t n, uint32_t* __restrict__ dheads,
+                             uint32_t* __restrict__ gheads, unsigned long long* __restrict__ counters /* [5]=groups [6]=diagonals */) {
     int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= n) return;
-    bool head = (e == 0) || keys[e] != keys[e - 1];
-    unsigned m = __ballot_sync(__activemask(), head);
-    // order of heads[] does not matter: the gapped kernel only needs the set of group starts
-    if (head) {
-        unsigned long long g = atomicAdd(n_groups, 1ull);
-        heads[g] = (uint32_t)e;
+    const uint64_t k = keys[e], kp = e ? keys[e - 1] : ~k;
+    if (k != kp) dheads[atomicAdd(counters + 6, 1ull)] = (uint32_t)e;
+    if ((k >> RCQ_DIAG_BITS) != (kp >> RCQ_DIAG_BITS)) gheads[atomicAdd(counters + 5, 1ull)] = (uint32_t)e;
+}
+// BLAST's diagonal rule, thread per diagonal: seeds in ascending position; a seed that starts inside
+// the ungapped HSP extended from an earlier seed of the diagonal is skipped.  U is indexed like the
+// sorted seed list; slots of skipped seeds keep score = -1.
+__global__ void __launch_bounds__(128) k_ungapped_diag(const Seed* __restrict__ seeds, const uint32_t* __restrict__ order,
+                                                       const uint64_t* __restrict__ keys, int64_t n,
+                                                       const uint32_t* __restrict__ dheads, int64_t n_diag, PairView P,
+                                                       Ungapped* __restrict__ U,
+                                                       unsigned long long* __restrict__ counters /* [4]=bases [7]=HSPs */) {
+    int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long work = 0, made = 0;
+    if (g < n_diag) {
+        const int64_t h = dheads[g];
+        const uint64_t key = keys[h];
+        int64_t e = h + 1;
+        while (e < n && keys[e] == key) e++;
+        int32_t last_end = -1;
+        while (true) {
+            int64_t pick = -1;
+            int32_t pick_rs = 0x7fffffff;
+            for (int64_t x = h; x < e; x++) {
+                int32_t rs = seeds[order[x]].rs;
+                if (rs >= last_end && rs < pick_rs) { pick_rs = rs; pick = x; }
+            }
+            if (pick < 0) break;
+            const Seed s = seeds[order[pick]];
+            Ungapped u = ungapped_one(s, P, work);
+            U[pick] = u;
+            made++;
+            last_end = max(u.a1, s.rs + 1);
+        }
     }
-    (void)m;
+    for (int o = 16; o; o >>= 1) {
+        work += __shfl_down_sync(0xffffffffu, work, o);
+        made += __shfl_down_sync(0xffffffffu, made, o);
+    }
+    if ((threadIdx.x & 31) == 0 && work) { atomicAdd(counters + 4, work); atomicAdd(counters + 7, made); }
 }
 
