@@ -40,6 +40,7 @@ def parse_args():
     ap.add_argument("--seed", type=int, default=487)
     ap.add_argument("--cpu-sample", type=int, default=600, help="top-gene transcripts per sample in the CPU legs")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--streams", type=int, default=3, help="CUDA streams (host threads) per GPU")
     return ap.parse_args()
 
 
@@ -183,7 +184,7 @@ def main():
         dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local))
         dist = dist_mod
     from rna_clique_b200.engine import Engine, select_top_genes
-    eng = Engine(local)
+    eng = Engine(local, streams=a.streams)
     stream = torch.cuda.ExternalStream(eng.ctx.stream, device=torch.device("cuda", local))
 
     _, inputs_dev, labels = make_inputs(a, f"cuda:{local}")
@@ -210,8 +211,8 @@ def main():
         for _ in range(warmup):
             out = fn()
         barrier()
-        eng.ctx.stage_times(reset=True)
-        l0 = eng.ctx.launches
+        eng.stage_times(reset=True)
+        l0 = eng.launches
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
         walls = []
@@ -227,7 +228,7 @@ def main():
             t = torch.tensor([ms], device=f"cuda:{local}", dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             ms = float(t.item())
-        return ms / steps, out, eng.ctx.stage_times(reset=True), (eng.ctx.launches - l0) / steps
+        return ms / steps, out, eng.stage_times(reset=True), (eng.launches - l0) / steps
 
     sampler = ClockSampler(local)
     sampler.start()
@@ -289,7 +290,7 @@ def main():
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s"},
             "stages_ms_per_step": {k: v["ms"] / a.steps for k, v in stages.items()},
             "search_stats_per_step": agg,
-            "phase2_counts": res["counts"], "host_wall_ms_per_step": step_walls,
+            "phase2_counts": res["counts"], "host_wall_ms_per_step": step_walls, "host_ms_last_step": {"hbm_resident": res["host_ms"], "from_host_buffers": res2["host_ms"]},
         }
     if dist is not None:
         dist.barrier()

@@ -131,11 +131,12 @@ __device__ __forceinline__ uint32_t kmer_hash(const uint32_t* fwd, const uint32_
 // Window-minimizer selection (window = 13 consecutive 16-mers = one 28-mer).  Position p is
 // selected iff its hash equals the minimum of SOME window containing it (all tied minima are
 // kept, so the choice is symmetric under reverse complement).  Warp per transcript.
-template <bool FILL>
+// Entries are appended with one atomic per warp step; entries past `cap` are counted but not
+// written (the host then re-runs with the exact size).
 __global__ void k_minimizers(const uint32_t* __restrict__ fwd, const uint32_t* __restrict__ mask,
                              const int32_t* __restrict__ aoff, const int32_t* __restrict__ len,
                              int32_t n_seq, unsigned long long* __restrict__ counter,
-                             uint64_t* __restrict__ out, uint32_t* __restrict__ selmap) {
+                             uint64_t* __restrict__ out, unsigned long long cap, uint32_t* __restrict__ selmap) {
     __shared__ uint32_t sh[8][256 + 8];
     __shared__ uint8_t so[8][256 + 8];
     int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -176,10 +177,11 @@ __global__ void k_minimizers(const uint32_t* __restrict__ fwd, const uint32_t* _
                     unsigned long long base = 0;
                     if (lane == 0) base = atomicAdd(counter, (unsigned long long)__popc(m));
                     base = __shfl_sync(0xffffffffu, base, 0);
-                    if (FILL && sel) {
+                    if (sel) {
                         unsigned long long pos = (unsigned long long)(off + p);
-                        out[base + __popc(m & ((1u << lane) - 1u))] =
-                            ((unsigned long long)rcq_index_key(h) << 32) | (pos << 1) | so[wib][i + H];
+                        unsigned long long slot = base + __popc(m & ((1u << lane) - 1u));
+                        if (slot < cap)
+                            out[slot] = ((unsigned long long)rcq_index_key(h) << 32) | (pos << 1) | so[wib][i + H];
                         atomicOr(selmap + (pos >> 5), 1u << (pos & 31));
                     }
                 }
@@ -209,17 +211,17 @@ __global__ void k_build_dir(const uint64_t* __restrict__ index, int64_t n, uint3
     for (uint32_t b = lo; b <= hi; b++) dir[b] = (uint32_t)i;
 }
 
-static int sort_u64(rcq_ctx* ctx, uint64_t* keys, int64_t n) {
+static int sort_u64(rcq_ctx* ctx, uint64_t* keys, int64_t n, int begin_bit = 0) {
     if (n <= 1) return 0;
     uint64_t* tmp = nullptr;
     RC(dalloc(ctx, &tmp, n));
     cub::DoubleBuffer<uint64_t> db(keys, tmp);
     size_t bytes = 0;
-    CU(cub::DeviceRadixSort::SortKeys(nullptr, bytes, db, (int)n, 0, 64, ctx->stream));
+    CU(cub::DeviceRadixSort::SortKeys(nullptr, bytes, db, (int)n, begin_bit, 64, ctx->stream));
     void* ws = nullptr;
     CU(cudaMallocAsync(&ws, bytes, ctx->stream));
-    CU(cub::DeviceRadixSort::SortKeys(ws, bytes, db, (int)n, 0, 64, ctx->stream));
-    ctx->launches += 8;
+    CU(cub::DeviceRadixSort::SortKeys(ws, bytes, db, (int)n, begin_bit, 64, ctx->stream));
+    ctx->launches += (64 - begin_bit) / 8 + 1;
     if (db.Current() != keys)
         CU(cudaMemcpyAsync(keys, db.Current(), n * sizeof(uint64_t), cudaMemcpyDeviceToDevice,
                            ctx->stream));
@@ -256,20 +258,27 @@ int rcq_sample_build(rcq_ctx* ctx, rcq_sample* s, const uint8_t* d_ascii, int64_
         LAUNCH(ctx, k_tx_tables, blocks, 256, 0, s->off, s->len, s->n_seq, s->blk2tx, s->ol);
         LAUNCH(ctx, k_revcomp, blocks, 256, 0, s->fwd, s->mask, s->off, s->len, s->n_seq, s->rc,
                s->mask_rc);
-        LAUNCH(ctx, k_minimizers<false>, blocks, 256, 0, s->fwd, s->mask, s->off, s->len, s->n_seq,
-               ctr + 1, (uint64_t*)nullptr, (uint32_t*)nullptr);
     }
-    CU(cudaMemcpyAsync(ctx->h_pin, ctr, 2 * sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
-    CU(cudaStreamSynchronize(ctx->stream));
-    s->n_masked = ctx->h_pin[0];
-    s->n_index = ctx->h_pin[1];
-    RC(dalloc(ctx, &s->index, s->n_index));
-    if (s->n_index) {
+    // minimizer entries: one pass into a buffer sized for the usual density (2/14 per base);
+    // a denser sample is re-run once with the exact count
+    int64_t cap = s->total / 5 + 4096;
+    for (int attempt = 0; attempt < 2; attempt++) {
+        RC(dalloc(ctx, &s->index, cap));
         CU(cudaMemsetAsync(ctr + 1, 0, sizeof(unsigned long long), ctx->stream));
-        LAUNCH(ctx, k_minimizers<true>, blocks, 256, 0, s->fwd, s->mask, s->off, s->len, s->n_seq,
-               ctr + 1, s->index, s->sel);
-        RC(sort_u64(ctx, s->index, s->n_index));
+        if (s->n_seq)
+            LAUNCH(ctx, k_minimizers, blocks, 256, 0, s->fwd, s->mask, s->off, s->len, s->n_seq, ctr + 1, s->index,
+                   (unsigned long long)cap, s->sel);
+        CU(cudaMemcpyAsync(ctx->h_pin, ctr, 2 * sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+        CU(cudaStreamSynchronize(ctx->stream));
+        s->n_masked = ctx->h_pin[0];
+        s->n_index = ctx->h_pin[1];
+        if (s->n_index <= cap) break;
+        dfree(ctx, s->index); s->index = nullptr;
+        cap = s->n_index;
     }
+    // sorted by key only (bits 32..63): entries of one key stay in append order, which no result
+    // depends on (seeds are re-sorted by transcript and diagonal)
+    if (s->n_index) RC(sort_u64(ctx, s->index, s->n_index, 32));
     LAUNCH(ctx, k_build_dir, grid_for(s->n_index + 1, 256), 256, 0, s->index, s->n_index, s->dir);
     return 0;
 }

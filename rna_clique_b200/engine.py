@@ -12,6 +12,8 @@ collective is an all-gather of the flat hit tables (torch.distributed, NCCL) bef
 from __future__ import annotations
 
 import itertools
+import time
+from concurrent.futures import ThreadPoolExecutor
 from fractions import Fraction
 from typing import Optional, Sequence
 
@@ -24,24 +26,7 @@ class NoIdealComponentsError(Exception):
     """Reference: filtered_distance.py:126-127."""
 
 
-def select_top_genes(coverage: np.ndarray, gene: np.ndarray, top: int) -> np.ndarray:
-    """Indices (file order) of every transcript whose gene is among the `top` genes by
-    max-isoform coverage.  Ties: heapq.nlargest over (coverage, gene) tuples => larger gene id
-    wins (select_top_genes.py:108-127).  Coverage starts from 0.0 (defaultdict(float))."""
-    coverage = np.asarray(coverage, dtype=np.float64)
-    gene = np.asarray(gene)
-    ug, inv = np.unique(gene, return_inverse=True)
-    best = np.zeros(len(ug), dtype=np.float64)
-    np.maximum.at(best, inv, coverage)
-    if top >= len(ug):
-        keep_gene = np.ones(len(ug), dtype=bool)
-    elif top <= 0:
-        keep_gene = np.zeros(len(ug), dtype=bool)
-    else:
-        order = np.lexsort((ug, best))            # ascending by coverage, then gene
-        keep_gene = np.zeros(len(ug), dtype=bool)
-        keep_gene[order[len(ug) - top:]] = True
-    return np.flatnonzero(keep_gene[inv])
+from .select_top_genes import top_gene_mask as select_top_genes  # noqa: E402  (select_top_genes.py:108-127)
 
 
 def schedule_pairs(n: int, totals: Sequence[int], world: int):
@@ -59,20 +44,61 @@ def schedule_pairs(n: int, totals: Sequence[int], world: int):
 
 
 class Engine:
-    def __init__(self, device: int = 0):
-        self.ctx = _native.Context(device)
+    """`streams` CUDA contexts (one stream + scratch each) on one GPU, each driven by its own host
+    thread: while one pair's host code waits for a device counter, the other streams keep the SMs
+    busy.  ctypes releases the GIL during library calls, so the threads overlap for real."""
+
+    def __init__(self, device: int = 0, streams: int = 3):
+        self.ctxs = [_native.Context(device) for _ in range(max(1, streams))]
+        self.ctx = self.ctxs[0]
         self.device = device
+        self._pool = ThreadPoolExecutor(len(self.ctxs)) if len(self.ctxs) > 1 else None
+
+    def _fan_out(self, n_items: int, fn):
+        """out[k] = fn(ctx, k) for k < n_items; item k runs on context k % streams, and each context
+        is only ever used by one thread at a time."""
+        out = [None] * n_items
+        S = len(self.ctxs)
+
+        def work(w):
+            for k in range(w, n_items, S):
+                out[k] = fn(self.ctxs[w], k)
+
+        if self._pool is None or n_items <= 1:
+            for w in range(S):
+                work(w)
+        else:
+            for f in [self._pool.submit(work, w) for w in range(S)]:
+                f.result()
+        return out
+
+    @property
+    def launches(self) -> int:
+        return sum(c.launches for c in self.ctxs)
+
+    def stage_times(self, reset: bool = False) -> dict:
+        tot = None
+        for c in self.ctxs:
+            st = c.stage_times(reset)
+            if tot is None:
+                tot = st
+            else:
+                for k, v in st.items():
+                    tot[k]["ms"] += v["ms"]
+                    tot[k]["calls"] += v["calls"]
+        return tot
 
     # ---- kernels (1)+(2)
-    def upload(self, ascii_, starts, lengths, gene, iso, name: str = "") -> _native.Sample:
-        return _native.Sample(self.ctx, ascii_, starts, gene, iso, name=name, lengths=lengths)
+    def upload(self, ascii_, starts, lengths, gene, iso, name: str = "", ctx=None) -> _native.Sample:
+        return _native.Sample(ctx or self.ctx, ascii_, starts, gene, iso, name=name, lengths=lengths)
 
     # ---- kernel (3)
     def search(self, samples, pairs=None, evalue: float = 1e-99, top_n: int = 1, keep_all: bool = True):
         """Returns (pairs, tables): tables[k] joins samples pairs[k] = (i, j), i = transcripts1."""
         if pairs is None:
             pairs = list(itertools.combinations(range(len(samples)), 2))
-        tables = [_native.search_pair(self.ctx, samples[i], samples[j], evalue, top_n, keep_all) for i, j in pairs]
+        tables = self._fan_out(len(pairs), lambda ctx, k: _native.search_pair(
+            ctx, samples[pairs[k][0]], samples[pairs[k][1]], evalue, top_n, keep_all))
         return pairs, tables
 
     # ---- kernel (4)
@@ -102,14 +128,19 @@ class Engine:
         Returns dict(labels, matrix, sums, pairs, stats[, tables, samples])."""
         world = dist.get_world_size() if dist is not None else 1
         rank = dist.get_rank() if dist is not None else 0
-        samples = []
-        for k, s in enumerate(inputs):
+        t_start = time.perf_counter()
+
+        def up(ctx, k):
+            s = inputs[k]
             starts, lengths, gene, iso = (np.asarray(s[c]) for c in ("starts", "lengths", "gene", "iso"))
             if top_genes is not None:
                 keep = select_top_genes(s["coverage"], gene, top_genes)
                 starts, lengths, gene, iso = starts[keep], lengths[keep], gene[keep], iso[keep]
-            samples.append(self.upload(s["ascii"], starts, lengths, gene, iso, name=labels[k]))
+            return self.upload(s["ascii"], starts, lengths, gene, iso, name=labels[k], ctx=ctx)
+
+        samples = self._fan_out(len(inputs), up)
         n = len(samples)
+        t_upload = time.perf_counter()
         pairs, owner = schedule_pairs(n, [s.total for s in samples], world)
         mine = [k for k in range(len(pairs)) if owner[k] == rank]
         _, my_tables = self.search(samples, [pairs[k] for k in mine], evalue, top_n, keep_all)
@@ -117,14 +148,19 @@ class Engine:
         for t in my_tables:
             for key, v in t.stats.items():
                 stats[key] = stats.get(key, 0) + v
+        t_search = time.perf_counter()
         if world > 1:
             from .exchange import allgather_tables
             tables = allgather_tables(self.ctx, dist, pairs, owner, mine, my_tables)
         else:
             tables = my_tables
         stride = 1 + max([0] + [int(np.max(s["gene"], initial=0)) for s in inputs])
+        t_exchange = time.perf_counter()
         res = self.phase2(n, pairs, tables, stride)
-        out = dict(pairs=pairs, nident_sum=res["nident_sum"], denom_sum=res["denom_sum"], counts=res["counts"],
+        t_phase2 = time.perf_counter()
+        out = dict(host_ms=dict(upload=(t_upload - t_start) * 1e3, search=(t_search - t_upload) * 1e3,
+                                exchange=(t_exchange - t_search) * 1e3, phase2=(t_phase2 - t_exchange) * 1e3),
+                   pairs=pairs, nident_sum=res["nident_sum"], denom_sum=res["denom_sum"], counts=res["counts"],
                    stats=stats, no_ideal=res["no_ideal"], n_local_pairs=len(mine),
                    lengths=[s.total for s in samples])
         if not res["no_ideal"]:
@@ -139,4 +175,8 @@ class Engine:
         return out
 
     def close(self):
-        self.ctx.close()
+        if self._pool is not None:
+            self._pool.shutdown()
+            self._pool = None
+        for c in self.ctxs:
+            c.close()
