@@ -43,7 +43,7 @@ void* rcq_ctx_stream(rcq_ctx* ctx);
 int64_t rcq_ctx_launches(rcq_ctx* ctx);
 /* device time per stage, measured with CUDA events on the context's stream and accumulated over
  * calls: 0 pack+index, 1 seed join, 2 ungapped, 3 sort/group, 4 gapped DP, 5 selection+table,
- * 6 phase 2 (7 unused).  reset != 0 clears the accumulators after reading. */
+ * 6 phase 2, 7 seed probe alone (also inside 1).  reset != 0 clears the accumulators after reading. */
 int rcq_ctx_stage_times(rcq_ctx* ctx, double ms[8], int64_t calls[8], int reset);
 
 /* ---- kernels (1)+(2): pack + seed index.  Replaces makeblastdb per sample
@@ -69,7 +69,7 @@ int rcq_sample_download(const rcq_sample* s, uint32_t* fwd, uint32_t* rc, uint32
  * best-bitscore reduction (:135-164) and HomologFinder.get_match_table (:215-302).
  * s1 plays transcripts1 (ssample side), s2 transcripts2 (qsample side). */
 typedef struct {
-    int64_t n_candidates;   /* minimizer join matches examined */
+    int64_t n_candidates;   /* minimizer join key matches examined by the probe */
     int64_t n_seeds;        /* exact runs >= 28 that triggered an ungapped extension */
     int64_t n_ungapped;     /* distinct ungapped HSPs */
     int64_t n_gapped;       /* gapped HSPs produced */
@@ -78,6 +78,7 @@ typedef struct {
     int64_t n_fwd, n_bwd;   /* rows of the two direction tables after best-hit selection */
     int64_t n_rows;         /* rows of the gene-matches table */
     int64_t band_retries;   /* gapped extensions re-run with a wider band */
+    int64_t n_verified;     /* key matches that survived the flank filter and were verified on the sequences */
 } rcq_search_stats;
 
 int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sample* s2, double evalue,

@@ -38,7 +38,7 @@ class NoIdealComponents(RcqError):
 
 class SearchStats(C.Structure):
     _fields_ = [(n, C.c_int64) for n in ["n_candidates", "n_seeds", "n_ungapped", "n_gapped", "dp_cells",
-                                         "ungapped_cells", "n_fwd", "n_bwd", "n_rows", "band_retries"]]
+                                         "ungapped_cells", "n_fwd", "n_bwd", "n_rows", "band_retries", "n_verified"]]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -130,7 +130,7 @@ class Context:
     def launches(self) -> int:
         return lib().rcq_ctx_launches(self.h)
 
-    STAGES = ["pack_index", "seed_join", "ungapped", "sort_group", "gapped_dp", "select_table", "phase2"]
+    STAGES = ["pack_index", "seed_join", "ungapped", "sort_group", "gapped_dp", "select_table", "phase2", "seed_probe"]
 
     def stage_times(self, reset: bool = False) -> dict:
         ms = np.zeros(8, dtype=np.float64)

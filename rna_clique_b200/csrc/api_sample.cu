@@ -140,7 +140,7 @@ void rcq_sample_free(rcq_sample* s) {
     cudaSetDevice(c->device);
     dfree(c, s->fwd); dfree(c, s->rc); dfree(c, s->mask); dfree(c, s->mask_rc);
     dfree(c, s->off); dfree(c, s->len); dfree(c, s->gene); dfree(c, s->iso);
-    dfree(c, s->index); dfree(c, s->dir); dfree(c, s->sel); dfree(c, s->gidx);
+    dfree(c, s->index); dfree(c, s->fctx); dfree(c, s->dir); dfree(c, s->sel); dfree(c, s->gidx);
     dfree(c, s->blk2tx); dfree(c, s->ol);
     delete s;
 }

@@ -191,9 +191,9 @@ __device__ __forceinline__ bool ung_before(const Ungapped& x, const Ungapped& y)
 // dropped; at most RCQ_MAX_GAPPED_PER_GROUP gapped HSPs are kept.  Group g writes its results
 // to out[head .. head+count), the remaining slots of its range keep ta = -1.
 // U is indexed like the sorted seed list (slots of seeds the diagonal rule skipped have score < 0);
-// keys[] are the seed sort keys: group = key >> 21.
+// keys[] are the seed sort keys (KeyFmt): group = key >> d_bits.
 __global__ void __launch_bounds__(128) k_gapped(const Ungapped* __restrict__ U,
-                                                const uint64_t* __restrict__ keys, int64_t n,
+                                                const uint64_t* __restrict__ keys, int64_t n, KeyFmt F,
                                                 const uint32_t* __restrict__ heads, int64_t n_groups,
                                                 PairView P, Gapped* __restrict__ out,
                                                 int32_t* __restrict__ scratch, int64_t scratch_per_warp,
@@ -211,10 +211,10 @@ __global__ void __launch_bounds__(128) k_gapped(const Ungapped* __restrict__ U,
         if ((int64_t)g >= n_groups) break;
         const int64_t h = heads[g];
         int64_t e = h + 1;
-        const uint64_t key = keys[h] >> 21;
-        while (e < n && (keys[e] >> 21) == key) e++;
+        const uint64_t key = keys[h] >> F.d_bits;
+        while (e < n && (keys[e] >> F.d_bits) == key) e++;
         const int32_t gsize = (int32_t)(e - h);
-        const int32_t ta = (int32_t)(key >> 22), tb = (int32_t)((key >> 1) & 0x1FFFFF), minus = (int32_t)(key & 1);
+        const int32_t ta = (int32_t)(key >> (F.tb_bits + 1)), tb = (int32_t)((key >> 1) & ((1u << F.tb_bits) - 1u)), minus = (int32_t)(key & 1);
         const int64_t oa = __ldg(P.offA + ta), ob = __ldg(P.offB + tb);
         const int32_t la = __ldg(P.lenA + ta), lb = __ldg(P.lenB + tb);
         const SeqArena Bs = minus ? P.Br : P.Bf, Bo = minus ? P.Bf : P.Br;

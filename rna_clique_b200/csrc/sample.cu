@@ -117,52 +117,101 @@ __global__ void k_revcomp(const uint32_t* __restrict__ fwd, const uint32_t* __re
 }
 
 // Canonical-16-mer hash at arena position p (0xFFFFFFFF = contains a masked base).
+// *pal = the 16-mer equals its own reverse complement.
 __device__ __forceinline__ uint32_t kmer_hash(const uint32_t* fwd, const uint32_t* mask, int64_t p,
-                                              uint32_t* orient) {
+                                              uint32_t* orient, uint32_t* pal) {
     if (fetchmask32(mask, p) & 0xFFFFu) return 0xFFFFFFFFu;
     uint32_t f = (uint32_t)fetch32(fwd, p);
     uint32_t r = rev2_32(~f);
     uint32_t hf = rcq_mix32(f), hr = rcq_mix32(r);
     *orient = hr < hf;
+    *pal = hr == hf;
     uint32_t h = min(hf, hr);
     return min(h, 0xFFFFFFFEu);
 }
 
+// reverse complement of 13 bases held in the low 26 bits
+__device__ __forceinline__ uint32_t rc13(uint32_t x) { return rev2_32(~x & 0x03FFFFFFu) >> 6; }
+
+// Flank context of the index entry at transcript position p (arena offset off, transcript length n,
+// orientation o of its canonical 16-mer): the 13 bases before and after the 16-mer, read on the
+// canonical strand.  Word layout: bits 0..25 bases, bit 30 (low word only) = palindromic 16-mer,
+// bit 31 = flank not available (runs off the transcript or holds a masked base).
+// Two entries of the same key whose "incoming" flanks are equal and available lie in an exact run
+// that started >= 13 bases earlier, so they can never be the leftmost joint anchor of that run:
+// k_seed_probe drops such key matches without touching the sequences (seed_kernels.cuh).
+__device__ __forceinline__ uint64_t flank_ctx(const uint32_t* fwd, const uint32_t* mask, int64_t off, int32_t p,
+                                              int32_t n, uint32_t o, uint32_t pal) {
+    const uint32_t M26 = 0x03FFFFFFu, M13 = 0x1FFFu;
+    uint32_t L = 0x80000000u, R = 0x80000000u;
+    if (p >= RCQ_WIN && !(fetchmask32(mask, off + p - RCQ_WIN) & M13))
+        L = (uint32_t)fetch32(fwd, off + p - RCQ_WIN) & M26;
+    if (p + RCQ_KMER + RCQ_WIN <= n && !(fetchmask32(mask, off + p + RCQ_KMER) & M13))
+        R = (uint32_t)fetch32(fwd, off + p + RCQ_KMER) & M26;
+    uint32_t cl, cr;
+    if (!o) { cl = L; cr = R; }
+    else {
+        cl = (R >> 31) ? R : rc13(R);
+        cr = (L >> 31) ? L : rc13(L);
+    }
+    if (pal) cl |= 0x40000000u;
+    return ((uint64_t)cr << 32) | cl;
+}
+
 // Window-minimizer selection (window = 13 consecutive 16-mers = one 28-mer).  Position p is
 // selected iff its hash equals the minimum of SOME window containing it (all tied minima are
-// kept, so the choice is symmetric under reverse complement).  Warp per transcript.
-// Entries are appended with one atomic per warp step; entries past `cap` are counted but not
-// written (the host then re-runs with the exact size).
-__global__ void k_minimizers(const uint32_t* __restrict__ fwd, const uint32_t* __restrict__ mask,
-                             const int32_t* __restrict__ aoff, const int32_t* __restrict__ len,
-                             int32_t n_seq, unsigned long long* __restrict__ counter,
-                             uint64_t* __restrict__ out, unsigned long long cap, uint32_t* __restrict__ selmap) {
-    __shared__ uint32_t sh[8][256 + 8];
-    __shared__ uint8_t so[8][256 + 8];
-    int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    int warp = blockIdx.x * (blockDim.x >> 5) + wib;
-    int nwarps = gridDim.x * (blockDim.x >> 5);
+// kept, so the choice is symmetric under reverse complement).  Warp per transcript; selected
+// entries are staged in a per-warp shared-memory buffer and appended with ONE atomic per flush
+// (a single global counter serialises at ~1 atomic/ns, which bounded the per-step version).
+// The 32 positions of a warp step are one aligned word of the `sel` bitmap: plain store of the ballot.
+// Entries past `cap` are counted but not written (the host then re-runs with the exact size).
+#define MZ_WARPS 8
+#define MZ_BUF 256
+__global__ void __launch_bounds__(32 * MZ_WARPS) k_minimizers(
+    const uint32_t* __restrict__ fwd, const uint32_t* __restrict__ mask, const int32_t* __restrict__ aoff,
+    const int32_t* __restrict__ len, int32_t n_seq, unsigned long long* __restrict__ counter,
+    uint64_t* __restrict__ out, uint64_t* __restrict__ out_ctx, unsigned long long cap,
+    uint32_t* __restrict__ selmap) {
+    __shared__ uint32_t sh[MZ_WARPS][256 + 8];
+    __shared__ uint8_t so[MZ_WARPS][256 + 8];
+    __shared__ uint64_t be[MZ_WARPS][MZ_BUF], bc[MZ_WARPS][MZ_BUF];
+    const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = blockIdx.x * MZ_WARPS + wib;
+    const int nwarps = gridDim.x * MZ_WARPS;
     const int T = 224, H = RCQ_WIN - 1;  // tile and halo
+    int nbuf = 0;                        // warp-uniform fill of be/bc
+    auto flush = [&]() {
+        if (!nbuf) return;
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(counter, (unsigned long long)nbuf);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        __syncwarp();
+        for (int i = lane; i < nbuf; i += 32)
+            if (base + i < cap) { out[base + i] = be[wib][i]; out_ctx[base + i] = bc[wib][i]; }
+        __syncwarp();
+        nbuf = 0;
+    };
     for (int t = warp; t < n_seq; t += nwarps) {
-        int64_t off = aoff[t];
-        int32_t nk = len[t] - RCQ_KMER + 1;
+        const int64_t off = aoff[t];
+        const int32_t n = len[t];
+        const int32_t nk = n - RCQ_KMER + 1;
         if (nk < RCQ_WIN) continue;
         for (int32_t c = 0; c < nk; c += T) {
             __syncwarp();
             for (int i = lane; i < T + 2 * H; i += 32) {
                 int32_t p = c - H + i;
-                uint32_t o = 0, h = 0xFFFFFFFFu;
-                if (p >= 0 && p < nk) h = kmer_hash(fwd, mask, off + p, &o);
+                uint32_t o = 0, pal = 0, h = 0xFFFFFFFFu;
+                if (p >= 0 && p < nk) h = kmer_hash(fwd, mask, off + p, &o, &pal);
                 sh[wib][i] = h;
-                so[wib][i] = (uint8_t)o;
+                so[wib][i] = (uint8_t)(o | (pal << 1));
             }
             __syncwarp();
             for (int i0 = 0; i0 < T; i0 += 32) {
-                int i = i0 + lane;
-                int32_t p = c + i;
+                const int i = i0 + lane;
+                const int32_t p = c + i;
                 bool sel = false;
                 uint32_t h = 0xFFFFFFFFu;
-                if (i < T && p < nk) {
+                if (p < nk) {
                     h = sh[wib][i + H];
                     if (h != 0xFFFFFFFFu) {
                         int a = 0, b = 0;
@@ -172,22 +221,23 @@ __global__ void k_minimizers(const uint32_t* __restrict__ fwd, const uint32_t* _
                         sel = (H - b) <= a;  // some window [p-j, p-j+12], j<=a, 12-j<=b
                     }
                 }
-                unsigned m = __ballot_sync(0xffffffffu, sel);
+                const unsigned m = __ballot_sync(0xffffffffu, sel);
+                if (c + i0 < nk && lane == 0) selmap[(off + c + i0) >> 5] = m;
                 if (m) {
-                    unsigned long long base = 0;
-                    if (lane == 0) base = atomicAdd(counter, (unsigned long long)__popc(m));
-                    base = __shfl_sync(0xffffffffu, base, 0);
+                    if (nbuf + 32 > MZ_BUF) flush();
                     if (sel) {
-                        unsigned long long pos = (unsigned long long)(off + p);
-                        unsigned long long slot = base + __popc(m & ((1u << lane) - 1u));
-                        if (slot < cap)
-                            out[slot] = ((unsigned long long)rcq_index_key(h) << 32) | (pos << 1) | so[wib][i + H];
-                        atomicOr(selmap + (pos >> 5), 1u << (pos & 31));
+                        const uint32_t oo = so[wib][i + H];
+                        const int slot = nbuf + __popc(m & ((1u << lane) - 1u));
+                        be[wib][slot] = ((unsigned long long)rcq_index_key(h) << 32) |
+                                        ((unsigned long long)(off + p) << 1) | (oo & 1u);
+                        bc[wib][slot] = flank_ctx(fwd, mask, off, p, n, oo & 1u, oo >> 1);
                     }
+                    nbuf += __popc(m);
                 }
             }
         }
     }
+    flush();
 }
 
 // blk2tx / ol tables: warp per transcript
@@ -211,25 +261,26 @@ __global__ void k_build_dir(const uint64_t* __restrict__ index, int64_t n, uint3
     for (uint32_t b = lo; b <= hi; b++) dir[b] = (uint32_t)i;
 }
 
-static int sort_u64(rcq_ctx* ctx, uint64_t* keys, int64_t n, int begin_bit = 0) {
+// index entries sorted by key (bits 32..63) with their flank contexts as payload
+static int sort_index(rcq_ctx* ctx, uint64_t** keys, uint64_t** vals, int64_t n) {
     if (n <= 1) return 0;
-    uint64_t* tmp = nullptr;
-    RC(dalloc(ctx, &tmp, n));
-    cub::DoubleBuffer<uint64_t> db(keys, tmp);
+    uint64_t *k2 = nullptr, *v2 = nullptr;
+    RC(dalloc(ctx, &k2, n));
+    RC(dalloc(ctx, &v2, n));
+    cub::DoubleBuffer<uint64_t> dk(*keys, k2), dv(*vals, v2);
     size_t bytes = 0;
-    CU(cub::DeviceRadixSort::SortKeys(nullptr, bytes, db, (int)n, begin_bit, 64, ctx->stream));
+    CU(cub::DeviceRadixSort::SortPairs(nullptr, bytes, dk, dv, (int)n, 32, 64, ctx->stream));
     void* ws = nullptr;
     CU(cudaMallocAsync(&ws, bytes, ctx->stream));
-    CU(cub::DeviceRadixSort::SortKeys(ws, bytes, db, (int)n, begin_bit, 64, ctx->stream));
-    ctx->launches += (64 - begin_bit) / 8 + 1;
-    if (db.Current() != keys)
-        CU(cudaMemcpyAsync(keys, db.Current(), n * sizeof(uint64_t), cudaMemcpyDeviceToDevice,
-                           ctx->stream));
+    CU(cub::DeviceRadixSort::SortPairs(ws, bytes, dk, dv, (int)n, 32, 64, ctx->stream));
+    ctx->launches += 32 / 8 + 1;
     cudaFreeAsync(ws, ctx->stream);
-    dfree(ctx, tmp);
+    uint64_t *ko = dk.Current(), *vo = dv.Current();
+    dfree(ctx, ko == *keys ? k2 : *keys);
+    dfree(ctx, vo == *vals ? v2 : *vals);
+    *keys = ko; *vals = vo;
     return 0;
 }
-int rcq_sort_u64(rcq_ctx* ctx, uint64_t* keys, int64_t n) { return sort_u64(ctx, keys, n); }
 
 // Pack + reverse complement + minimizer index for one sample (stream-ordered).
 int rcq_sample_build(rcq_ctx* ctx, rcq_sample* s, const uint8_t* d_ascii, int64_t ascii_len,
@@ -264,21 +315,23 @@ int rcq_sample_build(rcq_ctx* ctx, rcq_sample* s, const uint8_t* d_ascii, int64_
     int64_t cap = s->total / 5 + 4096;
     for (int attempt = 0; attempt < 2; attempt++) {
         RC(dalloc(ctx, &s->index, cap));
+        RC(dalloc(ctx, &s->fctx, cap));
         CU(cudaMemsetAsync(ctr + 1, 0, sizeof(unsigned long long), ctx->stream));
         if (s->n_seq)
-            LAUNCH(ctx, k_minimizers, blocks, 256, 0, s->fwd, s->mask, s->off, s->len, s->n_seq, ctr + 1, s->index,
-                   (unsigned long long)cap, s->sel);
+            LAUNCH(ctx, k_minimizers, blocks, 32 * MZ_WARPS, 0, s->fwd, s->mask, s->off, s->len, s->n_seq, ctr + 1,
+                   s->index, s->fctx, (unsigned long long)cap, s->sel);
         CU(cudaMemcpyAsync(ctx->h_pin, ctr, 2 * sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
         CU(cudaStreamSynchronize(ctx->stream));
         s->n_masked = ctx->h_pin[0];
         s->n_index = ctx->h_pin[1];
         if (s->n_index <= cap) break;
         dfree(ctx, s->index); s->index = nullptr;
+        dfree(ctx, s->fctx); s->fctx = nullptr;
         cap = s->n_index;
     }
     // sorted by key only (bits 32..63): entries of one key stay in append order, which no result
     // depends on (seeds are re-sorted by transcript and diagonal)
-    if (s->n_index) RC(sort_u64(ctx, s->index, s->n_index, 32));
+    if (s->n_index) RC(sort_index(ctx, &s->index, &s->fctx, s->n_index));
     LAUNCH(ctx, k_build_dir, grid_for(s->n_index + 1, 256), 256, 0, s->index, s->n_index, s->dir);
     return 0;
 }

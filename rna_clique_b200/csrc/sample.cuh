@@ -10,6 +10,8 @@
 //   index[n_index]  uint64  sorted minimizer entries  key<<32 | pos<<1 | orient, key = a second
 //                   bijective mix of the canonical 16-mer hash: minimizer hashes crowd towards 0, the
 //                   remix spreads them evenly over the directory buckets
+//   fctx[n_index]   uint64  flank context of each entry: the 13 bases before / after the 16-mer on its
+//                   canonical strand (low / high word; bit 31 = unavailable, bit 30 low = palindrome)
 //   dir[2^DIRBITS+1] uint32 first index entry of each hash-prefix bucket
 //   sel[arena/32]   uint32  bitmap of indexed positions;  gidx[n_seq] dense gene index
 //   blk2tx[arena/32] int32  transcript owning each 32-base block (transcripts start on block
@@ -30,6 +32,7 @@ struct rcq_sample {
     uint32_t *fwd = nullptr, *rc = nullptr, *mask = nullptr, *mask_rc = nullptr;
     int32_t *off = nullptr, *len = nullptr, *gene = nullptr, *iso = nullptr;
     uint64_t* index = nullptr;
+    uint64_t* fctx = nullptr;  // flank context of index[i] (sample.cu: flank_ctx)
     uint32_t* dir = nullptr;
     uint32_t* sel = nullptr;   // arena/32 words: bit p set = position p holds an index entry
     int32_t* gidx = nullptr;   // dense index of gene[t] among the sample's sorted distinct genes

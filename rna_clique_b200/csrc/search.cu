@@ -34,6 +34,12 @@ static int sort_pairs_u64_u32(rcq_ctx* ctx, uint64_t** keys, uint32_t** vals, in
     return 0;
 }
 
+static inline int bits_for(int64_t n) {  // bits needed to hold values 0 .. n-1 (at least 1)
+    int b = 1;
+    while ((1ll << b) < n) b++;
+    return b;
+}
+
 static int read_counters(rcq_ctx* ctx, int n) {
     CU(cudaMemcpyAsync(ctx->h_pin, ctx->d_ctr, n * sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
@@ -67,25 +73,28 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
     Seed* seeds = nullptr;
     uint2* cand = nullptr;
     int64_t n_seeds = 0, cap = std::max<int64_t>(1 << 20, 48ll * std::max(s1->n_seq, s2->n_seq));
-    int64_t ccap = std::max<int64_t>(1 << 20, 2 * s1->n_index);
+    int64_t ccap = std::max<int64_t>(1 << 20, s1->n_index / 2);
     for (int attempt = 0; attempt < 3 && s1->n_index && s2->n_index; attempt++) {
         RC(dalloc(ctx, &seeds, cap));
         RC(dalloc(ctx, &cand, ccap));
         CU(cudaMemsetAsync(ctr, 0, 16 * sizeof(int64_t), ctx->stream));
         stage_tic(ctx, 1);
-        LAUNCH(ctx, k_seed_probe, grid_for(s1->n_index, 256), 256, 0, s1->index, s1->n_index, s2->index,
-               s2->dir, cand, ccap, ctr);
+        stage_tic(ctx, 7);
+        LAUNCH(ctx, k_seed_probe, grid_for(s1->n_index, 256), 256, 0, s1->index, s1->fctx, s1->n_index, s2->index,
+               s2->fctx, s2->dir, cand, ccap, ctr);
+        stage_toc(ctx, 7);
         LAUNCH(ctx, k_seed_verify, RCQ_SMS * 16, 256, 0, cand, ccap, P, seeds, cap, ctr);
         stage_toc(ctx, 1);
-        RC(read_counters(ctx, 2));
+        RC(read_counters(ctx, 3));
         stage_collect(ctx);
         n_seeds = ctx->h_pin[0];
-        st.n_candidates = ctx->h_pin[1];
+        st.n_verified = ctx->h_pin[1];
+        st.n_candidates = ctx->h_pin[2];
         dfree(ctx, cand); cand = nullptr;
-        if (n_seeds <= cap && st.n_candidates <= ccap) break;
+        if (n_seeds <= cap && st.n_verified <= ccap) break;
         dfree(ctx, seeds); seeds = nullptr;
         cap = std::max(cap, n_seeds);
-        ccap = std::max(ccap, st.n_candidates);
+        ccap = std::max(ccap, st.n_verified);
         n_seeds = 0;
     }
     st.n_seeds = n_seeds;
@@ -106,9 +115,14 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
         RC(dalloc(ctx, &order, n_seeds));
         RC(dalloc(ctx, &heads, n_seeds));
         RC(dalloc(ctx, &dheads, n_seeds));
-        LAUNCH(ctx, k_seed_keys, grid_for(n_seeds, 256), 256, 0, seeds, n_seeds, keys, order);
-        RC(sort_pairs_u64_u32(ctx, &keys, &order, n_seeds, 64));
-        LAUNCH(ctx, k_seed_heads, grid_for(n_seeds, 256), 256, 0, keys, n_seeds, dheads, heads, ctr);
+        KeyFmt F;
+        F.bias = s1->max_len;
+        F.d_bits = bits_for((int64_t)s1->max_len + s2->max_len + 1);
+        F.tb_bits = bits_for(s2->n_seq);
+        F.total_bits = F.d_bits + 1 + F.tb_bits + bits_for(s1->n_seq);
+        LAUNCH(ctx, k_seed_keys, grid_for(n_seeds, 256), 256, 0, seeds, n_seeds, F, keys, order);
+        RC(sort_pairs_u64_u32(ctx, &keys, &order, n_seeds, F.total_bits));
+        LAUNCH(ctx, k_seed_heads, grid_for(n_seeds, 256), 256, 0, keys, n_seeds, F, dheads, heads, ctr);
         stage_toc(ctx, 3);
         RC(read_counters(ctx, 7));
         stage_collect(ctx);
@@ -132,7 +146,7 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
         RC(dalloc(ctx, &scratch, per_warp * blocks * (threads / 32)));
         CU(cudaMemsetAsync(ctr, 0, 16 * sizeof(int64_t), ctx->stream));
         stage_tic(ctx, 4);
-        LAUNCH(ctx, k_gapped, blocks, threads, 0, U, keys, n_seeds, heads, n_groups, P, G, scratch, per_warp, ctr);
+        LAUNCH(ctx, k_gapped, blocks, threads, 0, U, keys, n_seeds, F, heads, n_groups, P, G, scratch, per_warp, ctr);
         stage_toc(ctx, 4);
         dfree(ctx, scratch); dfree(ctx, U); dfree(ctx, keys); dfree(ctx, heads);
         // ---- compact (stable: group order, then processing order inside the group)

@@ -54,43 +54,74 @@ __device__ __forceinline__ int32_t run_back(const SeqArena& A, int64_t pa, const
 
 // ---- phase 1: probe.  Thread per index entry of A; both indexes are sorted by the same key, so
 // neighbouring threads read neighbouring directory buckets and entries of B (coalesced, L2
-// friendly).  Every key match becomes a candidate (entry of A, entry of B), written with one
-// atomic per warp.  counters[1] = #candidates (may exceed cap: the host re-runs with a larger list).
+// friendly).  A key match whose incoming 13-base flanks are equal in both samples lies >= 13 bases
+// inside a shared exact run, which always holds an earlier joint anchor (see k_seed_verify): it
+// is dropped here from the 8-byte flank contexts alone (≈ 90 % of all key matches between
+// orthologs), so only run starts and chance matches reach the sequence-touching verify kernel.
+// Survivors become candidates (entry of A, entry of B), appended with one atomic per BLOCK.
+// counters[1] = #candidates (may exceed cap: the host re-runs with a larger list),
+// counters[2] = #key matches examined.
+__device__ __forceinline__ bool probe_keep(uint64_t cb, uint32_t oA, uint32_t want, bool usable) {
+    const uint32_t other = oA ? (uint32_t)(cb >> 32) : ((uint32_t)cb & 0xBFFFFFFFu);
+    return !(usable && other == want);
+}
 __global__ void __launch_bounds__(256) k_seed_probe(
-    const uint64_t* __restrict__ idxA, int64_t nIdxA, const uint64_t* __restrict__ idxB,
-    const uint32_t* __restrict__ dirB, uint2* __restrict__ cand, int64_t cap,
-    unsigned long long* __restrict__ counters) {
-    const int lane = threadIdx.x & 31;
-    int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t first = 0, cnt = 0, lowA = 0;
+    const uint64_t* __restrict__ idxA, const uint64_t* __restrict__ ctxA, int64_t nIdxA,
+    const uint64_t* __restrict__ idxB, const uint64_t* __restrict__ ctxB, const uint32_t* __restrict__ dirB,
+    uint2* __restrict__ cand, int64_t cap, unsigned long long* __restrict__ counters) {
+    __shared__ uint32_t wsum[8], wseen[8];
+    __shared__ unsigned long long bbase;
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t first = 0, last = 0, cnt = 0, lowA = 0, key = 0, oA = 0, want = 0, seen = 0;
+    bool usable = false;
     if (e < nIdxA) {
-        uint64_t ka = __ldg(idxA + e);
-        uint32_t key = (uint32_t)(ka >> 32);
+        const uint64_t ka = __ldg(idxA + e), ca = __ldg(ctxA + e);
+        key = (uint32_t)(ka >> 32);
         lowA = (uint32_t)ka;
-        uint32_t b = key >> (32 - RCQ_DIRBITS);
-        uint32_t lo = __ldg(dirB + b), hi = __ldg(dirB + b + 1);
+        oA = lowA & 1u;
+        want = oA ? (uint32_t)(ca >> 32) : ((uint32_t)ca & 0xBFFFFFFFu);
+        usable = !(want >> 31) && !((uint32_t)ca & 0x40000000u);
+        const uint32_t b = key >> (32 - RCQ_DIRBITS);
+        const uint32_t lo = __ldg(dirB + b), hi = __ldg(dirB + b + 1);
         for (uint32_t k = lo; k < hi; k++) {
-            uint32_t kb = (uint32_t)(__ldg(idxB + k) >> 32);
+            const uint32_t kb = (uint32_t)(__ldg(idxB + k) >> 32);
             if (kb < key) continue;
             if (kb > key) break;
+            seen++;
+            if (!probe_keep(__ldg(ctxB + k), oA, want, usable)) continue;
             if (!cnt) first = k;
+            last = k;
             cnt++;
         }
     }
-    // warp prefix sum of cnt
+    // block exclusive scan of cnt
     uint32_t incl = cnt;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
         uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
         if (lane >= o) incl += v;
     }
-    uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
-    if (!total) return;
-    unsigned long long base = 0;
-    if (lane == 31) base = atomicAdd(counters + 1, (unsigned long long)total);
-    base = __shfl_sync(0xffffffffu, base, 31) + (incl - cnt);
-    for (uint32_t c = 0; c < cnt; c++)
-        if ((int64_t)(base + c) < cap) cand[base + c] = make_uint2(lowA, (uint32_t)__ldg(idxB + first + c));
+    for (int o = 16; o; o >>= 1) seen += __shfl_down_sync(0xffffffffu, seen, o);
+    if (lane == 31) wsum[wib] = incl;
+    if (lane == 0) wseen[wib] = seen;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t tot = 0, sn = 0;
+        for (int w = 0; w < 8; w++) { uint32_t v = wsum[w]; wsum[w] = tot; tot += v; sn += wseen[w]; }
+        bbase = tot ? atomicAdd(counters + 1, (unsigned long long)tot) : 0ull;
+        if (sn) atomicAdd(counters + 2, (unsigned long long)sn);
+    }
+    __syncthreads();
+    if (!cnt) return;
+    unsigned long long slot = bbase + wsum[wib] + (incl - cnt);
+    for (uint32_t k = first; k <= last; k++) {
+        const uint64_t eb = __ldg(idxB + k);
+        if ((uint32_t)(eb >> 32) != key) continue;
+        if (!probe_keep(__ldg(ctxB + k), oA, want, usable)) continue;
+        if ((int64_t)slot < cap) cand[slot] = make_uint2(lowA, (uint32_t)eb);
+        slot++;
+    }
 }
 
 // ---- phase 2: verify.  Thread per candidate (grid-stride).  A candidate survives when the two
@@ -245,24 +276,26 @@ __device__ __forceinline__ Ungapped ungapped_one(const Seed& s, const PairView& 
 
 // sort key of a seed: (ta, tb, strand, diagonal); seeds of one diagonal end up adjacent, and so do
 // the diagonals of one (ta, tb, strand) group
-#define RCQ_DIAG_BITS 21
-__global__ void k_seed_keys(const Seed* __restrict__ seeds, int64_t n, uint64_t* __restrict__ keys,
+// The key is packed to the bit widths this pair needs (KeyFmt), so the radix sort runs over
+// ~46 bits instead of 64: [ta | tb (tb_bits) | strand (1) | diag + bias (d_bits)].
+struct KeyFmt { int32_t d_bits, tb_bits, bias, total_bits; };
+__global__ void k_seed_keys(const Seed* __restrict__ seeds, int64_t n, KeyFmt F, uint64_t* __restrict__ keys,
                             uint32_t* __restrict__ vals) {
     int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= n) return;
     const Seed s = seeds[e];
-    keys[e] = ((uint64_t)(uint32_t)s.ta << 43) | ((uint64_t)(uint32_t)s.tb << 22) | ((uint64_t)s.minus << 21) |
-              (uint64_t)(uint32_t)(s.diag + (1 << 20));
+    keys[e] = ((((((uint64_t)(uint32_t)s.ta << F.tb_bits) | (uint64_t)(uint32_t)s.tb) << 1) | (uint64_t)s.minus) << F.d_bits) |
+              (uint64_t)(uint32_t)(s.diag + F.bias);
     vals[e] = (uint32_t)e;
 }
 // heads of diagonals and of (ta, tb, strand) groups in the sorted order (list order is irrelevant)
-__global__ void k_seed_heads(const uint64_t* __restrict__ keys, int64_t n, uint32_t* __restrict__ dheads,
+__global__ void k_seed_heads(const uint64_t* __restrict__ keys, int64_t n, KeyFmt F, uint32_t* __restrict__ dheads,
                              uint32_t* __restrict__ gheads, unsigned long long* __restrict__ counters /* [5]=groups [6]=diagonals */) {
     int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= n) return;
     const uint64_t k = keys[e], kp = e ? keys[e - 1] : ~k;
     if (k != kp) dheads[atomicAdd(counters + 6, 1ull)] = (uint32_t)e;
-    if ((k >> RCQ_DIAG_BITS) != (kp >> RCQ_DIAG_BITS)) gheads[atomicAdd(counters + 5, 1ull)] = (uint32_t)e;
+    if ((k >> F.d_bits) != (kp >> F.d_bits)) gheads[atomicAdd(counters + 5, 1ull)] = (uint32_t)e;
 }
 // BLAST's diagonal rule, thread per diagonal: seeds in ascending position; a seed that starts inside
 // the ungapped HSP extended from an earlier seed of the diagonal is skipped.  U is indexed like the
