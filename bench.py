@@ -31,7 +31,7 @@ SMS = 148
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--taxa", type=int, default=10)
@@ -41,6 +41,7 @@ def parse_args():
     ap.add_argument("--cpu-sample", type=int, default=600, help="top-gene transcripts per sample in the CPU legs")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--streams", type=int, default=3, help="CUDA streams (host threads) per GPU")
+    ap.add_argument("--clock-interval", type=float, default=0.05, help="seconds between nvidia-smi/NVML clock samples (0 = off)")
     return ap.parse_args()
 
 
@@ -56,8 +57,9 @@ def equiv_cells(lengths):
 
 
 class ClockSampler(threading.Thread):
-    def __init__(self, device):
+    def __init__(self, device, interval=0.05):
         super().__init__(daemon=True)
+        self.interval = interval
         self.device, self.samples, self.reasons, self.stop_flag, self.max_mhz = device, [], set(), False, None
 
     def run(self):
@@ -76,7 +78,7 @@ class ClockSampler(threading.Thread):
                 for bit, n in names.items():
                     if r & bit:
                         self.reasons.add(n)
-                time.sleep(0.05)
+                time.sleep(self.interval)
         except Exception as e:  # noqa: BLE001
             self.reasons.add(f"nvml_unavailable:{type(e).__name__}")
 
@@ -230,12 +232,14 @@ def main():
             ms = float(t.item())
         return ms / steps, out, eng.stage_times(reset=True), (eng.launches - l0) / steps
 
-    sampler = ClockSampler(local)
-    sampler.start()
+    sampler = ClockSampler(local, a.clock_interval or 0.05)
+    if a.clock_interval > 0:
+        sampler.start()
     ms_dev, res, stages, launches = timed(lambda: eng.all_vs_all(resident, labels, None, dist=dist), a.steps, a.warmup)
     ms_e2e, res2, _, _ = timed(lambda: eng.all_vs_all(host, labels, a.top, dist=dist), a.steps, 1)
     sampler.stop_flag = True
-    sampler.join(timeout=2)
+    if a.clock_interval > 0:
+        sampler.join(timeout=2)
     assert np.array_equal(res["matrix"], res2["matrix"])
 
     lengths = res["lengths"]

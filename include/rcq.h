@@ -101,6 +101,9 @@ void rcq_table_free(rcq_table* t);
  * tx1, tx2, minus, q0, q1, s0, s1 (0-based half-open, s on the strand given), score2 (doubled
  * score), mismatch, gaps, gapopen, nident.  Returns the count; copies min(count, cap) rows. */
 int64_t rcq_debug_last_hsps(rcq_ctx* ctx, int32_t* out, int64_t cap);
+/* the HSP set is kept only after rcq_debug_keep_hsps(ctx, 1) (off by default: it costs a device-wide
+ * allocation per search) */
+void rcq_debug_keep_hsps(rcq_ctx* ctx, int on);
 /* Karlin-Altschul helpers shared by the host layer (blastn 1/-2 linear-gap parameters):
  * length adjustment and evalue of a raw score for query length m against a db (n bases, nseq). */
 int32_t rcq_length_adjustment(int64_t m, int64_t n, int64_t nseq);

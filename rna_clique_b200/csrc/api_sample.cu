@@ -24,10 +24,18 @@ int rcq_ctx_create(int device, rcq_ctx** out) {
     CU(cudaMallocHost((void**)&c->h_pin, 64 * sizeof(int64_t)));
     CU(cudaMalloc((void**)&c->d_ctr, 64 * sizeof(int64_t)));
     for (int i = 0; i < 16; i++) CU(cudaEventCreate(&c->ev[i]));
-    cudaMemPool_t pool;
-    CU(cudaDeviceGetDefaultMemPool(&pool, device));
+    // one explicit pool per context: blocks freed on this stream are reused by this stream at once;
+    // with the device's default pool a block freed on another stream forces a fresh (slow, device-wide)
+    // physical allocation whenever that stream has not caught up yet
+    cudaMemPoolProps props;
+    memset(&props, 0, sizeof props);
+    props.allocType = cudaMemAllocationTypePinned;
+    props.handleTypes = cudaMemHandleTypeNone;
+    props.location.type = cudaMemLocationTypeDevice;
+    props.location.id = device;
+    CU(cudaMemPoolCreate(&c->pool, &props));
     uint64_t thr = UINT64_MAX;  // keep freed blocks in the pool: no OS round trips per pair
-    CU(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
+    CU(cudaMemPoolSetAttribute(c->pool, cudaMemPoolAttrReleaseThreshold, &thr));
     *out = c;
     return 0;
 }
@@ -37,10 +45,13 @@ void rcq_ctx_destroy(rcq_ctx* c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     if (c->dbg_hsp) cudaFree(c->dbg_hsp);
+    if (c->gs_rows) cudaFree(c->gs_rows);
+    if (c->gs_locks) cudaFree(c->gs_locks);
     for (int i = 0; i < 16; i++) cudaEventDestroy(c->ev[i]);
     cudaFreeHost(c->h_pin);
     cudaFree(c->d_ctr);
     cudaStreamDestroy(c->stream);
+    if (c->pool) cudaMemPoolDestroy(c->pool);
     delete c;
 }
 

@@ -39,6 +39,7 @@ static inline int rcq_fail(int code, const char* fmt, const char* a = "", const 
 struct rcq_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
+    cudaMemPool_t pool = nullptr;   // this context's own stream-ordered pool (no cross-stream reuse stalls)
     int64_t launches = 0;
     // pinned staging for small device->host result reads
     int64_t* h_pin = nullptr;  // 64 int64
@@ -46,6 +47,12 @@ struct rcq_ctx {
     // debug: gapped HSPs of the last search (device, 12 int32 each)
     int32_t* dbg_hsp = nullptr;
     int64_t dbg_n = 0;
+    int dbg_keep = 0;
+    // fallback rows of the gapped kernel (search.cu: scratch_pool)
+    int32_t* gs_rows = nullptr;
+    unsigned int* gs_locks = nullptr;
+    int64_t gs_per_slot = 0;
+    int32_t gs_slots = 0;
     // per-stage device time (CUDA events on this stream), accumulated across calls:
     // 0 pack+index, 1 seed join, 2 ungapped, 3 sort/group, 4 gapped DP, 5 selection+table, 6 phase 2
     double stage_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -73,7 +80,7 @@ static inline void stage_collect(rcq_ctx* c) {
 template <typename T>
 static inline int dalloc(rcq_ctx* c, T** p, int64_t n) {
     if (n < 1) n = 1;
-    CU(cudaMallocAsync((void**)p, (size_t)n * sizeof(T), c->stream));
+    CU(cudaMallocFromPoolAsync((void**)p, (size_t)n * sizeof(T), c->pool, c->stream));
     return 0;
 }
 template <typename T>

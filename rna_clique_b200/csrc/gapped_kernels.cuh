@@ -166,14 +166,187 @@ __device__ bool greedy_extend(const SeqArena Q, int64_t qpos, int32_t qn, const 
     return true;
 }
 
-// ---- one extension: shared-memory ring first, global rows when a wave outgrows it ------------
-__device__ __forceinline__ void extend(const SeqArena Q, int64_t qpos, int32_t qn, const SeqArena S,
-                                       int64_t spos, int32_t sn, int32_t* ring, int32_t* scratch, ExtRes* r,
-                                       unsigned long long* steps, unsigned long long* retries) {
-    if (!greedy_extend<true>(Q, qpos, qn, S, spos, sn, ring, RCQ_RING, r, steps)) {
-        if ((threadIdx.x & 31) == 0) (*retries)++;
+// ---- fast path for samples without masked bases (no N): same recurrence, fewer instructions ----
+// 16 bases per first slide step from two 32-bit words (one funnel shift, no 64-bit compress), 32-bit
+// offsets from per-extension base pointers, dead cells stored as NEG with two sentinels either side
+// of every wave so the three-way max needs no range checks.
+__device__ __forceinline__ uint32_t fetch16(const uint32_t* __restrict__ b, int32_t x) {
+    const int32_t w = x >> 4;
+    return __funnelshift_r(__ldg(b + w), __ldg(b + w + 1), (x & 15) * 2);
+}
+__device__ __forceinline__ int32_t run16(const uint32_t* __restrict__ Qb, int32_t xq,
+                                         const uint32_t* __restrict__ Sb, int32_t xs) {
+    uint32_t d = fetch16(Qb, xq) ^ fetch16(Sb, xs);
+    d = (d | (d >> 1)) & 0x55555555u;
+    return d ? ((__ffs(d) - 1) >> 1) : 16;
+}
+__device__ __forceinline__ int32_t coop_slide16(const uint32_t* __restrict__ Qb, int32_t xq,
+                                                const uint32_t* __restrict__ Sb, int32_t xs, int32_t lim) {
+    const int lane = threadIdx.x & 31;
+    int32_t base = 0;
+    while (base < lim) {
+        const int32_t o = base + 16 * lane;
+        int32_t z = 0;
+        if (o < lim) z = min(run16(Qb, xq + o, Sb, xs + o), lim - o);
+        const unsigned stop = __ballot_sync(FULL, z < 16);
+        if (stop) {
+            const int src = __ffs(stop) - 1;
+            return base + 16 * src + __shfl_sync(FULL, z, src);
+        }
+        base += 512;
+    }
+    return lim;
+}
+
+// rows: 6 arrays of rowlen int32.  RING: index k & (RCQ_RING-1); else index k + qn + 2 (rowlen >= qn+sn+5).
+template <bool RING>
+__device__ bool greedy_fast(const uint32_t* __restrict__ Qb, int32_t qo, int32_t qn,
+                            const uint32_t* __restrict__ Sb, int32_t so, int32_t sn, int32_t* rows,
+                            int32_t rowlen, ExtRes* res, unsigned long long* steps) {
+    const int lane = threadIdx.x & 31;
+    int32_t* Rr = rows; int32_t* Mr = rows + 2 * rowlen; int32_t* Gr = rows + 4 * rowlen;
+#define IX(k) (RING ? ((k) & (RCQ_RING - 1)) : ((k) + qn + 2))
+    const int32_t i0 = coop_slide16(Qb, qo, Sb, so, min(qn, sn));
+    unsigned long long nstep = (lane == 0) ? (unsigned long long)(i0 + 1) : 0ull;
+    if (lane == 0) { Rr[IX(0)] = i0; Mr[IX(0)] = 0; Gr[IX(0)] = 0; }
+    if (lane >= 1 && lane <= 4) Rr[IX(lane <= 2 ? -lane : lane - 2)] = NEG;
+    int32_t bS = (lane == 0) ? 2 * i0 : NEG, bD = 0, bK = 0, bI = i0, bM = 0, bG = 0;
+    int32_t gb = 2 * i0;
+    int32_t Tl = (lane == 0) ? gb : 0;   // lane (d & 31) holds T[d]
+    int32_t Tprev = gb, L = 0, U = 0;
+    bool ok = true;
+    __syncwarp();
+    for (int32_t d = 1; d <= qn + sn; d++) {
+        const int32_t p = ((d - 1) & 1) * rowlen, c = (d & 1) * rowlen;
+        int32_t tref = __shfl_sync(FULL, Tl, (d - RCQ_XDROP_OFFSET) & 31);
+        if (d < RCQ_XDROP_OFFSET) tref = 0;
+        const int32_t klo = max(L - 1, -qn), khi = min(U + 1, sn);
+        if (RING && khi - klo + 5 > RCQ_RING) { ok = false; break; }
+        const int32_t xcut = tref - RCQ_XDROP_GAPPED2 + 6 * d;   // alive iff 2*row + k >= xcut
+        int32_t nL = 1 << 28, nU = -(1 << 28), wbest = NEG, ubmax = NEG;
+        for (int32_t kb = klo; kb <= khi; kb += 32) {
+            const int32_t k = kb + lane;
+            const bool active = k <= khi;
+            int32_t bi = NEG, op = 0, rowmax = 0, e = NEG, mm = 0, gw = 0, lim = 0;
+            bool cont = false;
+            if (active) {
+                rowmax = min(qn, sn - k);
+                int32_t c0 = Rr[p + IX(k)] + 1, c1 = Rr[p + IX(k + 1)] + 1, c2 = Rr[p + IX(k - 1)];
+                if (c0 > rowmax) c0 = NEG;
+                if (c1 > rowmax) c1 = NEG;
+                if (c2 > rowmax) c2 = NEG;
+                bi = c0;
+                if (c1 > bi) { bi = c1; op = 1; }
+                if (c2 > bi) { bi = c2; op = 2; }
+                if (2 * bi + k < xcut) bi = NEG;
+            }
+            if (bi >= 0) {
+                const int32_t src = k + (op == 1) - (op == 2);
+                mm = Mr[p + IX(src)];
+                const int32_t g = Gr[p + IX(src)];
+                if (op == 0) { mm++; gw = g & ~7; }
+                else gw = ((g & ~7) | op) + (1 << 17) + (((g & 7) != op) ? 8 : 0);
+                lim = rowmax - bi;
+                int32_t z = 0;
+                if (lim > 0) z = min(run16(Qb, qo + bi, Sb, so + bi + k), lim);
+                nstep += z + 1;
+                e = bi + z;
+                cont = (z == 16 && lim > 16);
+            }
+            unsigned more = __ballot_sync(FULL, cont);
+            while (more) {
+                const int sl = __ffs(more) - 1;
+                more &= more - 1;
+                const int32_t e2 = __shfl_sync(FULL, e, sl), k2 = __shfl_sync(FULL, k, sl), l2 = __shfl_sync(FULL, lim, sl);
+                const int32_t extra = coop_slide16(Qb, qo + e2, Sb, so + e2 + k2, l2 - 16);
+                if (lane == sl) { e += extra; nstep += extra; }
+            }
+            if (active) {
+                if (bi >= 0) {
+                    if (e > bi) gw |= 4;
+                    Rr[c + IX(k)] = e; Mr[c + IX(k)] = mm; Gr[c + IX(k)] = gw;
+                    const int32_t sc = 2 * e + k - 6 * d;
+                    wbest = max(wbest, sc);
+                    nL = min(nL, k); nU = max(nU, k);
+                    ubmax = max(ubmax, 2 * rowmax + k - 6 * d);
+                    if (sc > bS) { bS = sc; bD = d; bK = k; bI = e; bM = mm; bG = gw; }
+                } else {
+                    Rr[c + IX(k)] = NEG;
+                }
+            }
+        }
+        if (lane < 4) Rr[c + IX(lane < 2 ? klo - 1 - lane : khi + lane - 1)] = NEG;   // sentinels
+        wbest = __reduce_max_sync(FULL, wbest);
+        nL = __reduce_min_sync(FULL, nL);
+        nU = __reduce_max_sync(FULL, nU);
+        ubmax = __reduce_max_sync(FULL, ubmax);
+        Tprev = max(Tprev, wbest);
+        if (lane == (d & 31)) Tl = Tprev;
+        gb = max(gb, wbest);
+        L = nL; U = nU;
         __syncwarp();
-        greedy_extend<false>(Q, qpos, qn, S, spos, sn, scratch, qn + sn + 3, r, steps);
+        if (L > U) break;
+        if (ubmax <= gb) break;      // nothing still alive can beat the best end point
+    }
+#undef IX
+    for (int o = 16; o; o >>= 1) nstep += __shfl_down_sync(FULL, nstep, o);
+    if (lane == 0) *steps += nstep;
+    if (!ok) return false;
+    uint64_t key = 0;
+    if (bS > NEG)
+        key = ((uint64_t)(uint32_t)(bS + (1 << 20)) << 42) | ((uint64_t)((1 << 21) - 1 - bD) << 21) |
+              (uint64_t)((1 << 21) - 1 - (bK + (1 << 20)));
+    uint64_t best = key;
+    for (int o = 16; o; o >>= 1) { uint64_t x = __shfl_xor_sync(FULL, best, o); if (x > best) best = x; }
+    const int src = __ffs(__ballot_sync(FULL, key == best)) - 1;
+    res->score2 = __shfl_sync(FULL, bS, src);
+    res->qi = __shfl_sync(FULL, bI, src);
+    res->sj = res->qi + __shfl_sync(FULL, bK, src);
+    res->mism = __shfl_sync(FULL, bM, src);
+    res->gw = __shfl_sync(FULL, bG, src);
+    return true;
+}
+
+// ---- one extension: shared-memory ring first; a wave that outgrows the ring re-runs the extension
+// on global rows.  Those rows come from a small pool of slots shared by all warps (try-lock per
+// slot; a holder never waits on anything, so the spin cannot deadlock) instead of one private
+// region per resident warp, which cost 0.5 GB per search for a path almost never taken.
+struct ScratchPool { int32_t* rows; int64_t per_slot; unsigned int* locks; int32_t n_slots; };
+
+__device__ __forceinline__ int32_t scratch_acquire(const ScratchPool& sp) {
+    int32_t s = 0;
+    if ((threadIdx.x & 31) == 0) {
+        s = (int32_t)(((blockIdx.x * blockDim.x + threadIdx.x) >> 5) % sp.n_slots);
+        while (atomicCAS(sp.locks + s, 0u, 1u) != 0u) s = (s + 1 == sp.n_slots) ? 0 : s + 1;
+    }
+    return __shfl_sync(FULL, s, 0);
+}
+__device__ __forceinline__ void scratch_release(const ScratchPool& sp, int32_t s) {
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) { __threadfence(); atomicExch(sp.locks + s, 0u); }
+}
+
+template <bool MASKED>
+__device__ __forceinline__ void extend(const SeqArena Q, int64_t qpos, int32_t qn, const SeqArena S,
+                                       int64_t spos, int32_t sn, int32_t* ring, const ScratchPool& sp, ExtRes* r,
+                                       unsigned long long* steps, unsigned long long* retries) {
+    if (MASKED) {
+        if (!greedy_extend<true>(Q, qpos, qn, S, spos, sn, ring, RCQ_RING, r, steps)) {
+            if ((threadIdx.x & 31) == 0) (*retries)++;
+            const int32_t slot = scratch_acquire(sp);
+            greedy_extend<false>(Q, qpos, qn, S, spos, sn, sp.rows + slot * sp.per_slot, qn + sn + 3, r, steps);
+            scratch_release(sp, slot);
+        }
+    } else {
+        const uint32_t* Qb = Q.bits + (qpos >> 4);
+        const uint32_t* Sb = S.bits + (spos >> 4);
+        const int32_t qo = (int32_t)(qpos & 15), so = (int32_t)(spos & 15);
+        if (!greedy_fast<true>(Qb, qo, qn, Sb, so, sn, ring, RCQ_RING, r, steps)) {
+            if ((threadIdx.x & 31) == 0) (*retries)++;
+            const int32_t slot = scratch_acquire(sp);
+            greedy_fast<false>(Qb, qo, qn, Sb, so, sn, sp.rows + slot * sp.per_slot, qn + sn + 5, r, steps);
+            scratch_release(sp, slot);
+        }
     }
     __syncwarp();
 }
@@ -192,15 +365,13 @@ __device__ __forceinline__ bool ung_before(const Ungapped& x, const Ungapped& y)
 // to out[head .. head+count), the remaining slots of its range keep ta = -1.
 // U is indexed like the sorted seed list (slots of seeds the diagonal rule skipped have score < 0);
 // keys[] are the seed sort keys (KeyFmt): group = key >> d_bits.
+template <bool MASKED>
 __global__ void __launch_bounds__(128) k_gapped(const Ungapped* __restrict__ U,
                                                 const uint64_t* __restrict__ keys, int64_t n, KeyFmt F,
                                                 const uint32_t* __restrict__ heads, int64_t n_groups,
-                                                PairView P, Gapped* __restrict__ out,
-                                                int32_t* __restrict__ scratch, int64_t scratch_per_warp,
+                                                PairView P, Gapped* __restrict__ out, ScratchPool sp,
                                                 unsigned long long* __restrict__ ctr /* [0]=next group [1]=cells [2]=retries [3]=n gapped */) {
     const int lane = threadIdx.x & 31;
-    const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    int32_t* my_scratch = scratch + (int64_t)warp_global * scratch_per_warp;
     __shared__ int32_t ring_all[4][6 * RCQ_RING];
     int32_t* ring = ring_all[threadIdx.x >> 5];
     unsigned long long cells = 0, retries = 0, produced = 0;
@@ -253,8 +424,8 @@ __global__ void __launch_bounds__(128) k_gapped(const Ungapped* __restrict__ U,
             if (__any_sync(FULL, contained)) continue;
             const int32_t i0 = cur.i0, j0 = i0 + cur.diag;
             ExtRes L, R;
-            extend(P.Ar, oa + (la - 1 - i0), i0 + 1, Bo, ob + (lb - 1 - j0), j0 + 1, ring, my_scratch, &L, &cells, &retries);
-            extend(P.Af, oa + i0 + 1, la - i0 - 1, Bs, ob + j0 + 1, lb - j0 - 1, ring, my_scratch, &R, &cells, &retries);
+            extend<MASKED>(P.Ar, oa + (la - 1 - i0), i0 + 1, Bo, ob + (lb - 1 - j0), j0 + 1, ring, sp, &L, &cells, &retries);
+            extend<MASKED>(P.Af, oa + i0 + 1, la - i0 - 1, Bs, ob + j0 + 1, lb - j0 - 1, ring, sp, &R, &cells, &retries);
             Gapped gp;
             gp.ta = ta; gp.tb = tb; gp.minus = minus;
             gp.a0 = i0 + 1 - L.qi; gp.a1 = i0 + 1 + R.qi;

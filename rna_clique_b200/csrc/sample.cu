@@ -271,7 +271,7 @@ static int sort_index(rcq_ctx* ctx, uint64_t** keys, uint64_t** vals, int64_t n)
     size_t bytes = 0;
     CU(cub::DeviceRadixSort::SortPairs(nullptr, bytes, dk, dv, (int)n, 32, 64, ctx->stream));
     void* ws = nullptr;
-    CU(cudaMallocAsync(&ws, bytes, ctx->stream));
+    CU(cudaMallocFromPoolAsync(&ws, bytes, ctx->pool, ctx->stream));
     CU(cub::DeviceRadixSort::SortPairs(ws, bytes, dk, dv, (int)n, 32, 64, ctx->stream));
     ctx->launches += 32 / 8 + 1;
     cudaFreeAsync(ws, ctx->stream);

@@ -23,7 +23,7 @@ static int sort_pairs_u64_u32(rcq_ctx* ctx, uint64_t** keys, uint32_t** vals, in
     size_t bytes = 0;
     CU(cub::DeviceRadixSort::SortPairs(nullptr, bytes, dk, dv, (int)n, 0, end_bit, ctx->stream));
     void* ws = nullptr;
-    CU(cudaMallocAsync(&ws, bytes, ctx->stream));
+    CU(cudaMallocFromPoolAsync(&ws, bytes, ctx->pool, ctx->stream));
     CU(cub::DeviceRadixSort::SortPairs(ws, bytes, dk, dv, (int)n, 0, end_bit, ctx->stream));
     ctx->launches += (end_bit + 7) / 8 + 1;
     cudaFreeAsync(ws, ctx->stream);
@@ -38,6 +38,26 @@ static inline int bits_for(int64_t n) {  // bits needed to hold values 0 .. n-1 
     int b = 1;
     while ((1ll << b) < n) b++;
     return b;
+}
+
+// Fallback rows of the gapped kernel: a pool of slots owned by the context, grown when a pair with
+// longer transcripts arrives (slots x rows of 6 * (max_len1 + max_len2 + 8) int32, at most ~1 GB).
+static int scratch_pool(rcq_ctx* ctx, int64_t per_slot, ScratchPool* sp) {
+    if (per_slot > ctx->gs_per_slot) {
+        int64_t n_slots = RCQ_SMS * 4;
+        while (n_slots > 16 && n_slots * per_slot * 4 > (1ll << 30)) n_slots /= 2;
+        CU(cudaStreamSynchronize(ctx->stream));
+        if (ctx->gs_rows) CU(cudaFree(ctx->gs_rows));
+        if (ctx->gs_locks) CU(cudaFree(ctx->gs_locks));
+        ctx->gs_rows = nullptr; ctx->gs_locks = nullptr; ctx->gs_per_slot = 0;
+        CU(cudaMalloc((void**)&ctx->gs_rows, (size_t)n_slots * per_slot * 4));
+        CU(cudaMalloc((void**)&ctx->gs_locks, (size_t)n_slots * sizeof(unsigned int)));
+        CU(cudaMemset(ctx->gs_locks, 0, (size_t)n_slots * sizeof(unsigned int)));
+        ctx->gs_per_slot = per_slot;
+        ctx->gs_slots = (int32_t)n_slots;
+    }
+    sp->rows = ctx->gs_rows; sp->per_slot = ctx->gs_per_slot; sp->locks = ctx->gs_locks; sp->n_slots = ctx->gs_slots;
+    return 0;
 }
 
 static int read_counters(rcq_ctx* ctx, int n) {
@@ -141,20 +161,22 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
         RC(dalloc(ctx, &G, n_seeds));
         CU(cudaMemsetAsync(G, 0xFF, n_seeds * sizeof(Gapped), ctx->stream));
         const int blocks = RCQ_SMS * 8, threads = 128;
-        int64_t per_warp = 6ll * ((int64_t)s1->max_len + s2->max_len + 8);
-        int32_t* scratch = nullptr;
-        RC(dalloc(ctx, &scratch, per_warp * blocks * (threads / 32)));
+        ScratchPool sp;
+        RC(scratch_pool(ctx, 6ll * ((int64_t)s1->max_len + s2->max_len + 8), &sp));
         CU(cudaMemsetAsync(ctr, 0, 16 * sizeof(int64_t), ctx->stream));
         stage_tic(ctx, 4);
-        LAUNCH(ctx, k_gapped, blocks, threads, 0, U, keys, n_seeds, F, heads, n_groups, P, G, scratch, per_warp, ctr);
+        if (s1->n_masked || s2->n_masked)
+            LAUNCH(ctx, k_gapped<true>, blocks, threads, 0, U, keys, n_seeds, F, heads, n_groups, P, G, sp, ctr);
+        else
+            LAUNCH(ctx, k_gapped<false>, blocks, threads, 0, U, keys, n_seeds, F, heads, n_groups, P, G, sp, ctr);
         stage_toc(ctx, 4);
-        dfree(ctx, scratch); dfree(ctx, U); dfree(ctx, keys); dfree(ctx, heads);
+        dfree(ctx, U); dfree(ctx, keys); dfree(ctx, heads);
         // ---- compact (stable: group order, then processing order inside the group)
         RC(dalloc(ctx, &Gd, n_seeds));
         size_t bytes = 0;
         CU(cub::DeviceSelect::If(nullptr, bytes, G, Gd, (int*)(ctr + 8), (int)n_seeds, GappedValid(), ctx->stream));
         void* ws = nullptr;
-        CU(cudaMallocAsync(&ws, bytes, ctx->stream));
+        CU(cudaMallocFromPoolAsync(&ws, bytes, ctx->pool, ctx->stream));
         CU(cub::DeviceSelect::If(ws, bytes, G, Gd, (int*)(ctr + 8), (int)n_seeds, GappedValid(), ctx->stream));
         ctx->launches += 2;
         cudaFreeAsync(ws, ctx->stream);
@@ -167,12 +189,15 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
     } else {
         dfree(ctx, seeds);
     }
-    // debug copy of the HSP list
-    if (ctx->dbg_hsp) { cudaFree(ctx->dbg_hsp); ctx->dbg_hsp = nullptr; }
-    ctx->dbg_n = n_gapped;
-    if (n_gapped) {
-        CU(cudaMalloc((void**)&ctx->dbg_hsp, n_gapped * sizeof(Gapped)));
-        CU(cudaMemcpyAsync(ctx->dbg_hsp, Gd, n_gapped * sizeof(Gapped), cudaMemcpyDeviceToDevice, ctx->stream));
+    // debug copy of the HSP list (test hook, off unless rcq_debug_keep_hsps(ctx, 1): cudaMalloc/cudaFree
+    // synchronise the whole device and would serialise the streams of the engine)
+    if (ctx->dbg_keep) {
+        if (ctx->dbg_hsp) { cudaFree(ctx->dbg_hsp); ctx->dbg_hsp = nullptr; }
+        ctx->dbg_n = n_gapped;
+        if (n_gapped) {
+            CU(cudaMalloc((void**)&ctx->dbg_hsp, n_gapped * sizeof(Gapped)));
+            CU(cudaMemcpyAsync(ctx->dbg_hsp, Gd, n_gapped * sizeof(Gapped), cudaMemcpyDeviceToDevice, ctx->stream));
+        }
     }
     if (n_gapped >= (1 << 22)) return rcq_fail(RCQ_ERR_CAPACITY, "rcq_search_pair: more than 2^22 gapped HSPs in one pair");
     // ---- selection + table
@@ -263,6 +288,10 @@ extern "C" int rcq_table_download(const rcq_table* t, rcq_table_cols* h) {
         if (h->reverse) h->reverse[r] = (uint8_t)buf[(size_t)RCQ_COL_REVERSE * t->n + r];
     }
     return 0;
+}
+
+extern "C" void rcq_debug_keep_hsps(rcq_ctx* ctx, int on) {
+    if (ctx) ctx->dbg_keep = on;
 }
 
 extern "C" int64_t rcq_debug_last_hsps(rcq_ctx* ctx, int32_t* out, int64_t cap) {

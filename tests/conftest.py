@@ -16,5 +16,6 @@ def pytest_configure(config):
 def ctx():
     from rna_clique_b200 import _native
     c = _native.Context(0)
+    _native.debug_keep_hsps(c)   # tests compare the gapped-HSP set itself with the oracle's
     yield c
     c.close()
