@@ -160,25 +160,32 @@ __device__ __forceinline__ uint64_t flank_ctx(const uint32_t* fwd, const uint32_
 
 // Window-minimizer selection (window = 13 consecutive 16-mers = one 28-mer).  Position p is
 // selected iff its hash equals the minimum of SOME window containing it (all tied minima are
-// kept, so the choice is symmetric under reverse complement).  Warp per transcript; selected
-// entries are staged in a per-warp shared-memory buffer and appended with ONE atomic per flush
-// (a single global counter serialises at ~1 atomic/ns, which bounded the per-step version).
-// The 32 positions of a warp step are one aligned word of the `sel` bitmap: plain store of the ballot.
+// kept, so the choice is symmetric under reverse complement); windows lie inside the transcript.
+//
+// Warp per transcript, tiles of 480 positions: lane l hashes the 16 word-aligned positions
+// [c - 16 + 16 l, +16) from four 2-bit words held in registers (lanes 0 and 31 are the halo of the
+// tile), parks the hashes in shared memory, reads back its 12 + 16 + 12 neighbourhood and decides
+// its 16 positions with two branch-free doubling passes in registers:
+//   w[t] = min of the 13 hashes of window t (0 for a window that leaves the transcript),
+//   sel  = max of the 13 windows containing p == hash(p).
+// Entries and their flank contexts (sample.cu: flank_ctx semantics) are staged in a per-warp
+// buffer and appended with one atomic per flush; two lanes' decisions form one aligned word of `sel`.
 // Entries past `cap` are counted but not written (the host then re-runs with the exact size).
-#define MZ_WARPS 8
-#define MZ_BUF 256
+#define MZ_WARPS 4
+#define MZ_BUF 576
+#define MZ_TILE 480
+#define MZ_STRIDE 20   // padded words per lane in the hash exchange buffer (bank-conflict-free LDS.128)
 __global__ void __launch_bounds__(32 * MZ_WARPS) k_minimizers(
     const uint32_t* __restrict__ fwd, const uint32_t* __restrict__ mask, const int32_t* __restrict__ aoff,
     const int32_t* __restrict__ len, int32_t n_seq, unsigned long long* __restrict__ counter,
     uint64_t* __restrict__ out, uint64_t* __restrict__ out_ctx, unsigned long long cap,
     uint32_t* __restrict__ selmap) {
-    __shared__ uint32_t sh[MZ_WARPS][256 + 8];
-    __shared__ uint8_t so[MZ_WARPS][256 + 8];
+    __shared__ __align__(16) uint32_t hx[MZ_WARPS][32 * MZ_STRIDE];
     __shared__ uint64_t be[MZ_WARPS][MZ_BUF], bc[MZ_WARPS][MZ_BUF];
     const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int warp = blockIdx.x * MZ_WARPS + wib;
     const int nwarps = gridDim.x * MZ_WARPS;
-    const int T = 224, H = RCQ_WIN - 1;  // tile and halo
+    const uint32_t M26 = 0x03FFFFFFu;
     int nbuf = 0;                        // warp-uniform fill of be/bc
     auto flush = [&]() {
         if (!nbuf) return;
@@ -196,44 +203,125 @@ __global__ void __launch_bounds__(32 * MZ_WARPS) k_minimizers(
         const int32_t n = len[t];
         const int32_t nk = n - RCQ_KMER + 1;
         if (nk < RCQ_WIN) continue;
-        for (int32_t c = 0; c < nk; c += T) {
-            __syncwarp();
-            for (int i = lane; i < T + 2 * H; i += 32) {
-                int32_t p = c - H + i;
-                uint32_t o = 0, pal = 0, h = 0xFFFFFFFFu;
-                if (p >= 0 && p < nk) h = kmer_hash(fwd, mask, off + p, &o, &pal);
-                sh[wib][i] = h;
-                so[wib][i] = (uint8_t)(o | (pal << 1));
+        for (int32_t c = 0; c < nk; c += MZ_TILE) {
+            const int32_t q0 = c - 16 + 16 * lane;          // first position of this lane (may be < 0 or >= nk)
+            // ---- bases [q0-16, q0+48) as four words, mask bits of the same span
+            uint32_t a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+            uint64_t M64 = ~0ull;
+            const bool live = q0 + 16 > 0 && q0 < nk;       // some position of the lane is a k-mer start
+            if (live) {
+                const int64_t w = (off + q0 - 16) >> 4;     // >= 2: the arena has a 64-base front guard
+                a0 = __ldg(fwd + w); a1 = __ldg(fwd + w + 1); a2 = __ldg(fwd + w + 2); a3 = __ldg(fwd + w + 3);
+                const int64_t mw = (off + q0 - 16) >> 5;
+                const uint32_t m0 = __ldg(mask + mw), m1 = __ldg(mask + mw + 1), m2 = __ldg(mask + mw + 2);
+                if ((off + q0 - 16) & 16) M64 = ((uint64_t)(m0 >> 16)) | ((uint64_t)m1 << 16) | ((uint64_t)m2 << 48);
+                else M64 = (uint64_t)m0 | ((uint64_t)m1 << 32);
+            }
+            // ---- 16 canonical hashes
+            uint32_t h[16];
+            uint32_t obits = 0, pbits = 0;
+#pragma unroll
+            for (int j = 0; j < 16; j++) {
+                const int32_t p = q0 + j;
+                const uint32_t f = __funnelshift_r(a1, a2, 2 * j);
+                const uint32_t r = rev2_32(~f);
+                const uint32_t hf = rcq_mix32(f), hr = rcq_mix32(r);
+                uint32_t v = min(min(hf, hr), 0xFFFFFFFEu);
+                if (p < 0 || p >= nk || ((uint32_t)(M64 >> (16 + j)) & 0xFFFFu)) v = 0xFFFFFFFFu;
+                h[j] = v;
+                obits |= (uint32_t)(hr < hf) << j;
+                pbits |= (uint32_t)(hr == hf) << j;
             }
             __syncwarp();
-            for (int i0 = 0; i0 < T; i0 += 32) {
-                const int i = i0 + lane;
-                const int32_t p = c + i;
-                bool sel = false;
-                uint32_t h = 0xFFFFFFFFu;
-                if (p < nk) {
-                    h = sh[wib][i + H];
-                    if (h != 0xFFFFFFFFu) {
-                        int a = 0, b = 0;
-                        int amax = min(H, p), bmax = min(H, nk - 1 - p);
-                        while (a < amax && sh[wib][i + H - a - 1] >= h) a++;
-                        while (b < bmax && sh[wib][i + H + b + 1] >= h) b++;
-                        sel = (H - b) <= a;  // some window [p-j, p-j+12], j<=a, 12-j<=b
+            uint4* mine = (uint4*)(hx[wib] + lane * MZ_STRIDE);
+            mine[0] = make_uint4(h[0], h[1], h[2], h[3]);
+            mine[1] = make_uint4(h[4], h[5], h[6], h[7]);
+            mine[2] = make_uint4(h[8], h[9], h[10], h[11]);
+            mine[3] = make_uint4(h[12], h[13], h[14], h[15]);
+            __syncwarp();
+            // ---- neighbourhood v[0..40) = hashes of positions q0-12 .. q0+27
+            uint32_t v[40];
+            {
+                const uint4* L = (const uint4*)(hx[wib] + ((lane + 31) & 31) * MZ_STRIDE);
+                const uint4* R = (const uint4*)(hx[wib] + ((lane + 1) & 31) * MZ_STRIDE);
+                const uint4 l1 = L[1], l2 = L[2], l3 = L[3], r0 = R[0], r1 = R[1], r2 = R[2];
+                v[0] = l1.x; v[1] = l1.y; v[2] = l1.z; v[3] = l1.w; v[4] = l2.x; v[5] = l2.y; v[6] = l2.z; v[7] = l2.w;
+                v[8] = l3.x; v[9] = l3.y; v[10] = l3.z; v[11] = l3.w;
+#pragma unroll
+                for (int j = 0; j < 16; j++) v[12 + j] = h[j];
+                v[28] = r0.x; v[29] = r0.y; v[30] = r0.z; v[31] = r0.w; v[32] = r1.x; v[33] = r1.y; v[34] = r1.z; v[35] = r1.w;
+                v[36] = r2.x; v[37] = r2.y; v[38] = r2.z; v[39] = r2.w;
+            }
+            // ---- w[t] = min(v[t..t+12]), t < 28, by doubling (in place)
+#pragma unroll
+            for (int i = 0; i < 39; i++) v[i] = min(v[i], v[i + 1]);       // spans of 2
+#pragma unroll
+            for (int i = 0; i < 37; i++) v[i] = min(v[i], v[i + 2]);       // 4
+#pragma unroll
+            for (int i = 0; i < 33; i++) v[i] = min(v[i], v[i + 4]);       // 8
+#pragma unroll
+            for (int i = 0; i < 28; i++) {
+                uint32_t x = min(v[i], v[i + 5]);                          // 13
+                const int32_t ps = q0 - 12 + i;                            // window start
+                v[i] = (ps < 0 || ps > nk - RCQ_WIN) ? 0u : x;
+            }
+            // ---- x[j] = max(w[j..j+12]), j < 16
+#pragma unroll
+            for (int i = 0; i < 27; i++) v[i] = max(v[i], v[i + 1]);
+#pragma unroll
+            for (int i = 0; i < 25; i++) v[i] = max(v[i], v[i + 2]);
+#pragma unroll
+            for (int i = 0; i < 21; i++) v[i] = max(v[i], v[i + 4]);
+            uint32_t sel = 0;
+#pragma unroll
+            for (int j = 0; j < 16; j++) {
+                const uint32_t x = max(v[j], v[j + 5]);
+                sel |= (uint32_t)(h[j] != 0xFFFFFFFFu && x == h[j]) << j;
+            }
+            if (lane == 0 || lane == 31) sel = 0;          // halo lanes decide nothing
+            // ---- sel bitmap: lanes (odd, odd+1) make one aligned 32-position word
+            {
+                const uint32_t hi = __shfl_down_sync(0xffffffffu, sel, 1);
+                if ((lane & 1) && lane < 31 && q0 < nk) selmap[(off + q0) >> 5] = sel | (hi << 16);
+            }
+            // ---- append
+            const int cnt = __popc(sel);
+            int incl = cnt;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                int x = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += x;
+            }
+            const int total = __shfl_sync(0xffffffffu, incl, 31);
+            if (total) {
+                if (nbuf + total > MZ_BUF) flush();
+                int slot = nbuf + incl - cnt;
+#pragma unroll
+                for (int j = 0; j < 16; j++) {
+                    if (!((sel >> j) & 1u)) continue;
+                    const int32_t p = q0 + j;
+                    const uint32_t o = (obits >> j) & 1u;
+                    // flanks: 13 bases before (window offset 3+j) and after (window offset 32+j) the 16-mer
+                    uint32_t Lf = 0x80000000u, Rf = 0x80000000u;
+                    if (p >= RCQ_WIN && !((uint32_t)(M64 >> (3 + j)) & 0x1FFFu)) {
+                        const int bo = 3 + j;
+                        Lf = (bo < 16 ? __funnelshift_r(a0, a1, 2 * (bo & 15)) : __funnelshift_r(a1, a2, 2 * (bo & 15))) & M26;
                     }
-                }
-                const unsigned m = __ballot_sync(0xffffffffu, sel);
-                if (c + i0 < nk && lane == 0) selmap[(off + c + i0) >> 5] = m;
-                if (m) {
-                    if (nbuf + 32 > MZ_BUF) flush();
-                    if (sel) {
-                        const uint32_t oo = so[wib][i + H];
-                        const int slot = nbuf + __popc(m & ((1u << lane) - 1u));
-                        be[wib][slot] = ((unsigned long long)rcq_index_key(h) << 32) |
-                                        ((unsigned long long)(off + p) << 1) | (oo & 1u);
-                        bc[wib][slot] = flank_ctx(fwd, mask, off, p, n, oo & 1u, oo >> 1);
+                    if (p + RCQ_KMER + RCQ_WIN <= n && !((uint32_t)(M64 >> (32 + j)) & 0x1FFFu))
+                        Rf = __funnelshift_r(a2, a3, 2 * j) & M26;
+                    uint32_t cl, cr;
+                    if (!o) { cl = Lf; cr = Rf; }
+                    else {
+                        cl = (Rf >> 31) ? Rf : rc13(Rf);
+                        cr = (Lf >> 31) ? Lf : rc13(Lf);
                     }
-                    nbuf += __popc(m);
+                    if ((pbits >> j) & 1u) cl |= 0x40000000u;
+                    be[wib][slot] = ((unsigned long long)rcq_index_key(h[j]) << 32) |
+                                    ((unsigned long long)(off + p) << 1) | o;
+                    bc[wib][slot] = ((uint64_t)cr << 32) | cl;
+                    slot++;
                 }
+                nbuf += total;
             }
         }
     }

@@ -162,7 +162,7 @@ class Engine:
                                 exchange=(t_exchange - t_search) * 1e3, phase2=(t_phase2 - t_exchange) * 1e3),
                    pairs=pairs, nident_sum=res["nident_sum"], denom_sum=res["denom_sum"], counts=res["counts"],
                    stats=stats, no_ideal=res["no_ideal"], n_local_pairs=len(mine),
-                   lengths=[s.total for s in samples])
+                   lengths=[s.total for s in samples], n_index=[s.n_index for s in samples])
         if not res["no_ideal"]:
             out["labels"], out["matrix"] = self.matrix_from_sums(labels, pairs, res["nident_sum"], res["denom_sum"])
         if keep_tables:
