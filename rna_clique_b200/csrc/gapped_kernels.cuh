@@ -366,7 +366,7 @@ __device__ __forceinline__ bool ung_before(const Ungapped& x, const Ungapped& y)
 // U is indexed like the sorted seed list (slots of seeds the diagonal rule skipped have score < 0);
 // keys[] are the seed sort keys (KeyFmt): group = key >> d_bits.
 template <bool MASKED>
-__global__ void __launch_bounds__(128) k_gapped(const Ungapped* __restrict__ U,
+__global__ void __launch_bounds__(128, 6) k_gapped(const Ungapped* __restrict__ U,
                                                 const uint64_t* __restrict__ keys, int64_t n, KeyFmt F,
                                                 const uint32_t* __restrict__ heads, int64_t n_groups,
                                                 PairView P, Gapped* __restrict__ out, ScratchPool sp,

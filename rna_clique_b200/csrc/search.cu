@@ -160,12 +160,21 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
         Gapped* G = nullptr;
         RC(dalloc(ctx, &G, n_seeds));
         CU(cudaMemsetAsync(G, 0xFF, n_seeds * sizeof(Gapped), ctx->stream));
-        const int blocks = RCQ_SMS * 8, threads = 128;
+        const int threads = 128;
+        const bool masked = s1->n_masked || s2->n_masked;
+        static int occ[2] = {0, 0};   // resident blocks per SM of the two variants
+        if (!occ[masked]) {
+            int nb = 0;
+            if (masked) CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_gapped<true>, threads, 0));
+            else CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_gapped<false>, threads, 0));
+            occ[masked] = nb > 0 ? nb : 1;
+        }
+        const int blocks = RCQ_SMS * occ[masked];   // persistent warps, groups handed out by an atomic counter
         ScratchPool sp;
         RC(scratch_pool(ctx, 6ll * ((int64_t)s1->max_len + s2->max_len + 8), &sp));
         CU(cudaMemsetAsync(ctr, 0, 16 * sizeof(int64_t), ctx->stream));
         stage_tic(ctx, 4);
-        if (s1->n_masked || s2->n_masked)
+        if (masked)
             LAUNCH(ctx, k_gapped<true>, blocks, threads, 0, U, keys, n_seeds, F, heads, n_groups, P, G, sp, ctr);
         else
             LAUNCH(ctx, k_gapped<false>, blocks, threads, 0, U, keys, n_seeds, F, heads, n_groups, P, G, sp, ctr);

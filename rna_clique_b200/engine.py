@@ -72,6 +72,68 @@ class Engine:
                 f.result()
         return out
 
+    def _run_tasks(self, tasks, samples, tables, do_upload, do_search, pair_of):
+        """Workers (one per context) drain `tasks` in order, skipping searches whose samples are not
+        resident yet; an exception in any worker is re-raised here."""
+        import threading
+        cv = threading.Condition()
+        state = {"next": [True] * len(tasks), "left": len(tasks), "err": None}
+
+        S = len(self.ctxs)
+
+        def ready(task, w):
+            if task[0] == "u":
+                # uploads are pinned to a context (sample k -> context k % S): every context's memory
+                # pool then sees the same allocation sequence each step and stops growing after warm-up
+                return task[1] % S == w
+            i, j = pair_of(task[1])
+            return samples[i] is not None and samples[j] is not None
+
+        def work(w):
+            ctx = self.ctxs[w]
+            while True:
+                with cv:
+                    pick = None
+                    while pick is None:
+                        if state["err"] is not None or state["left"] == 0:
+                            return
+                        pending = False
+                        for t, open_ in enumerate(state["next"]):
+                            if not open_:
+                                continue
+                            pending = True
+                            if ready(tasks[t], w):
+                                pick = t
+                                break
+                        if pick is None:
+                            if not pending:
+                                return
+                            cv.wait()
+                    state["next"][pick] = False
+                kind, x = tasks[pick]
+                try:
+                    r = do_upload(ctx, x) if kind == "u" else do_search(ctx, x)
+                except BaseException as e:  # noqa: BLE001
+                    with cv:
+                        state["err"] = e
+                        cv.notify_all()
+                    return
+                with cv:
+                    if kind == "u":
+                        samples[x] = r
+                    else:
+                        tables[x] = r
+                    state["left"] -= 1
+                    cv.notify_all()
+
+        if self._pool is None:
+            work(0)
+        else:
+            for f in [self._pool.submit(work, w) for w in range(S)]:
+                f.result()
+        if state["err"] is not None:
+            raise state["err"]
+
     @property
     def launches(self) -> int:
         return sum(c.launches for c in self.ctxs)
@@ -138,12 +200,29 @@ class Engine:
                 starts, lengths, gene, iso = starts[keep], lengths[keep], gene[keep], iso[keep]
             return self.upload(s["ascii"], starts, lengths, gene, iso, name=labels[k], ctx=ctx)
 
-        samples = self._fan_out(len(inputs), up)
-        n = len(samples)
-        t_upload = time.perf_counter()
-        pairs, owner = schedule_pairs(n, [s.total for s in samples], world)
+        # One task list, dependency-driven: [upload 0, upload 1, search (0,1), upload 2, search (0,2), ...].
+        # A worker (one per stream) takes the first task whose samples are resident, so host->device copies
+        # and index builds of later samples overlap the searches of earlier ones instead of forming a
+        # barrier before the first search.
+        n = len(inputs)
+        # cost estimate for the pair schedule: all bases of a sample (identical on every rank)
+        totals = [int(np.sum(np.asarray(inputs[k]["lengths"], dtype=np.int64))) for k in range(n)]
+        pairs, owner = schedule_pairs(n, totals, world)
         mine = [k for k in range(len(pairs)) if owner[k] == rank]
-        _, my_tables = self.search(samples, [pairs[k] for k in mine], evalue, top_n, keep_all)
+        samples = [None] * n
+        my_tables = [None] * len(mine)
+        tasks = []
+        by_last = {}
+        for slot, k in enumerate(mine):
+            by_last.setdefault(max(pairs[k]), []).append(slot)
+        for k in range(n):
+            tasks.append(("u", k))
+            tasks.extend(("s", slot) for slot in by_last.get(k, []))
+        self._run_tasks(tasks, samples, my_tables, up,
+                        lambda ctx, slot: _native.search_pair(ctx, samples[pairs[mine[slot]][0]], samples[pairs[mine[slot]][1]],
+                                                              evalue, top_n, keep_all),
+                        lambda slot: pairs[mine[slot]])
+        t_upload = time.perf_counter()
         stats = {}
         for t in my_tables:
             for key, v in t.stats.items():
