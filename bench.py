@@ -200,6 +200,8 @@ def main():
     torch.cuda.set_device(local)
     dist = None
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"   # NCCL_DEBUG=VERSION prints a banner on stdout; stdout carries one JSON line
         import torch.distributed as dist_mod
         dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local))
         dist = dist_mod
@@ -254,7 +256,7 @@ def main():
     if a.clock_interval > 0:
         sampler.start()
     ms_dev, res, stages, launches = timed(lambda: eng.all_vs_all(resident, labels, None, dist=dist), a.steps, a.warmup)
-    ms_e2e, res2, _, _ = timed(lambda: eng.all_vs_all(host, labels, a.top, dist=dist), a.steps, 1)
+    ms_e2e, res2, _, _ = timed(lambda: eng.all_vs_all(host, labels, a.top, dist=dist), a.steps, a.warmup)
     sampler.stop_flag = True
     if a.clock_interval > 0:
         sampler.join(timeout=2)

@@ -1,5 +1,7 @@
 // api_sample.cu — context lifetime and rcq_sample_* entry points of the C ABI (include/rcq.h).
 #include <algorithm>
+#include <chrono>
+#include <cstdlib>
 #include "sample.cuh"
 
 thread_local std::string g_rcq_err;
@@ -78,6 +80,14 @@ int rcq_sample_create(rcq_ctx* ctx, const uint8_t* ascii, int64_t ascii_len, int
     if (!ctx || !out || n_seq < 0 || ascii_len < 0 || (n_seq > 0 && (!ascii || !starts || !lengths || !gene || !iso)))
         return rcq_fail(RCQ_ERR_ARG, "rcq_sample_create: bad argument");
     CU(cudaSetDevice(ctx->device));
+    static const bool trace = getenv("RCQ_TRACE") != nullptr;
+    auto T0 = std::chrono::steady_clock::now();
+    auto lap = [&](const char* what) {
+        if (!trace) return;
+        auto T1 = std::chrono::steady_clock::now();
+        fprintf(stderr, "[rcq_sample_create] %-12s %.3f ms\n", what, std::chrono::duration<double, std::milli>(T1 - T0).count());
+        T0 = T1;
+    };
     rcq_sample* s = new rcq_sample();
     s->ctx = ctx;
     s->n_seq = n_seq;
@@ -98,6 +108,7 @@ int rcq_sample_create(rcq_ctx* ctx, const uint8_t* ascii, int64_t ascii_len, int
         pos = (pos + l + 31) & ~31ll;
         if (pos > 0x7ffffff0ll - 256) { delete s; return rcq_fail(RCQ_ERR_ARG, "rcq_sample_create: sample exceeds 2^31 bases"); }
     }
+    lap("offsets");
     s->total = total;
     s->max_len = max_len;
     s->arena = ((pos + 63) & ~63ll) + 128;
@@ -118,13 +129,30 @@ int rcq_sample_create(rcq_ctx* ctx, const uint8_t* ascii, int64_t ascii_len, int
     RC(dalloc(ctx, &s->gidx, n_seq));
     std::vector<int32_t> gidx(n_seq > 0 ? n_seq : 1);
     {
-        std::vector<int32_t> u(gene, gene + n_seq);
-        std::sort(u.begin(), u.end());
-        u.erase(std::unique(u.begin(), u.end()), u.end());
-        s->n_genes = (int32_t)u.size();
-        for (int32_t t = 0; t < n_seq; t++)
-            gidx[t] = (int32_t)(std::lower_bound(u.begin(), u.end(), gene[t]) - u.begin());
+        // dense rank of every gene id among the sample's distinct ids: counting pass when the ids are
+        // small non-negative integers (rnaSPAdes gene numbers), sort otherwise
+        int32_t gmin = 0, gmax = -1;
+        for (int32_t t = 0; t < n_seq; t++) {
+            if (t == 0 || gene[t] < gmin) gmin = gene[t];
+            if (t == 0 || gene[t] > gmax) gmax = gene[t];
+        }
+        if (n_seq > 0 && gmin >= 0 && (int64_t)gmax < 8ll * n_seq + 1024) {
+            std::vector<int32_t> rank((size_t)gmax + 2, 0);
+            for (int32_t t = 0; t < n_seq; t++) rank[gene[t]] = 1;
+            int32_t acc = 0;
+            for (int64_t g = 0; g <= gmax; g++) { int32_t present = rank[g]; rank[g] = acc; acc += present; }
+            s->n_genes = acc;
+            for (int32_t t = 0; t < n_seq; t++) gidx[t] = rank[gene[t]];
+        } else {
+            std::vector<int32_t> u(gene, gene + n_seq);
+            std::sort(u.begin(), u.end());
+            u.erase(std::unique(u.begin(), u.end()), u.end());
+            s->n_genes = (int32_t)u.size();
+            for (int32_t t = 0; t < n_seq; t++)
+                gidx[t] = (int32_t)(std::lower_bound(u.begin(), u.end(), gene[t]) - u.begin());
+        }
     }
+    lap("gene index");
     if (n_seq) {
         CU(cudaMemcpyAsync(s->gidx, gidx.data(), n_seq * 4, cudaMemcpyHostToDevice, ctx->stream));
         CU(cudaMemcpyAsync(s->off, aoff.data(), n_seq * 4, cudaMemcpyHostToDevice, ctx->stream));
@@ -132,12 +160,15 @@ int rcq_sample_create(rcq_ctx* ctx, const uint8_t* ascii, int64_t ascii_len, int
         CU(cudaMemcpyAsync(s->gene, gene, n_seq * 4, cudaMemcpyHostToDevice, ctx->stream));
         CU(cudaMemcpyAsync(s->iso, iso, n_seq * 4, cudaMemcpyHostToDevice, ctx->stream));
     }
+    lap("h2d small");
     stage_tic(ctx, 0);
     int rc = rcq_sample_build(ctx, s, d_ascii, ascii_len, d_starts);
     stage_toc(ctx, 0);
+    lap("build launch");
     // the host staging vectors (aoff, len) must outlive the async copies
     cudaStreamSynchronize(ctx->stream);
     stage_collect(ctx);
+    lap("final sync");
     dfree(ctx, own_ascii);
     dfree(ctx, d_starts);
     if (rc) { rcq_sample_free(s); return rc; }

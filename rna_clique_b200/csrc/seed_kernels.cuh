@@ -65,62 +65,91 @@ __device__ __forceinline__ bool probe_keep(uint64_t cb, uint32_t oA, uint32_t wa
     const uint32_t other = oA ? (uint32_t)(cb >> 32) : ((uint32_t)cb & 0xBFFFFFFFu);
     return !(usable && other == want);
 }
+// Block-tiled merge join.  A block owns PROBE_TA consecutive entries of A (registers, 4 per thread);
+// their key span maps through B's directory to one contiguous range of B, which is streamed through
+// shared memory PROBE_TB entries (+ contexts) at a time with coalesced 8-byte loads.  Every global
+// access of the kernel is therefore a sequential stream (16 B per entry of A and of B, 8 B per
+// surviving candidate); the per-entry lookup is a binary search in shared memory.
+#define PROBE_TA 1024
+#define PROBE_TB 1024
 __global__ void __launch_bounds__(256) k_seed_probe(
     const uint64_t* __restrict__ idxA, const uint64_t* __restrict__ ctxA, int64_t nIdxA,
     const uint64_t* __restrict__ idxB, const uint64_t* __restrict__ ctxB, const uint32_t* __restrict__ dirB,
     uint2* __restrict__ cand, int64_t cap, unsigned long long* __restrict__ counters) {
+    __shared__ uint64_t sB[PROBE_TB], sC[PROBE_TB];
     __shared__ uint32_t wsum[8], wseen[8];
     __shared__ unsigned long long bbase;
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t first = 0, last = 0, cnt = 0, lowA = 0, key = 0, oA = 0, want = 0, seen = 0;
-    bool usable = false;
-    if (e < nIdxA) {
-        const uint64_t ka = __ldg(idxA + e), ca = __ldg(ctxA + e);
-        key = (uint32_t)(ka >> 32);
-        lowA = (uint32_t)ka;
-        oA = lowA & 1u;
-        want = oA ? (uint32_t)(ca >> 32) : ((uint32_t)ca & 0xBFFFFFFFu);
-        usable = !(want >> 31) && !((uint32_t)ca & 0x40000000u);
-        const uint32_t b = key >> (32 - RCQ_DIRBITS);
-        const uint32_t lo = __ldg(dirB + b), hi = __ldg(dirB + b + 1);
-        for (uint32_t k = lo; k < hi; k++) {
-            const uint32_t kb = (uint32_t)(__ldg(idxB + k) >> 32);
-            if (kb < key) continue;
-            if (kb > key) break;
-            seen++;
-            if (!probe_keep(__ldg(ctxB + k), oA, want, usable)) continue;
-            if (!cnt) first = k;
-            last = k;
-            cnt++;
+    const int64_t a0 = (int64_t)blockIdx.x * PROBE_TA;
+    const int64_t a1 = min(a0 + (int64_t)PROBE_TA, nIdxA);
+    uint32_t key[4], lowA[4], want[4];
+    bool usable[4], have[4];
+#pragma unroll
+    for (int r = 0; r < 4; r++) {
+        const int64_t e = a0 + threadIdx.x + 256 * r;
+        have[r] = e < a1;
+        key[r] = 0; lowA[r] = 0; want[r] = 0; usable[r] = false;
+        if (have[r]) {
+            const uint64_t ka = __ldg(idxA + e), ca = __ldg(ctxA + e);
+            key[r] = (uint32_t)(ka >> 32);
+            lowA[r] = (uint32_t)ka;
+            want[r] = (lowA[r] & 1u) ? (uint32_t)(ca >> 32) : ((uint32_t)ca & 0xBFFFFFFFu);
+            usable[r] = !(want[r] >> 31) && !((uint32_t)ca & 0x40000000u);
         }
     }
-    // block exclusive scan of cnt
-    uint32_t incl = cnt;
+    const uint32_t kfirst = (uint32_t)(__ldg(idxA + a0) >> 32), klast = (uint32_t)(__ldg(idxA + a1 - 1) >> 32);
+    const uint32_t blo = __ldg(dirB + (kfirst >> (32 - RCQ_DIRBITS))), bhi = __ldg(dirB + (klast >> (32 - RCQ_DIRBITS)) + 1);
+    for (uint32_t b0 = blo; b0 < bhi; b0 += PROBE_TB) {
+        const int nb = (int)min((uint32_t)PROBE_TB, bhi - b0);
+        for (int i = threadIdx.x; i < nb; i += 256) { sB[i] = __ldg(idxB + b0 + i); sC[i] = __ldg(ctxB + b0 + i); }
+        __syncthreads();
+        // ---- count survivors of this chunk
+        int pos[4];
+        uint32_t cnt = 0, seen = 0;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= o) incl += v;
-    }
-    for (int o = 16; o; o >>= 1) seen += __shfl_down_sync(0xffffffffu, seen, o);
-    if (lane == 31) wsum[wib] = incl;
-    if (lane == 0) wseen[wib] = seen;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        uint32_t tot = 0, sn = 0;
-        for (int w = 0; w < 8; w++) { uint32_t v = wsum[w]; wsum[w] = tot; tot += v; sn += wseen[w]; }
-        bbase = tot ? atomicAdd(counters + 1, (unsigned long long)tot) : 0ull;
-        if (sn) atomicAdd(counters + 2, (unsigned long long)sn);
-    }
-    __syncthreads();
-    if (!cnt) return;
-    unsigned long long slot = bbase + wsum[wib] + (incl - cnt);
-    for (uint32_t k = first; k <= last; k++) {
-        const uint64_t eb = __ldg(idxB + k);
-        if ((uint32_t)(eb >> 32) != key) continue;
-        if (!probe_keep(__ldg(ctxB + k), oA, want, usable)) continue;
-        if ((int64_t)slot < cap) cand[slot] = make_uint2(lowA, (uint32_t)eb);
-        slot++;
+        for (int r = 0; r < 4; r++) {
+            pos[r] = nb;
+            if (!have[r]) continue;
+            int lo = 0, hi = nb;                      // first entry of the chunk with key >= key[r]
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                if ((uint32_t)(sB[mid] >> 32) < key[r]) lo = mid + 1; else hi = mid;
+            }
+            pos[r] = lo;
+            for (int k = lo; k < nb && (uint32_t)(sB[k] >> 32) == key[r]; k++) {
+                seen++;
+                cnt += probe_keep(sC[k], lowA[r] & 1u, want[r], usable[r]);
+            }
+        }
+        uint32_t incl = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        for (int o = 16; o; o >>= 1) seen += __shfl_down_sync(0xffffffffu, seen, o);
+        if (lane == 31) wsum[wib] = incl;
+        if (lane == 0) wseen[wib] = seen;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            uint32_t tot = 0, sn = 0;
+            for (int w = 0; w < 8; w++) { uint32_t v = wsum[w]; wsum[w] = tot; tot += v; sn += wseen[w]; }
+            bbase = tot ? atomicAdd(counters + 1, (unsigned long long)tot) : 0ull;
+            if (sn) atomicAdd(counters + 2, (unsigned long long)sn);
+        }
+        __syncthreads();
+        if (cnt) {
+            unsigned long long slot = bbase + wsum[wib] + (incl - cnt);
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                for (int k = pos[r]; k < nb && (uint32_t)(sB[k] >> 32) == key[r]; k++) {
+                    if (!probe_keep(sC[k], lowA[r] & 1u, want[r], usable[r])) continue;
+                    if ((int64_t)slot < cap) cand[slot] = make_uint2(lowA[r], (uint32_t)sB[k]);
+                    slot++;
+                }
+            }
+        }
+        __syncthreads();
     }
 }
 
