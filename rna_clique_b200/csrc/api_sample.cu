@@ -48,6 +48,8 @@ void rcq_ctx_destroy(rcq_ctx* c) {
     cudaStreamSynchronize(c->stream);
     if (c->dbg_hsp) cudaFree(c->dbg_hsp);
     if (c->gs_rows) cudaFree(c->gs_rows);
+    for (void* p : c->arena_overflow) cudaFreeAsync(p, c->stream);
+    if (c->arena) cudaFree(c->arena);
     if (c->gs_locks) cudaFree(c->gs_locks);
     for (int i = 0; i < 16; i++) cudaEventDestroy(c->ev[i]);
     cudaFreeHost(c->h_pin);
@@ -115,9 +117,10 @@ int rcq_sample_create(rcq_ctx* ctx, const uint8_t* ascii, int64_t ascii_len, int
     const uint8_t* d_ascii = ascii;
     uint8_t* own_ascii = nullptr;
     int64_t* d_starts = nullptr;
-    RC(dalloc(ctx, &d_starts, n_seq));
+    RC(arena_reset(ctx));
+    RC(talloc(ctx, &d_starts, n_seq));
     if (!ascii_on_device && n_seq) {
-        RC(dalloc(ctx, &own_ascii, ascii_len + 64));
+        RC(talloc(ctx, &own_ascii, ascii_len + 64));
         CU(cudaMemcpyAsync(own_ascii, ascii, ascii_len, cudaMemcpyHostToDevice, ctx->stream));
         d_ascii = own_ascii;
     }
@@ -169,8 +172,6 @@ int rcq_sample_create(rcq_ctx* ctx, const uint8_t* ascii, int64_t ascii_len, int
     cudaStreamSynchronize(ctx->stream);
     stage_collect(ctx);
     lap("final sync");
-    dfree(ctx, own_ascii);
-    dfree(ctx, d_starts);
     if (rc) { rcq_sample_free(s); return rc; }
     *out = s;
     return 0;

@@ -48,6 +48,10 @@ struct rcq_ctx {
     int32_t* dbg_hsp = nullptr;
     int64_t dbg_n = 0;
     int dbg_keep = 0;
+    // transient arena (talloc/arena_reset below): scratch of one API call, bump-allocated
+    char* arena = nullptr;
+    size_t arena_cap = 0, arena_used = 0, arena_need = 0;
+    std::vector<void*> arena_overflow;
     // fallback rows of the gapped kernel (search.cu: scratch_pool)
     int32_t* gs_rows = nullptr;
     unsigned int* gs_locks = nullptr;
@@ -87,6 +91,42 @@ template <typename T>
 static inline void dfree(rcq_ctx* c, T* p) {
     if (p) cudaFreeAsync((void*)p, c->stream);
 }
+
+// Transient scratch of one API call: bump allocation out of one per-context slab, so the steady
+// state makes no allocator calls at all (a pool that has to grow mid-step maps new physical memory,
+// which stalls every stream of the device for tens to hundreds of milliseconds).  Every entry point
+// that uses talloc starts with arena_reset and ends with a stream synchronise.  A request that does
+// not fit falls back to the pool for this call and the slab is regrown at the next reset.
+static inline int arena_reset(rcq_ctx* c) {
+    for (void* p : c->arena_overflow) cudaFreeAsync(p, c->stream);
+    c->arena_overflow.clear();
+    if (c->arena_need > c->arena_cap) {
+        CU(cudaStreamSynchronize(c->stream));
+        if (c->arena) CU(cudaFree(c->arena));
+        c->arena = nullptr;
+        c->arena_cap = c->arena_need + c->arena_need / 4 + (64u << 20);
+        CU(cudaMalloc((void**)&c->arena, c->arena_cap));
+    }
+    c->arena_used = 0;
+    c->arena_need = 0;
+    return 0;
+}
+template <typename T>
+static inline int talloc(rcq_ctx* c, T** p, int64_t n) {
+    if (n < 1) n = 1;
+    const size_t bytes = ((size_t)n * sizeof(T) + 255) & ~(size_t)255;
+    c->arena_need += bytes;
+    if (c->arena_used + bytes <= c->arena_cap) {
+        *p = (T*)(c->arena + c->arena_used);
+        c->arena_used += bytes;
+        return 0;
+    }
+    CU(cudaMallocFromPoolAsync((void**)p, bytes, c->pool, c->stream));
+    c->arena_overflow.push_back((void*)*p);
+    return 0;
+}
+template <typename T>
+static inline void tfree(rcq_ctx*, T*) {}   // released wholesale by the next arena_reset
 
 #define LAUNCH(ctx, kern, grid, block, smem, ...)                       \
     do {                                                                \

@@ -363,8 +363,8 @@ __device__ __forceinline__ bool ung_before(const Ungapped& x, const Ungapped& y)
 // order; one contained in an earlier gapped HSP of the group is skipped; identical results are
 // dropped; at most RCQ_MAX_GAPPED_PER_GROUP gapped HSPs are kept.  Group g writes its results
 // to out[head .. head+count), the remaining slots of its range keep ta = -1.
-// U is indexed like the sorted seed list (slots of seeds the diagonal rule skipped have score < 0);
-// keys[] are the seed sort keys (KeyFmt): group = key >> d_bits.
+// U is the HSP list sorted by group (empty slots, score < 0, sort behind every group);
+// keys[] are the sorted group keys of U (k_hsp_keys): ta | tb | strand.
 template <bool MASKED>
 __global__ void __launch_bounds__(128, 6) k_gapped(const Ungapped* __restrict__ U,
                                                 const uint64_t* __restrict__ keys, int64_t n, KeyFmt F,
@@ -382,8 +382,8 @@ __global__ void __launch_bounds__(128, 6) k_gapped(const Ungapped* __restrict__ 
         if ((int64_t)g >= n_groups) break;
         const int64_t h = heads[g];
         int64_t e = h + 1;
-        const uint64_t key = keys[h] >> F.d_bits;
-        while (e < n && (keys[e] >> F.d_bits) == key) e++;
+        const uint64_t key = keys[h];
+        while (e < n && keys[e] == key) e++;
         const int32_t gsize = (int32_t)(e - h);
         const int32_t ta = (int32_t)(key >> (F.tb_bits + 1)), tb = (int32_t)((key >> 1) & ((1u << F.tb_bits) - 1u)), minus = (int32_t)(key & 1);
         const int64_t oa = __ldg(P.offA + ta), ob = __ldg(P.offB + tb);

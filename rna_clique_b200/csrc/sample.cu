@@ -350,23 +350,21 @@ __global__ void k_build_dir(const uint64_t* __restrict__ index, int64_t n, uint3
 }
 
 // index entries sorted by key (bits 32..63) with their flank contexts as payload
-static int sort_index(rcq_ctx* ctx, uint64_t** keys, uint64_t** vals, int64_t n) {
+static int sort_index(rcq_ctx* ctx, uint64_t* keys, uint64_t* vals, int64_t n) {
     if (n <= 1) return 0;
     uint64_t *k2 = nullptr, *v2 = nullptr;
-    RC(dalloc(ctx, &k2, n));
-    RC(dalloc(ctx, &v2, n));
-    cub::DoubleBuffer<uint64_t> dk(*keys, k2), dv(*vals, v2);
+    RC(talloc(ctx, &k2, n));
+    RC(talloc(ctx, &v2, n));
+    cub::DoubleBuffer<uint64_t> dk(keys, k2), dv(vals, v2);
     size_t bytes = 0;
     CU(cub::DeviceRadixSort::SortPairs(nullptr, bytes, dk, dv, (int)n, 32, 64, ctx->stream));
-    void* ws = nullptr;
-    CU(cudaMallocFromPoolAsync(&ws, bytes, ctx->pool, ctx->stream));
+    char* ws = nullptr;
+    RC(talloc(ctx, &ws, (int64_t)bytes));
     CU(cub::DeviceRadixSort::SortPairs(ws, bytes, dk, dv, (int)n, 32, 64, ctx->stream));
     ctx->launches += 32 / 8 + 1;
-    cudaFreeAsync(ws, ctx->stream);
-    uint64_t *ko = dk.Current(), *vo = dv.Current();
-    dfree(ctx, ko == *keys ? k2 : *keys);
-    dfree(ctx, vo == *vals ? v2 : *vals);
-    *keys = ko; *vals = vo;
+    // four 8-bit passes end in the buffers they started from; copy back if a CUB version ever differs
+    if (dk.Current() != keys) CU(cudaMemcpyAsync(keys, dk.Current(), n * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+    if (dv.Current() != vals) CU(cudaMemcpyAsync(vals, dv.Current(), n * 8, cudaMemcpyDeviceToDevice, ctx->stream));
     return 0;
 }
 
@@ -419,7 +417,7 @@ int rcq_sample_build(rcq_ctx* ctx, rcq_sample* s, const uint8_t* d_ascii, int64_
     }
     // sorted by key only (bits 32..63): entries of one key stay in append order, which no result
     // depends on (seeds are re-sorted by transcript and diagonal)
-    if (s->n_index) RC(sort_index(ctx, &s->index, &s->fctx, s->n_index));
+    if (s->n_index) RC(sort_index(ctx, s->index, s->fctx, s->n_index));
     LAUNCH(ctx, k_build_dir, grid_for(s->n_index + 1, 256), 256, 0, s->index, s->n_index, s->dir);
     return 0;
 }

@@ -3,6 +3,8 @@
 // pandas post-processing of find_homologs.py:82-164,215-302.
 #include <cub/cub.cuh>
 #include <math.h>
+#include <cstdlib>
+#include <algorithm>
 #include "search.cuh"
 
 #include "seed_kernels.cuh"
@@ -16,20 +18,19 @@ struct GappedValid {
 static int sort_pairs_u64_u32(rcq_ctx* ctx, uint64_t** keys, uint32_t** vals, int64_t n, int end_bit) {
     if (n <= 1) return 0;
     uint64_t* k2 = nullptr; uint32_t* v2 = nullptr;
-    RC(dalloc(ctx, &k2, n));
-    RC(dalloc(ctx, &v2, n));
+    RC(talloc(ctx, &k2, n));
+    RC(talloc(ctx, &v2, n));
     cub::DoubleBuffer<uint64_t> dk(*keys, k2);
     cub::DoubleBuffer<uint32_t> dv(*vals, v2);
     size_t bytes = 0;
     CU(cub::DeviceRadixSort::SortPairs(nullptr, bytes, dk, dv, (int)n, 0, end_bit, ctx->stream));
     void* ws = nullptr;
-    CU(cudaMallocFromPoolAsync(&ws, bytes, ctx->pool, ctx->stream));
+    RC(talloc(ctx, (char**)&ws, (int64_t)bytes));
     CU(cub::DeviceRadixSort::SortPairs(ws, bytes, dk, dv, (int)n, 0, end_bit, ctx->stream));
     ctx->launches += (end_bit + 7) / 8 + 1;
-    cudaFreeAsync(ws, ctx->stream);
     uint64_t* ko = dk.Current(); uint32_t* vo = dv.Current();
-    dfree(ctx, ko == *keys ? k2 : *keys);
-    dfree(ctx, vo == *vals ? v2 : *vals);
+    tfree(ctx, ko == *keys ? k2 : *keys);
+    tfree(ctx, vo == *vals ? v2 : *vals);
     *keys = ko; *vals = vo;
     return 0;
 }
@@ -74,6 +75,7 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
     if (s1->n_genes >= (1 << 20) || s2->n_genes >= (1 << 20))
         return rcq_fail(RCQ_ERR_CAPACITY, "rcq_search_pair: more than 2^20 genes in a sample");
     CU(cudaSetDevice(ctx->device));
+    RC(arena_reset(ctx));
     rcq_search_stats st;
     memset(&st, 0, sizeof st);
     PairView P;
@@ -95,8 +97,8 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
     int64_t n_seeds = 0, cap = std::max<int64_t>(1 << 20, 48ll * std::max(s1->n_seq, s2->n_seq));
     int64_t ccap = std::max<int64_t>(1 << 20, s1->n_index / 2);
     for (int attempt = 0; attempt < 3 && s1->n_index && s2->n_index; attempt++) {
-        RC(dalloc(ctx, &seeds, cap));
-        RC(dalloc(ctx, &cand, ccap));
+        RC(talloc(ctx, &seeds, cap));
+        RC(talloc(ctx, &cand, ccap));
         CU(cudaMemsetAsync(ctr, 0, 16 * sizeof(int64_t), ctx->stream));
         stage_tic(ctx, 1);
         stage_tic(ctx, 7);
@@ -110,9 +112,9 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
         n_seeds = ctx->h_pin[0];
         st.n_verified = ctx->h_pin[1];
         st.n_candidates = ctx->h_pin[2];
-        dfree(ctx, cand); cand = nullptr;
+        tfree(ctx, cand); cand = nullptr;
         if (n_seeds <= cap && st.n_verified <= ccap) break;
-        dfree(ctx, seeds); seeds = nullptr;
+        tfree(ctx, seeds); seeds = nullptr;
         cap = std::max(cap, n_seeds);
         ccap = std::max(ccap, st.n_verified);
         n_seeds = 0;
@@ -122,44 +124,93 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
     int64_t n_gapped = 0;
     Gapped* Gd = nullptr;
     if (n_seeds > 0) {
-        // ---- seeds sorted by (tx1, tx2, strand, diagonal); ungapped HSPs under the diagonal rule
+        // ---- ungapped HSPs under the diagonal rule: first HSP of every diagonal through the diagonal
+        // table, the seeds that start beyond it through the sort path (seed_kernels.cuh)
         if (s1->n_seq >= (1 << 21) || s2->n_seq >= (1 << 21))
             return rcq_fail(RCQ_ERR_CAPACITY, "rcq_search_pair: more than 2^21 transcripts in a sample");
-        Ungapped* U = nullptr;
-        RC(dalloc(ctx, &U, n_seeds));
-        CU(cudaMemsetAsync(U, 0xFF, n_seeds * sizeof(Ungapped), ctx->stream));
-        CU(cudaMemsetAsync(ctr, 0, 16 * sizeof(int64_t), ctx->stream));
-        stage_tic(ctx, 3);
-        uint64_t* keys = nullptr; uint32_t* order = nullptr; uint32_t* heads = nullptr; uint32_t* dheads = nullptr;
-        RC(dalloc(ctx, &keys, n_seeds));
-        RC(dalloc(ctx, &order, n_seeds));
-        RC(dalloc(ctx, &heads, n_seeds));
-        RC(dalloc(ctx, &dheads, n_seeds));
         KeyFmt F;
         F.bias = s1->max_len;
         F.d_bits = bits_for((int64_t)s1->max_len + s2->max_len + 1);
         F.tb_bits = bits_for(s2->n_seq);
         F.total_bits = F.d_bits + 1 + F.tb_bits + bits_for(s1->n_seq);
-        LAUNCH(ctx, k_seed_keys, grid_for(n_seeds, 256), 256, 0, seeds, n_seeds, F, keys, order);
-        RC(sort_pairs_u64_u32(ctx, &keys, &order, n_seeds, F.total_bits));
-        LAUNCH(ctx, k_seed_heads, grid_for(n_seeds, 256), 256, 0, keys, n_seeds, F, dheads, heads, ctr);
-        stage_toc(ctx, 3);
-        RC(read_counters(ctx, 7));
-        stage_collect(ctx);
-        int64_t n_groups = ctx->h_pin[5], n_diag = ctx->h_pin[6];
+        if (F.total_bits > 63) return rcq_fail(RCQ_ERR_CAPACITY, "rcq_search_pair: seed key does not fit 63 bits");
+        DiagTable T;
+        int64_t tcap = 1024;
+        while (tcap < 2 * n_seeds) tcap <<= 1;
+        T.mask = (uint32_t)(tcap - 1);
+        RC(talloc(ctx, &T.keys, 2 * tcap));
+        T.vals = T.keys + tcap;
+        uint32_t* slots = nullptr;
+        Ungapped* U1 = nullptr;
+        Seed* surv = nullptr;
+        RC(talloc(ctx, &slots, n_seeds));
+        RC(talloc(ctx, &U1, n_seeds));
+        RC(talloc(ctx, &surv, n_seeds));
+        CU(cudaMemsetAsync(T.keys, 0xFF, 2 * tcap * sizeof(unsigned long long), ctx->stream));
+        CU(cudaMemsetAsync(ctr, 0, 16 * sizeof(int64_t), ctx->stream));
         stage_tic(ctx, 2);
-        LAUNCH(ctx, k_ungapped_diag, grid_for(n_diag, 128), 128, 0, seeds, order, keys, n_seeds, dheads, n_diag, P, U, ctr);
+        LAUNCH(ctx, k_diag_insert, grid_for(n_seeds, 256), 256, 0, seeds, n_seeds, F, T, slots, ctr);
+        LAUNCH(ctx, k_diag_first, grid_for(n_seeds, 128), 128, 0, seeds, slots, T, P, U1, ctr);
+        LAUNCH(ctx, k_diag_survivors, grid_for(n_seeds, 256), 256, 0, seeds, n_seeds, F, T, surv, ctr);
         stage_toc(ctx, 2);
+        RC(read_counters(ctx, 10));
+        stage_collect(ctx);
+        const int64_t n_diag = ctx->h_pin[6], n_surv = ctx->h_pin[9];
+        st.ungapped_cells = ctx->h_pin[4];
+        tfree(ctx, T.keys); tfree(ctx, slots);
+        tfree(ctx, seeds); seeds = nullptr;
+        const int64_t n_hsp = n_diag + n_surv;
+        Ungapped* Uall = nullptr;
+        RC(talloc(ctx, &Uall, n_hsp));
+        CU(cudaMemcpyAsync(Uall, U1, n_diag * sizeof(Ungapped), cudaMemcpyDeviceToDevice, ctx->stream));
+        tfree(ctx, U1);
+        CU(cudaMemsetAsync(ctr, 0, 16 * sizeof(int64_t), ctx->stream));
+        if (n_surv > 0) {
+            // survivors: sorted by (tx1, tx2, strand, diagonal), thread per diagonal continues the rule
+            uint64_t* keys = nullptr; uint32_t* order = nullptr; uint32_t* heads = nullptr; uint32_t* dheads = nullptr;
+            RC(talloc(ctx, &keys, n_surv));
+            RC(talloc(ctx, &order, n_surv));
+            RC(talloc(ctx, &heads, n_surv));
+            RC(talloc(ctx, &dheads, n_surv));
+            CU(cudaMemsetAsync(Uall + n_diag, 0xFF, n_surv * sizeof(Ungapped), ctx->stream));
+            stage_tic(ctx, 3);
+            LAUNCH(ctx, k_seed_keys, grid_for(n_surv, 256), 256, 0, surv, n_surv, F, keys, order);
+            RC(sort_pairs_u64_u32(ctx, &keys, &order, n_surv, F.total_bits));
+            LAUNCH(ctx, k_seed_heads, grid_for(n_surv, 256), 256, 0, keys, n_surv, F, dheads, heads, ctr);
+            stage_toc(ctx, 3);
+            RC(read_counters(ctx, 7));
+            stage_collect(ctx);
+            const int64_t n_diag2 = ctx->h_pin[6];
+            LAUNCH(ctx, k_ungapped_diag, grid_for(n_diag2, 128), 128, 0, surv, order, keys, n_surv, dheads, n_diag2, P,
+                   Uall + n_diag, ctr);
+            RC(read_counters(ctx, 5));
+            st.ungapped_cells += ctx->h_pin[4];
+            CU(cudaMemsetAsync(ctr, 0, 16 * sizeof(int64_t), ctx->stream));
+            tfree(ctx, keys); tfree(ctx, order); tfree(ctx, heads); tfree(ctx, dheads);
+        }
+        tfree(ctx, surv);
+        // ---- HSPs grouped by (tx1, tx2, strand)
+        uint64_t* keys = nullptr; uint32_t* order = nullptr; uint32_t* heads = nullptr;
+        Ungapped* U = nullptr;
+        RC(talloc(ctx, &keys, n_hsp));
+        RC(talloc(ctx, &order, n_hsp));
+        RC(talloc(ctx, &heads, n_hsp));
+        RC(talloc(ctx, &U, n_hsp));
+        stage_tic(ctx, 3);
+        LAUNCH(ctx, k_hsp_keys, grid_for(n_hsp, 256), 256, 0, Uall, n_hsp, F, keys, order, ctr);
+        RC(sort_pairs_u64_u32(ctx, &keys, &order, n_hsp, F.total_bits - F.d_bits + 1));
+        LAUNCH(ctx, k_hsp_gather, grid_for(n_hsp, 256), 256, 0, Uall, order, keys, n_hsp, F, U, heads, ctr);
+        stage_toc(ctx, 3);
         RC(read_counters(ctx, 8));
         stage_collect(ctx);
-        st.ungapped_cells = ctx->h_pin[4];
+        const int64_t n_groups = ctx->h_pin[5];
         st.n_ungapped = ctx->h_pin[7];
-        dfree(ctx, seeds); seeds = nullptr;
-        dfree(ctx, order); dfree(ctx, dheads);
+        tfree(ctx, Uall); tfree(ctx, order);
+        const int64_t n_slots = n_hsp;   // gapped HSP slots: group g writes into the range of its ungapped HSPs
         // ---- gapped extension, warp per group
         Gapped* G = nullptr;
-        RC(dalloc(ctx, &G, n_seeds));
-        CU(cudaMemsetAsync(G, 0xFF, n_seeds * sizeof(Gapped), ctx->stream));
+        RC(talloc(ctx, &G, n_slots));
+        CU(cudaMemsetAsync(G, 0xFF, n_slots * sizeof(Gapped), ctx->stream));
         const int threads = 128;
         const bool masked = s1->n_masked || s2->n_masked;
         static int occ[2] = {0, 0};   // resident blocks per SM of the two variants
@@ -168,6 +219,7 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
             if (masked) CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_gapped<true>, threads, 0));
             else CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_gapped<false>, threads, 0));
             occ[masked] = nb > 0 ? nb : 1;
+            if (const char* e = getenv("RCQ_GAPPED_BPS")) occ[masked] = std::max(1, std::min(occ[masked], atoi(e)));
         }
         const int blocks = RCQ_SMS * occ[masked];   // persistent warps, groups handed out by an atomic counter
         ScratchPool sp;
@@ -175,28 +227,27 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
         CU(cudaMemsetAsync(ctr, 0, 16 * sizeof(int64_t), ctx->stream));
         stage_tic(ctx, 4);
         if (masked)
-            LAUNCH(ctx, k_gapped<true>, blocks, threads, 0, U, keys, n_seeds, F, heads, n_groups, P, G, sp, ctr);
+            LAUNCH(ctx, k_gapped<true>, blocks, threads, 0, U, keys, n_hsp, F, heads, n_groups, P, G, sp, ctr);
         else
-            LAUNCH(ctx, k_gapped<false>, blocks, threads, 0, U, keys, n_seeds, F, heads, n_groups, P, G, sp, ctr);
+            LAUNCH(ctx, k_gapped<false>, blocks, threads, 0, U, keys, n_hsp, F, heads, n_groups, P, G, sp, ctr);
         stage_toc(ctx, 4);
-        dfree(ctx, U); dfree(ctx, keys); dfree(ctx, heads);
+        tfree(ctx, U); tfree(ctx, keys); tfree(ctx, heads);
         // ---- compact (stable: group order, then processing order inside the group)
-        RC(dalloc(ctx, &Gd, n_seeds));
+        RC(talloc(ctx, &Gd, n_slots));
         size_t bytes = 0;
-        CU(cub::DeviceSelect::If(nullptr, bytes, G, Gd, (int*)(ctr + 8), (int)n_seeds, GappedValid(), ctx->stream));
+        CU(cub::DeviceSelect::If(nullptr, bytes, G, Gd, (int*)(ctr + 8), (int)n_slots, GappedValid(), ctx->stream));
         void* ws = nullptr;
-        CU(cudaMallocFromPoolAsync(&ws, bytes, ctx->pool, ctx->stream));
-        CU(cub::DeviceSelect::If(ws, bytes, G, Gd, (int*)(ctr + 8), (int)n_seeds, GappedValid(), ctx->stream));
+        RC(talloc(ctx, (char**)&ws, (int64_t)bytes));
+        CU(cub::DeviceSelect::If(ws, bytes, G, Gd, (int*)(ctr + 8), (int)n_slots, GappedValid(), ctx->stream));
         ctx->launches += 2;
-        cudaFreeAsync(ws, ctx->stream);
-        dfree(ctx, G);
+            tfree(ctx, G);
         RC(read_counters(ctx, 9));
         st.dp_cells = ctx->h_pin[1];
         st.band_retries = ctx->h_pin[2];
         n_gapped = (int64_t)(int32_t)(ctx->h_pin[8] & 0xFFFFFFFF);
         st.n_gapped = n_gapped;
     } else {
-        dfree(ctx, seeds);
+        tfree(ctx, seeds);
     }
     // debug copy of the HSP list (test hook, off unless rcq_debug_keep_hsps(ctx, 1): cudaMalloc/cudaFree
     // synchronise the whole device and would serialise the streams of the engine)
@@ -220,14 +271,14 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
         int64_t hcap = 1024;
         while (hcap < 4 * n_gapped) hcap <<= 1;
         V.hmask = (uint32_t)(hcap - 1);
-        RC(dalloc(ctx, &V.pass, n_gapped));
-        RC(dalloc(ctx, &V.bestF, s2->n_genes));
-        RC(dalloc(ctx, &V.bestB, s1->n_genes));
-        RC(dalloc(ctx, &V.bestQ, s2->n_genes));
-        RC(dalloc(ctx, &V.firstkey, s2->n_genes));
-        RC(dalloc(ctx, &V.hkeys, hcap));
-        RC(dalloc(ctx, &V.hflags, hcap));
-        RC(dalloc(ctx, &V.hbest, hcap));
+        RC(talloc(ctx, &V.pass, n_gapped));
+        RC(talloc(ctx, &V.bestF, s2->n_genes));
+        RC(talloc(ctx, &V.bestB, s1->n_genes));
+        RC(talloc(ctx, &V.bestQ, s2->n_genes));
+        RC(talloc(ctx, &V.firstkey, s2->n_genes));
+        RC(talloc(ctx, &V.hkeys, hcap));
+        RC(talloc(ctx, &V.hflags, hcap));
+        RC(talloc(ctx, &V.hbest, hcap));
         CU(cudaMemsetAsync(V.bestF, 0xFF, s2->n_genes * 4, ctx->stream));
         CU(cudaMemsetAsync(V.bestB, 0xFF, s1->n_genes * 4, ctx->stream));
         CU(cudaMemsetAsync(V.bestQ, 0xFF, s2->n_genes * 4, ctx->stream));
@@ -237,8 +288,8 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
         CU(cudaMemsetAsync(V.hbest, 0xFF, hcap * 4, ctx->stream));
         CU(cudaMemsetAsync(ctr, 0, 16 * sizeof(int64_t), ctx->stream));
         uint64_t* rkeys = nullptr; uint32_t* rdesc = nullptr;
-        RC(dalloc(ctx, &rkeys, 2 * n_gapped));
-        RC(dalloc(ctx, &rdesc, 2 * n_gapped));
+        RC(talloc(ctx, &rkeys, 2 * n_gapped));
+        RC(talloc(ctx, &rdesc, 2 * n_gapped));
         int g = grid_for(n_gapped, 256);
         stage_tic(ctx, 5);
         LAUNCH(ctx, k_sel_best, g, 256, 0, V);
@@ -258,11 +309,11 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
                    s1->gene, s1->iso, s2->gene, s2->iso, T->cols);
         }
         stage_toc(ctx, 5);
-        dfree(ctx, rkeys); dfree(ctx, rdesc);
-        dfree(ctx, V.pass); dfree(ctx, V.bestF); dfree(ctx, V.bestB); dfree(ctx, V.bestQ);
-        dfree(ctx, V.firstkey); dfree(ctx, V.hkeys); dfree(ctx, V.hflags); dfree(ctx, V.hbest);
+        tfree(ctx, rkeys); tfree(ctx, rdesc);
+        tfree(ctx, V.pass); tfree(ctx, V.bestF); tfree(ctx, V.bestB); tfree(ctx, V.bestQ);
+        tfree(ctx, V.firstkey); tfree(ctx, V.hkeys); tfree(ctx, V.hflags); tfree(ctx, V.hbest);
     }
-    dfree(ctx, Gd);
+    tfree(ctx, Gd);
     T->n = n_rows;
     st.n_rows = n_rows;
     CU(cudaStreamSynchronize(ctx->stream));

@@ -364,3 +364,94 @@ __global__ void __launch_bounds__(128) k_ungapped_diag(const Seed* __restrict__ 
     if ((threadIdx.x & 31) == 0 && work) { atomicAdd(counters + 4, work); atomicAdd(counters + 7, made); }
 }
 
+
+// ---- diagonal table: the first ungapped HSP of every diagonal without sorting the seeds ----------
+// Between orthologs ~95 % of the seeds lie inside the ungapped HSP grown from the leftmost seed of
+// their diagonal and are skipped by the diagonal rule.  So: (1) every seed enters an open-addressing
+// table keyed by its packed (ta, tb, strand, diagonal), the slot keeps the leftmost seed
+// (atomicMin on rs<<32 | seed index); (2) one thread per occupied slot extends that seed; (3) every
+// seed compares its start with the end of its diagonal's first HSP — the few that start beyond it
+// ("survivors") go through the sort + k_ungapped_diag path, which continues the diagonal rule exactly
+// where step (2) left it (all of them start at or after that HSP's end).
+#define DIAG_EMPTY 0xFFFFFFFFFFFFFFFFull
+struct DiagTable { unsigned long long* keys; unsigned long long* vals; uint32_t mask; };
+
+__device__ __forceinline__ uint64_t seed_key(const Seed& s, const KeyFmt& F) {
+    return ((((((uint64_t)(uint32_t)s.ta << F.tb_bits) | (uint64_t)(uint32_t)s.tb) << 1) | (uint64_t)s.minus) << F.d_bits) |
+           (uint64_t)(uint32_t)(s.diag + F.bias);
+}
+__device__ __forceinline__ uint32_t diag_hash(uint64_t k) {
+    k ^= k >> 33; k *= 0xff51afd7ed558ccdull; k ^= k >> 29;
+    return (uint32_t)k;
+}
+
+__global__ void k_diag_insert(const Seed* __restrict__ seeds, int64_t n, KeyFmt F, DiagTable T,
+                              uint32_t* __restrict__ slots, unsigned long long* __restrict__ counters /* [6]=diagonals */) {
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n) return;
+    const Seed s = seeds[e];
+    const unsigned long long key = seed_key(s, F);
+    uint32_t h = diag_hash(key) & T.mask;
+    while (true) {
+        const unsigned long long old = atomicCAS(T.keys + h, DIAG_EMPTY, key);
+        if (old == DIAG_EMPTY) { slots[atomicAdd(counters + 6, 1ull)] = h; break; }
+        if (old == key) break;
+        h = (h + 1) & T.mask;
+    }
+    atomicMin(T.vals + h, ((unsigned long long)(uint32_t)s.rs << 32) | (unsigned long long)(uint32_t)e);
+}
+
+// thread per occupied slot (count read on the device): extend the leftmost seed of the diagonal
+__global__ void __launch_bounds__(128) k_diag_first(const Seed* __restrict__ seeds, const uint32_t* __restrict__ slots,
+                                                    DiagTable T, PairView P, Ungapped* __restrict__ U,
+                                                    unsigned long long* __restrict__ counters /* [4]=bases [6]=diagonals */) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long work = 0;
+    if (i < (int64_t)counters[6]) {
+        const uint32_t h = slots[i];
+        const Seed s = seeds[(uint32_t)T.vals[h]];
+        const Ungapped u = ungapped_one(s, P, work);
+        U[i] = u;
+        T.vals[h] = (unsigned long long)(uint32_t)max(u.a1, s.rs + 1);   // end of the diagonal's first HSP
+    }
+    for (int o = 16; o; o >>= 1) work += __shfl_down_sync(0xffffffffu, work, o);
+    if ((threadIdx.x & 31) == 0 && work) atomicAdd(counters + 4, work);
+}
+
+__global__ void k_diag_survivors(const Seed* __restrict__ seeds, int64_t n, KeyFmt F, DiagTable T,
+                                 Seed* __restrict__ surv, unsigned long long* __restrict__ counters /* [9]=survivors */) {
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n) return;
+    const Seed s = seeds[e];
+    const unsigned long long key = seed_key(s, F);
+    uint32_t h = diag_hash(key) & T.mask;
+    while (T.keys[h] != key) h = (h + 1) & T.mask;
+    if (s.rs >= (int32_t)(uint32_t)T.vals[h]) surv[atomicAdd(counters + 9, 1ull)] = s;
+}
+
+// ---- ungapped HSPs grouped by (ta, tb, strand) for the gapped kernel -----------------------------
+// group key = seed key without the diagonal; an empty slot (score < 0) sorts behind every group
+__global__ void k_hsp_keys(const Ungapped* __restrict__ U, int64_t n, KeyFmt F, uint64_t* __restrict__ keys,
+                           uint32_t* __restrict__ vals, unsigned long long* __restrict__ counters /* [7]=valid HSPs */) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    bool valid = false;
+    if (i < n) {
+        const Ungapped u = U[i];
+        valid = u.score >= 0;
+        const int gbits = F.total_bits - F.d_bits;
+        keys[i] = valid ? (((((uint64_t)(uint32_t)u.ta << F.tb_bits) | (uint64_t)(uint32_t)u.tb) << 1) | (uint64_t)u.minus)
+                        : (1ull << gbits);
+        vals[i] = (uint32_t)i;
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, valid);
+    if ((threadIdx.x & 31) == 0 && m) atomicAdd(counters + 7, (unsigned long long)__popc(m));
+}
+__global__ void k_hsp_gather(const Ungapped* __restrict__ U, const uint32_t* __restrict__ order,
+                             const uint64_t* __restrict__ keys, int64_t n, KeyFmt F, Ungapped* __restrict__ Us,
+                             uint32_t* __restrict__ gheads, unsigned long long* __restrict__ counters /* [5]=groups */) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Us[i] = U[order[i]];
+    const uint64_t k = keys[i];
+    if ((k >> (F.total_bits - F.d_bits)) == 0 && (i == 0 || keys[i - 1] != k)) gheads[atomicAdd(counters + 5, 1ull)] = (uint32_t)i;
+}
