@@ -46,6 +46,14 @@ int64_t rcq_ctx_launches(rcq_ctx* ctx);
  * 6 phase 2, 7 seed probe alone (also inside 1).  reset != 0 clears the accumulators after reading. */
 int rcq_ctx_stage_times(rcq_ctx* ctx, double ms[8], int64_t calls[8], int reset);
 
+/* ---- top-gene selection (host only, no device work).  Replaces TopGeneSelector.get_top_genes /
+ * get_top_gene_seqs (select_top_genes.py:108-127): per gene the maximum isoform coverage (starting
+ * from 0.0), the `top` genes by (coverage, gene id) descending — ties go to the larger gene id, as
+ * heapq.nlargest over tuples does — and keep[i] = 1 for every transcript of a selected gene (file
+ * order is the caller's).  Returns the number of kept transcripts, or a negative rcq_status. */
+int64_t rcq_top_gene_mask(const double* coverage, const int32_t* gene, int64_t n, int64_t top,
+                          uint8_t* keep);
+
 /* ---- kernels (1)+(2): pack + seed index.  Replaces makeblastdb per sample
  * (find_all_pairs.py:120-159 make_one_db/make_all_dbs -> BlastDBCache.makedb).
  * ascii[ascii_len]: nucleotide letters (no newlines) holding at least the selected transcripts;

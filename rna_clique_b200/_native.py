@@ -19,7 +19,7 @@ HSP_COLS = ["tx1", "tx2", "minus", "a0", "a1", "b0", "b1", "score2", "mismatch",
 # every symbol include/rcq.h declares (checked by tests/test_abi.py)
 SYMBOLS = [
     "rcq_last_error", "rcq_version", "rcq_ctx_create", "rcq_ctx_destroy", "rcq_ctx_sync", "rcq_ctx_stream",
-    "rcq_ctx_launches", "rcq_ctx_stage_times", "rcq_sample_create", "rcq_sample_free", "rcq_sample_info", "rcq_sample_download",
+    "rcq_ctx_launches", "rcq_ctx_stage_times", "rcq_top_gene_mask", "rcq_sample_create", "rcq_sample_free", "rcq_sample_info", "rcq_sample_download",
     "rcq_search_pair", "rcq_table_rows", "rcq_table_download", "rcq_table_free", "rcq_debug_last_hsps", "rcq_debug_keep_hsps",
     "rcq_length_adjustment", "rcq_evalue", "rcq_bitscore", "rcq_phase2_host", "rcq_phase2_tables",
     "rcq_table_flat_words", "rcq_table_flatten", "rcq_table_from_flat",
@@ -82,6 +82,8 @@ def lib():
         L.rcq_table_free.restype = None
         L.rcq_debug_last_hsps.argtypes = [vp, vp, i64]
         L.rcq_debug_last_hsps.restype = i64
+        L.rcq_top_gene_mask.argtypes = [vp, vp, i64, i64, vp]
+        L.rcq_top_gene_mask.restype = i64
         L.rcq_debug_keep_hsps.argtypes = [vp, C.c_int]
         L.rcq_debug_keep_hsps.restype = None
         L.rcq_length_adjustment.argtypes = [i64, i64, i64]
@@ -253,6 +255,17 @@ def search_pair(ctx: Context, s1: Sample, s2: Sample, evalue: float = 1e-99, top
     check(lib().rcq_search_pair(ctx.h, s1.h, s2.h, float(evalue), int(top_n), int(bool(keep_all)),
                                 C.byref(h), C.byref(st)))
     return Table(ctx, h, st.as_dict())
+
+
+def top_gene_mask(coverage, gene, top: int) -> np.ndarray:
+    """Indices (file order) of the transcripts whose gene is among the `top` genes (rcq_top_gene_mask)."""
+    coverage = np.ascontiguousarray(coverage, dtype=np.float64)
+    gene = np.ascontiguousarray(gene, dtype=np.int32)
+    keep = np.zeros(len(gene), dtype=np.uint8)
+    r = lib().rcq_top_gene_mask(coverage.ctypes.data, gene.ctypes.data, len(gene), int(top), keep.ctypes.data)
+    if r < 0:
+        check(int(r))
+    return np.flatnonzero(keep)
 
 
 def debug_keep_hsps(ctx: Context, on: bool = True) -> None:

@@ -296,16 +296,19 @@ __global__ void __launch_bounds__(32 * MZ_WARPS) k_minimizers(
             if (total) {
                 if (nbuf + total > MZ_BUF) flush();
                 int slot = nbuf + incl - cnt;
-#pragma unroll
-                for (int j = 0; j < 16; j++) {
-                    if (!((sel >> j) & 1u)) continue;
+                // one iteration per selected position of the lane (~2 of 16): dynamic j, so the hash is
+                // re-read from the exchange buffer and the flank words are picked by predicate
+                const uint32_t* myh = hx[wib] + lane * MZ_STRIDE;
+                for (uint32_t rest = sel; rest; rest &= rest - 1) {
+                    const int j = __ffs(rest) - 1;
                     const int32_t p = q0 + j;
                     const uint32_t o = (obits >> j) & 1u;
                     // flanks: 13 bases before (window offset 3+j) and after (window offset 32+j) the 16-mer
                     uint32_t Lf = 0x80000000u, Rf = 0x80000000u;
                     if (p >= RCQ_WIN && !((uint32_t)(M64 >> (3 + j)) & 0x1FFFu)) {
                         const int bo = 3 + j;
-                        Lf = (bo < 16 ? __funnelshift_r(a0, a1, 2 * (bo & 15)) : __funnelshift_r(a1, a2, 2 * (bo & 15))) & M26;
+                        const uint32_t lo = bo < 16 ? a0 : a1, hi = bo < 16 ? a1 : a2;
+                        Lf = __funnelshift_r(lo, hi, 2 * (bo & 15)) & M26;
                     }
                     if (p + RCQ_KMER + RCQ_WIN <= n && !((uint32_t)(M64 >> (32 + j)) & 0x1FFFu))
                         Rf = __funnelshift_r(a2, a3, 2 * j) & M26;
@@ -316,7 +319,7 @@ __global__ void __launch_bounds__(32 * MZ_WARPS) k_minimizers(
                         cr = (Lf >> 31) ? Lf : rc13(Lf);
                     }
                     if ((pbits >> j) & 1u) cl |= 0x40000000u;
-                    be[wib][slot] = ((unsigned long long)rcq_index_key(h[j]) << 32) |
+                    be[wib][slot] = ((unsigned long long)rcq_index_key(myh[j]) << 32) |
                                     ((unsigned long long)(off + p) << 1) | o;
                     bc[wib][slot] = ((uint64_t)cr << 32) | cl;
                     slot++;

@@ -150,7 +150,7 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
         CU(cudaMemsetAsync(ctr, 0, 16 * sizeof(int64_t), ctx->stream));
         stage_tic(ctx, 2);
         LAUNCH(ctx, k_diag_insert, grid_for(n_seeds, 256), 256, 0, seeds, n_seeds, F, T, slots, ctr);
-        LAUNCH(ctx, k_diag_first, grid_for(n_seeds, 128), 128, 0, seeds, slots, T, P, U1, ctr);
+        LAUNCH(ctx, k_diag_first, grid_for(2 * n_seeds, 128), 128, 0, seeds, slots, T, P, U1, ctr);
         LAUNCH(ctx, k_diag_survivors, grid_for(n_seeds, 256), 256, 0, seeds, n_seeds, F, T, surv, ctr);
         stage_toc(ctx, 2);
         RC(read_counters(ctx, 10));

@@ -71,7 +71,7 @@ __device__ __forceinline__ bool probe_keep(uint64_t cb, uint32_t oA, uint32_t wa
 // access of the kernel is therefore a sequential stream (16 B per entry of A and of B, 8 B per
 // surviving candidate); the per-entry lookup is a binary search in shared memory.
 #define PROBE_TA 1024
-#define PROBE_TB 1024
+#define PROBE_TB 1536   // > PROBE_TA: the B range of a tile is ~PROBE_TA entries plus two buckets of slack
 __global__ void __launch_bounds__(256) k_seed_probe(
     const uint64_t* __restrict__ idxA, const uint64_t* __restrict__ ctxA, int64_t nIdxA,
     const uint64_t* __restrict__ idxB, const uint64_t* __restrict__ ctxB, const uint32_t* __restrict__ dirB,
@@ -82,13 +82,15 @@ __global__ void __launch_bounds__(256) k_seed_probe(
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t a0 = (int64_t)blockIdx.x * PROBE_TA;
     const int64_t a1 = min(a0 + (int64_t)PROBE_TA, nIdxA);
+    // thread t owns the 4 CONSECUTIVE entries a0 + 4t .. +3 (ascending keys): one binary search for the
+    // first, the others continue the scan from where the previous one stopped
     uint32_t key[4], lowA[4], want[4];
     bool usable[4], have[4];
 #pragma unroll
     for (int r = 0; r < 4; r++) {
-        const int64_t e = a0 + threadIdx.x + 256 * r;
+        const int64_t e = a0 + 4 * threadIdx.x + r;
         have[r] = e < a1;
-        key[r] = 0; lowA[r] = 0; want[r] = 0; usable[r] = false;
+        key[r] = 0xFFFFFFFFu; lowA[r] = 0; want[r] = 0; usable[r] = false;
         if (have[r]) {
             const uint64_t ka = __ldg(idxA + e), ca = __ldg(ctxA + e);
             key[r] = (uint32_t)(ka >> 32);
@@ -106,19 +108,23 @@ __global__ void __launch_bounds__(256) k_seed_probe(
         // ---- count survivors of this chunk
         int pos[4];
         uint32_t cnt = 0, seen = 0;
-#pragma unroll
-        for (int r = 0; r < 4; r++) {
-            pos[r] = nb;
-            if (!have[r]) continue;
-            int lo = 0, hi = nb;                      // first entry of the chunk with key >= key[r]
+        {
+            int lo = 0, hi = have[0] ? nb : 0;        // first entry of the chunk with key >= key[0]
             while (lo < hi) {
                 const int mid = (lo + hi) >> 1;
-                if ((uint32_t)(sB[mid] >> 32) < key[r]) lo = mid + 1; else hi = mid;
+                if ((uint32_t)(sB[mid] >> 32) < key[0]) lo = mid + 1; else hi = mid;
             }
-            pos[r] = lo;
-            for (int k = lo; k < nb && (uint32_t)(sB[k] >> 32) == key[r]; k++) {
-                seen++;
-                cnt += probe_keep(sC[k], lowA[r] & 1u, want[r], usable[r]);
+            int k = have[0] ? lo : nb;
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                if (!have[r]) { pos[r] = nb; continue; }
+                while (k < nb && (uint32_t)(sB[k] >> 32) < key[r]) k++;
+                pos[r] = k;
+                // equal keys of A share the run of B: do not advance k past it
+                for (int q = k; q < nb && (uint32_t)(sB[q] >> 32) == key[r]; q++) {
+                    seen++;
+                    cnt += probe_keep(sC[q], lowA[r] & 1u, want[r], usable[r]);
+                }
             }
         }
         uint32_t incl = cnt;
@@ -401,18 +407,113 @@ __global__ void k_diag_insert(const Seed* __restrict__ seeds, int64_t n, KeyFmt 
     atomicMin(T.vals + h, ((unsigned long long)(uint32_t)s.rs << 32) | (unsigned long long)(uint32_t)e);
 }
 
-// thread per occupied slot (count read on the device): extend the leftmost seed of the diagonal
+// X-drop extension going forward from (pa, pb): best gain and the bases it spans (the right half of
+// ungapped_one; the left half is the same walk on the reverse-complement arenas)
+__device__ __forceinline__ void xdrop_fwd(const SeqArena& A, int64_t pa, const SeqArena& B, int64_t pb, int32_t lim,
+                                          int32_t& best, int32_t& ext, unsigned long long& work) {
+    int32_t sum = 0, k = 0;
+    best = 0; ext = 0;
+    bool stop = false;
+    while (k < lim && !stop) {
+        const uint32_t m = match32(A, pa + k, B, pb + k);
+        const int32_t v = min(32, lim - k);
+        int32_t i = 0;
+        while (i < v) {
+            const uint32_t rest = ~(m >> i);
+            int32_t z = rest ? (__ffs(rest) - 1) : 32;
+            if (z > v - i) z = v - i;
+            if (z) { sum += z; i += z; if (sum > best) { best = sum; ext = k + i; } }
+            if (i < v) {  // mismatch at bit i
+                sum -= 2; i++;
+                if (best - sum > RCQ_XDROP_UNGAPPED) { stop = true; break; }
+            }
+        }
+        k += i;
+    }
+    work += k;
+}
+// longest exact run inside [p0, p1) of diagonal d (earliest on ties), plus the runs touching both ends
+struct RunScan { int32_t best_len, best_s, lead, tail; };
+__device__ __forceinline__ RunScan run_scan(const SeqArena& A, int64_t ba, const SeqArena& B, int64_t bbd,
+                                            int32_t p0, int32_t p1) {
+    RunScan r;
+    int32_t run = 0;
+    r.best_len = 0; r.best_s = p0; r.lead = -1;
+    for (int32_t p = p0; p < p1; p += 32) {
+        const uint32_t m = match32(A, ba + p, B, bbd + p);
+        const int32_t v = min(32, p1 - p);
+        int32_t i = 0;
+        while (i < v) {
+            const uint32_t rest = ~(m >> i);
+            int32_t z = rest ? (__ffs(rest) - 1) : 32;
+            if (z > v - i) z = v - i;
+            run += z; i += z;
+            if (i < v) {
+                if (r.lead < 0) r.lead = run;
+                if (run > r.best_len) { r.best_len = run; r.best_s = p + i - run; }
+                run = 0; i++;
+            }
+        }
+    }
+    if (run > r.best_len) { r.best_len = run; r.best_s = p1 - run; }
+    if (r.lead < 0) r.lead = run;
+    r.tail = run;
+    return r;
+}
+
+// Two lanes per occupied slot (count read on the device): the even lane extends the leftmost seed of
+// the diagonal to the right, the odd lane to the left — as a forward walk on the reverse-complement
+// arenas, so both lanes run the same code — then each scans half of the HSP for its longest exact run.
 __global__ void __launch_bounds__(128) k_diag_first(const Seed* __restrict__ seeds, const uint32_t* __restrict__ slots,
                                                     DiagTable T, PairView P, Ungapped* __restrict__ U,
                                                     unsigned long long* __restrict__ counters /* [4]=bases [6]=diagonals */) {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 1;
+    const int role = threadIdx.x & 1;
     unsigned long long work = 0;
-    if (i < (int64_t)counters[6]) {
-        const uint32_t h = slots[i];
-        const Seed s = seeds[(uint32_t)T.vals[h]];
-        const Ungapped u = ungapped_one(s, P, work);
+    const bool on = i < (int64_t)counters[6];
+    uint32_t h = 0;
+    Seed s;
+    s.ta = s.tb = s.minus = s.rs = s.re = s.diag = 0;
+    int32_t best = 0, ext = 0, la = 0, lb = 0;
+    int64_t ba = 0, bb = 0;
+    if (on) {
+        h = slots[i];
+        s = seeds[(uint32_t)T.vals[h]];
+        ba = __ldg(P.offA + s.ta); bb = __ldg(P.offB + s.tb);
+        la = __ldg(P.lenA + s.ta); lb = __ldg(P.lenB + s.tb);
+        const int32_t d = s.diag;
+        if (role == 0) {
+            const SeqArena& B = s.minus ? P.Br : P.Bf;
+            xdrop_fwd(P.Af, ba + s.re, B, bb + s.re + d, min(la - s.re, lb - s.re - d), best, ext, work);
+        } else {
+            // bases rs-1, rs-2, ... of A and rs-1+d, ... of B, read forward on the opposite strands
+            const SeqArena& Bo = s.minus ? P.Bf : P.Br;
+            xdrop_fwd(P.Ar, ba + (la - s.rs), Bo, bb + (lb - s.rs - d), min(s.rs, s.rs + d), best, ext, work);
+        }
+    }
+    const int32_t obest = __shfl_xor_sync(0xffffffffu, best, 1), oext = __shfl_xor_sync(0xffffffffu, ext, 1);
+    const int32_t a1 = s.re + (role == 0 ? ext : oext), a0 = s.rs - (role == 0 ? oext : ext);
+    const int32_t score = (s.re - s.rs) + best + obest;
+    const int32_t mid = a0 + ((a1 - a0) >> 1);
+    RunScan r;
+    r.best_len = 0; r.best_s = 0; r.lead = 0; r.tail = 0;
+    if (on) {
+        const SeqArena& B = s.minus ? P.Br : P.Bf;
+        r = run_scan(P.Af, ba, B, bb + s.diag, role == 0 ? a0 : mid, role == 0 ? mid : a1);
+        work += (role == 0 ? mid - a0 : a1 - mid);
+    }
+    RunScan y;
+    y.best_len = __shfl_xor_sync(0xffffffffu, r.best_len, 1); y.best_s = __shfl_xor_sync(0xffffffffu, r.best_s, 1);
+    y.lead = __shfl_xor_sync(0xffffffffu, r.lead, 1); y.tail = __shfl_xor_sync(0xffffffffu, r.tail, 1);
+    if (on && role == 0) {
+        int32_t bl = r.best_len, bs = r.best_s;                  // left half, then the run across the middle, then the right half
+        if (r.tail + y.lead > bl) { bl = r.tail + y.lead; bs = mid - r.tail; }
+        if (y.best_len > bl) { bl = y.best_len; bs = y.best_s; }
+        Ungapped u;
+        u.ta = s.ta; u.tb = s.tb; u.minus = s.minus; u.diag = s.diag; u.a0 = a0; u.a1 = a1;
+        u.score = score; u.i0 = bs + bl / 2;
         U[i] = u;
-        T.vals[h] = (unsigned long long)(uint32_t)max(u.a1, s.rs + 1);   // end of the diagonal's first HSP
+        T.vals[h] = (unsigned long long)(uint32_t)max(a1, s.rs + 1);   // end of the diagonal's first HSP
     }
     for (int o = 16; o; o >>= 1) work += __shfl_down_sync(0xffffffffu, work, o);
     if ((threadIdx.x & 31) == 0 && work) atomicAdd(counters + 4, work);
