@@ -25,6 +25,8 @@
 #define FULL 0xffffffffu
 #define RCQ_RING 128            // diagonals per shared-memory row
 #define RCQ_XDROP_OFFSET 19     // floor((108 + 1) / 6) + 1
+#define RCQ_STAGE_MAX 4096      // longest transcript staged in shared memory by the fast path
+#define RCQ_STAGE_W (RCQ_STAGE_MAX / 16 + 4)
 
 struct ExtRes { int32_t score2, qi, sj, mism, gw; };  // gw = gaps<<17 | gapopen<<3 | slid<<2 | entry op
 
@@ -170,24 +172,35 @@ __device__ bool greedy_extend(const SeqArena Q, int64_t qpos, int32_t qn, const 
 // 16 bases per first slide step from two 32-bit words (one funnel shift, no 64-bit compress), 32-bit
 // offsets from per-extension base pointers, dead cells stored as NEG with two sentinels either side
 // of every wave so the three-way max needs no range checks.
-__device__ __forceinline__ uint32_t fetch16(const uint32_t* __restrict__ b, int32_t x) {
+// Sequence accessors of the fast path: words of one strand of one transcript, either straight from
+// the arena (read-only cache) or from the warp's staged copy in shared memory (LDS, 32-bit addresses).
+struct SeqGlobal {
+    const uint32_t* b;
+    __device__ __forceinline__ uint32_t w(int32_t i) const { return __ldg(b + i); }
+};
+struct SeqShared {
+    const uint32_t* b;
+    __device__ __forceinline__ uint32_t w(int32_t i) const { return b[i]; }
+};
+template <typename SEQ>
+__device__ __forceinline__ uint32_t fetch16(const SEQ& q, int32_t x) {
     const int32_t w = x >> 4;
-    return __funnelshift_r(__ldg(b + w), __ldg(b + w + 1), (x & 15) * 2);
+    return __funnelshift_r(q.w(w), q.w(w + 1), (x & 15) * 2);
 }
-__device__ __forceinline__ int32_t run16(const uint32_t* __restrict__ Qb, int32_t xq,
-                                         const uint32_t* __restrict__ Sb, int32_t xs) {
-    uint32_t d = fetch16(Qb, xq) ^ fetch16(Sb, xs);
+template <typename SEQ>
+__device__ __forceinline__ int32_t run16(const SEQ& Q, int32_t xq, const SEQ& S, int32_t xs) {
+    uint32_t d = fetch16(Q, xq) ^ fetch16(S, xs);
     d = (d | (d >> 1)) & 0x55555555u;
     return d ? ((__ffs(d) - 1) >> 1) : 16;
 }
-__device__ __forceinline__ int32_t coop_slide16(const uint32_t* __restrict__ Qb, int32_t xq,
-                                                const uint32_t* __restrict__ Sb, int32_t xs, int32_t lim) {
+template <typename SEQ>
+__device__ __forceinline__ int32_t coop_slide16(const SEQ& Q, int32_t xq, const SEQ& S, int32_t xs, int32_t lim) {
     const int lane = threadIdx.x & 31;
     int32_t base = 0;
     while (base < lim) {
         const int32_t o = base + 16 * lane;
         int32_t z = 0;
-        if (o < lim) z = min(run16(Qb, xq + o, Sb, xs + o), lim - o);
+        if (o < lim) z = min(run16(Q, xq + o, S, xs + o), lim - o);
         const unsigned stop = __ballot_sync(FULL, z < 16);
         if (stop) {
             const int src = __ffs(stop) - 1;
@@ -198,17 +211,18 @@ __device__ __forceinline__ int32_t coop_slide16(const uint32_t* __restrict__ Qb,
     return lim;
 }
 
-// rows: 6 arrays of rowlen int32.  RING: index k & (RCQ_RING-1); else index k + qn + 2 (rowlen >= qn+sn+5).
-template <bool RING>
-__device__ bool greedy_fast(const uint32_t* __restrict__ Qb, int32_t qo, int32_t qn,
-                            const uint32_t* __restrict__ Sb, int32_t so, int32_t sn, int32_t* rows,
+// rows: R (2 x rowlen int32) followed by MG (2 x rowlen uint64: mismatches | gap word << 32).
+// RING: index k & (RCQ_RING-1); else index k + qn + 2 (rowlen >= qn+sn+5).
+template <bool RING, typename SEQ>
+__device__ bool greedy_fast(const SEQ Q, int32_t qo, int32_t qn, const SEQ S, int32_t so, int32_t sn, int32_t* rows,
                             int32_t rowlen, ExtRes* res, unsigned long long* steps) {
     const int lane = threadIdx.x & 31;
-    int32_t* Rr = rows; int32_t* Mr = rows + 2 * rowlen; int32_t* Gr = rows + 4 * rowlen;
+    int32_t* Rr = rows;
+    uint2* MGr = (uint2*)(rows + 2 * rowlen);
 #define IX(k) (RING ? ((k) & (RCQ_RING - 1)) : ((k) + qn + 2))
-    const int32_t i0 = coop_slide16(Qb, qo, Sb, so, min(qn, sn));
-    unsigned long long nstep = (lane == 0) ? (unsigned long long)(i0 + 1) : 0ull;
-    if (lane == 0) { Rr[IX(0)] = i0; Mr[IX(0)] = 0; Gr[IX(0)] = 0; }
+    const int32_t i0 = coop_slide16(Q, qo, S, so, min(qn, sn));
+    uint32_t nstep = (lane == 0) ? (uint32_t)(i0 + 1) : 0u;
+    if (lane == 0) { Rr[IX(0)] = i0; MGr[IX(0)] = make_uint2(0u, 0u); }
     if (lane >= 1 && lane <= 4) Rr[IX(lane <= 2 ? -lane : lane - 2)] = NEG;
     int32_t bS = (lane == 0) ? 2 * i0 : NEG, bD = 0, bK = 0, bI = i0, bM = 0, bG = 0;
     int32_t gb = 2 * i0;
@@ -223,15 +237,18 @@ __device__ bool greedy_fast(const uint32_t* __restrict__ Qb, int32_t qo, int32_t
         const int32_t klo = max(L - 1, -qn), khi = min(U + 1, sn);
         if (RING && khi - klo + 5 > RCQ_RING) { ok = false; break; }
         const int32_t xcut = tref - RCQ_XDROP_GAPPED2 + 6 * d;   // alive iff 2*row + k >= xcut
+        const int32_t d6 = 6 * d;
         int32_t nL = 1 << 28, nU = -(1 << 28), wbest = NEG, ubmax = NEG;
         for (int32_t kb = klo; kb <= khi; kb += 32) {
             const int32_t k = kb + lane;
             const bool active = k <= khi;
-            int32_t bi = NEG, op = 0, rowmax = 0, e = NEG, mm = 0, gw = 0, lim = 0;
+            const int32_t ix = IX(k);
+            int32_t bi = NEG, op = 0, rowmax = 0, e = NEG, lim = 0;
+            uint32_t mm = 0, gw = 0;
             bool cont = false;
             if (active) {
                 rowmax = min(qn, sn - k);
-                int32_t c0 = Rr[p + IX(k)] + 1, c1 = Rr[p + IX(k + 1)] + 1, c2 = Rr[p + IX(k - 1)];
+                int32_t c0 = Rr[p + ix] + 1, c1 = Rr[p + IX(k + 1)] + 1, c2 = Rr[p + IX(k - 1)];
                 if (c0 > rowmax) c0 = NEG;
                 if (c1 > rowmax) c1 = NEG;
                 if (c2 > rowmax) c2 = NEG;
@@ -242,13 +259,14 @@ __device__ bool greedy_fast(const uint32_t* __restrict__ Qb, int32_t qo, int32_t
             }
             if (bi >= 0) {
                 const int32_t src = k + (op == 1) - (op == 2);
-                mm = Mr[p + IX(src)];
-                const int32_t g = Gr[p + IX(src)];
-                if (op == 0) { mm++; gw = g & ~7; }
-                else gw = ((g & ~7) | op) + (1 << 17) + (((g & 7) != op) ? 8 : 0);
+                const uint2 mg = MGr[p + IX(src)];
+                mm = mg.x;
+                const uint32_t g = mg.y;
+                if (op == 0) { mm++; gw = g & ~7u; }
+                else gw = ((g & ~7u) | (uint32_t)op) + (1u << 17) + (((g & 7u) != (uint32_t)op) ? 8u : 0u);
                 lim = rowmax - bi;
                 int32_t z = 0;
-                if (lim > 0) z = min(run16(Qb, qo + bi, Sb, so + bi + k), lim);
+                if (lim > 0) z = min(run16(Q, qo + bi, S, so + bi + k), lim);
                 nstep += z + 1;
                 e = bi + z;
                 cont = (z == 16 && lim > 16);
@@ -258,20 +276,21 @@ __device__ bool greedy_fast(const uint32_t* __restrict__ Qb, int32_t qo, int32_t
                 const int sl = __ffs(more) - 1;
                 more &= more - 1;
                 const int32_t e2 = __shfl_sync(FULL, e, sl), k2 = __shfl_sync(FULL, k, sl), l2 = __shfl_sync(FULL, lim, sl);
-                const int32_t extra = coop_slide16(Qb, qo + e2, Sb, so + e2 + k2, l2 - 16);
+                const int32_t extra = coop_slide16(Q, qo + e2, S, so + e2 + k2, l2 - 16);
                 if (lane == sl) { e += extra; nstep += extra; }
             }
             if (active) {
                 if (bi >= 0) {
-                    if (e > bi) gw |= 4;
-                    Rr[c + IX(k)] = e; Mr[c + IX(k)] = mm; Gr[c + IX(k)] = gw;
-                    const int32_t sc = 2 * e + k - 6 * d;
+                    if (e > bi) gw |= 4u;
+                    Rr[c + ix] = e;
+                    MGr[c + ix] = make_uint2(mm, gw);
+                    const int32_t sc = 2 * e + k - d6;
                     wbest = max(wbest, sc);
                     nL = min(nL, k); nU = max(nU, k);
-                    ubmax = max(ubmax, 2 * rowmax + k - 6 * d);
-                    if (sc > bS) { bS = sc; bD = d; bK = k; bI = e; bM = mm; bG = gw; }
+                    ubmax = max(ubmax, 2 * rowmax + k - d6);
+                    if (sc > bS) { bS = sc; bD = d; bK = k; bI = e; bM = (int32_t)mm; bG = (int32_t)gw; }
                 } else {
-                    Rr[c + IX(k)] = NEG;
+                    Rr[c + ix] = NEG;
                 }
             }
         }
@@ -289,7 +308,7 @@ __device__ bool greedy_fast(const uint32_t* __restrict__ Qb, int32_t qo, int32_t
         if (ubmax <= gb) break;      // nothing still alive can beat the best end point
     }
 #undef IX
-    for (int o = 16; o; o >>= 1) nstep += __shfl_down_sync(FULL, nstep, o);
+    nstep = __reduce_add_sync(FULL, nstep);
     if (lane == 0) *steps += nstep;
     if (!ok) return false;
     uint64_t key = 0;
@@ -326,26 +345,47 @@ __device__ __forceinline__ void scratch_release(const ScratchPool& sp, int32_t s
     if ((threadIdx.x & 31) == 0) { __threadfence(); atomicExch(sp.locks + s, 0u); }
 }
 
+// Fallback of the fast path on global rows (rare: a wave wider than the ring); kept out of line so the
+// hot loop stays small in the instruction cache.
+template <typename SEQ>
+__device__ __noinline__ void greedy_fast_wide(const SEQ Q, int32_t qo, int32_t qn, const SEQ S, int32_t so, int32_t sn,
+                                              const ScratchPool sp, ExtRes* r, unsigned long long* steps) {
+    const int32_t slot = scratch_acquire(sp);
+    greedy_fast<false, SEQ>(Q, qo, qn, S, so, sn, sp.rows + slot * sp.per_slot, qn + sn + 5, r, steps);
+    scratch_release(sp, slot);
+}
+
+// One extension.  MASKED: general path on the arenas (mask words consulted).  Otherwise the fast path,
+// on the warp's staged copies (stQ/stS != nullptr: word pointers into shared memory) or on the arenas.
 template <bool MASKED>
-__device__ __forceinline__ void extend(const SeqArena Q, int64_t qpos, int32_t qn, const SeqArena S,
-                                       int64_t spos, int32_t sn, int32_t* ring, const ScratchPool& sp, ExtRes* r,
+__device__ __forceinline__ void extend(const SeqArena Q, int64_t qbase, int32_t qrel, int32_t qn, const uint32_t* stQ,
+                                       const SeqArena S, int64_t sbase, int32_t srel, int32_t sn, const uint32_t* stS,
+                                       int32_t* ring, const ScratchPool& sp, ExtRes* r,
                                        unsigned long long* steps, unsigned long long* retries) {
     if (MASKED) {
-        if (!greedy_extend<true>(Q, qpos, qn, S, spos, sn, ring, RCQ_RING, r, steps)) {
+        if (!greedy_extend<true>(Q, qbase + qrel, qn, S, sbase + srel, sn, ring, RCQ_RING, r, steps)) {
             if ((threadIdx.x & 31) == 0) (*retries)++;
             const int32_t slot = scratch_acquire(sp);
-            greedy_extend<false>(Q, qpos, qn, S, spos, sn, sp.rows + slot * sp.per_slot, qn + sn + 3, r, steps);
+            greedy_extend<false>(Q, qbase + qrel, qn, S, sbase + srel, sn, sp.rows + slot * sp.per_slot, qn + sn + 3, r, steps);
             scratch_release(sp, slot);
         }
     } else {
-        const uint32_t* Qb = Q.bits + (qpos >> 4);
-        const uint32_t* Sb = S.bits + (spos >> 4);
-        const int32_t qo = (int32_t)(qpos & 15), so = (int32_t)(spos & 15);
-        if (!greedy_fast<true>(Qb, qo, qn, Sb, so, sn, ring, RCQ_RING, r, steps)) {
-            if ((threadIdx.x & 31) == 0) (*retries)++;
-            const int32_t slot = scratch_acquire(sp);
-            greedy_fast<false>(Qb, qo, qn, Sb, so, sn, sp.rows + slot * sp.per_slot, qn + sn + 5, r, steps);
-            scratch_release(sp, slot);
+        // transcripts start on 32-base boundaries, so word offsets inside a transcript are qrel >> 4
+        const int32_t qo = qrel & 15, so = srel & 15;
+        if (stQ) {
+            SeqShared q, t;
+            q.b = stQ + (qrel >> 4); t.b = stS + (srel >> 4);
+            if (!greedy_fast<true, SeqShared>(q, qo, qn, t, so, sn, ring, RCQ_RING, r, steps)) {
+                if ((threadIdx.x & 31) == 0) (*retries)++;
+                greedy_fast_wide<SeqShared>(q, qo, qn, t, so, sn, sp, r, steps);
+            }
+        } else {
+            SeqGlobal q, t;
+            q.b = Q.bits + ((qbase + qrel) >> 4); t.b = S.bits + ((sbase + srel) >> 4);
+            if (!greedy_fast<true, SeqGlobal>(q, qo, qn, t, so, sn, ring, RCQ_RING, r, steps)) {
+                if ((threadIdx.x & 31) == 0) (*retries)++;
+                greedy_fast_wide<SeqGlobal>(q, qo, qn, t, so, sn, sp, r, steps);
+            }
         }
     }
     __syncwarp();
@@ -366,14 +406,18 @@ __device__ __forceinline__ bool ung_before(const Ungapped& x, const Ungapped& y)
 // U is the HSP list sorted by group (empty slots, score < 0, sort behind every group);
 // keys[] are the sorted group keys of U (k_hsp_keys): ta | tb | strand.
 template <bool MASKED>
-__global__ void __launch_bounds__(128, 6) k_gapped(const Ungapped* __restrict__ U,
+__global__ void __launch_bounds__(128, 5) k_gapped(const Ungapped* __restrict__ U,
                                                 const uint64_t* __restrict__ keys, int64_t n, KeyFmt F,
                                                 const uint32_t* __restrict__ heads, int64_t n_groups,
                                                 PairView P, Gapped* __restrict__ out, ScratchPool sp,
                                                 unsigned long long* __restrict__ ctr /* [0]=next group [1]=cells [2]=retries [3]=n gapped */) {
     const int lane = threadIdx.x & 31;
-    __shared__ int32_t ring_all[4][6 * RCQ_RING];
+    __shared__ __align__(16) int32_t ring_all[4][6 * RCQ_RING];
+    // staged strands of the group's two transcripts (fast path): A forward, A reverse complement, B on the
+    // hit strand, B on the opposite strand; RCQ_STAGE_W words each (transcripts up to RCQ_STAGE_MAX bases)
+    __shared__ uint32_t stage_all[MASKED ? 1 : 4][MASKED ? 1 : 4 * RCQ_STAGE_W];
     int32_t* ring = ring_all[threadIdx.x >> 5];
+    uint32_t* stage = stage_all[MASKED ? 0 : (threadIdx.x >> 5)];
     unsigned long long cells = 0, retries = 0, produced = 0;
     while (true) {
         unsigned long long g = 0;
@@ -389,6 +433,20 @@ __global__ void __launch_bounds__(128, 6) k_gapped(const Ungapped* __restrict__ 
         const int64_t oa = __ldg(P.offA + ta), ob = __ldg(P.offB + tb);
         const int32_t la = __ldg(P.lenA + ta), lb = __ldg(P.lenB + tb);
         const SeqArena Bs = minus ? P.Br : P.Bf, Bo = minus ? P.Bf : P.Br;
+        const bool staged = !MASKED && la <= RCQ_STAGE_MAX && lb <= RCQ_STAGE_MAX;
+        if (staged) {
+            __syncwarp();
+            const int32_t wa = (la + 15) / 16 + 2, wb = (lb + 15) / 16 + 2;
+            const uint32_t* ga = P.Af.bits + (oa >> 4); const uint32_t* gr = P.Ar.bits + (oa >> 4);
+            const uint32_t* gs = Bs.bits + (ob >> 4); const uint32_t* go = Bo.bits + (ob >> 4);
+            for (int32_t w = lane; w < wa; w += 32) { stage[w] = __ldg(ga + w); stage[RCQ_STAGE_W + w] = __ldg(gr + w); }
+            for (int32_t w = lane; w < wb; w += 32) { stage[2 * RCQ_STAGE_W + w] = __ldg(gs + w); stage[3 * RCQ_STAGE_W + w] = __ldg(go + w); }
+            __syncwarp();
+        }
+        const uint32_t* stAf = staged ? stage : nullptr;
+        const uint32_t* stAr = staged ? stage + RCQ_STAGE_W : nullptr;
+        const uint32_t* stBs = staged ? stage + 2 * RCQ_STAGE_W : nullptr;
+        const uint32_t* stBo = staged ? stage + 3 * RCQ_STAGE_W : nullptr;
         int32_t count = 0;
         Ungapped last; last.score = 0x7fffffff; last.diag = -0x7fffffff; last.a0 = -1; last.a1 = -1;
         bool have_last = false;
@@ -424,8 +482,8 @@ __global__ void __launch_bounds__(128, 6) k_gapped(const Ungapped* __restrict__ 
             if (__any_sync(FULL, contained)) continue;
             const int32_t i0 = cur.i0, j0 = i0 + cur.diag;
             ExtRes L, R;
-            extend<MASKED>(P.Ar, oa + (la - 1 - i0), i0 + 1, Bo, ob + (lb - 1 - j0), j0 + 1, ring, sp, &L, &cells, &retries);
-            extend<MASKED>(P.Af, oa + i0 + 1, la - i0 - 1, Bs, ob + j0 + 1, lb - j0 - 1, ring, sp, &R, &cells, &retries);
+            extend<MASKED>(P.Ar, oa, la - 1 - i0, i0 + 1, stAr, Bo, ob, lb - 1 - j0, j0 + 1, stBo, ring, sp, &L, &cells, &retries);
+            extend<MASKED>(P.Af, oa, i0 + 1, la - i0 - 1, stAf, Bs, ob, j0 + 1, lb - j0 - 1, stBs, ring, sp, &R, &cells, &retries);
             Gapped gp;
             gp.ta = ta; gp.tb = tb; gp.minus = minus;
             gp.a0 = i0 + 1 - L.qi; gp.a1 = i0 + 1 + R.qi;
