@@ -219,7 +219,7 @@ __device__ bool greedy_fast(const SEQ Q, int32_t qo, int32_t qn, const SEQ S, in
     const int lane = threadIdx.x & 31;
     int32_t* Rr = rows;
     uint2* MGr = (uint2*)(rows + 2 * rowlen);
-#define IX(k) (RING ? ((k) & (RCQ_RING - 1)) : ((k) + qn + 2))
+#define IX(k) (RING ? ((k) + RCQ_RING / 2) : ((k) + qn + 2))   // RING: diagonals -62 .. 61 in place, no wrap
     const int32_t i0 = coop_slide16(Q, qo, S, so, min(qn, sn));
     uint32_t nstep = (lane == 0) ? (uint32_t)(i0 + 1) : 0u;
     if (lane == 0) { Rr[IX(0)] = i0; MGr[IX(0)] = make_uint2(0u, 0u); }
@@ -235,7 +235,7 @@ __device__ bool greedy_fast(const SEQ Q, int32_t qo, int32_t qn, const SEQ S, in
         int32_t tref = __shfl_sync(FULL, Tl, (d - RCQ_XDROP_OFFSET) & 31);
         if (d < RCQ_XDROP_OFFSET) tref = 0;
         const int32_t klo = max(L - 1, -qn), khi = min(U + 1, sn);
-        if (RING && khi - klo + 5 > RCQ_RING) { ok = false; break; }
+        if (RING && (klo - 2 < -RCQ_RING / 2 || khi + 2 >= RCQ_RING / 2)) { ok = false; break; }
         const int32_t xcut = tref - RCQ_XDROP_GAPPED2 + 6 * d;   // alive iff 2*row + k >= xcut
         const int32_t d6 = 6 * d;
         int32_t nL = 1 << 28, nU = -(1 << 28), wbest = NEG, ubmax = NEG;
