@@ -46,8 +46,10 @@ def parse_args():
 
 
 def workload_name(a):
+    cfg = {(3, 5000, 2000): "BASELINE.json configs[0]", (10, 60000, 50000): "BASELINE.json configs[1]",
+           (30, 100000, 50000): "BASELINE.json configs[2]"}.get((a.taxa, a.count, a.top), "custom size")
     return (f"{a.taxa} simulated samples x {a.count} transcripts, top_genes={a.top} "
-            f"(BASELINE.json configs[1]; birth-death tree, JC/HKY85 mu=0.01, seed {a.seed})")
+            f"({cfg}; birth-death tree, JC/HKY85 mu=0.01, seed {a.seed})")
 
 
 def equiv_cells(lengths):
@@ -200,8 +202,11 @@ def main():
     torch.cuda.set_device(local)
     dist = None
     if world > 1:
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"   # NCCL_DEBUG=VERSION prints a banner on stdout; stdout carries one JSON line
+        # stdout carries exactly one JSON line: NCCL's version banner (NCCL_DEBUG=VERSION) and any other
+        # NCCL logging go to stderr
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            os.environ.pop("NCCL_DEBUG")
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         import torch.distributed as dist_mod
         dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local))
         dist = dist_mod

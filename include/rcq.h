@@ -143,6 +143,14 @@ int rcq_phase2_tables(rcq_ctx* ctx, int32_t n_samples, int64_t stride, int32_t n
                       int32_t sample_count, int64_t* nident_sum, int64_t* denom_sum,
                       uint8_t* valid, int64_t counts[5]);
 
+/* ---- multi-GPU: a built sample as one flat device buffer.  With N ranks each rank builds the samples
+ * k = rank mod N (kernels 1+2 are not repeated on every GPU) and broadcasts them over NCCL/NVLink; the
+ * receivers import the buffer.  meta: [0]=n_seq [1]=total bases [2]=arena bases [3]=#index entries
+ * [4]=#masked bases [5]=longest transcript [6]=#genes [7]=bytes of the flat buffer. */
+int rcq_sample_meta(const rcq_sample* s, int64_t meta[8]);
+int rcq_sample_export(rcq_ctx* ctx, const rcq_sample* s, uint8_t* dev_flat);
+int rcq_sample_import(rcq_ctx* ctx, const int64_t meta[8], const uint8_t* dev_flat, rcq_sample** out);
+
 /* ---- multi-GPU exchange: serialise a table to / from a flat int32 buffer that the
  * host layer all-gathers with NCCL (torch.distributed) — device pointers in, device pointers out. */
 int64_t rcq_table_flat_words(const rcq_table* t);

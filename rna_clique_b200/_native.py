@@ -22,7 +22,7 @@ SYMBOLS = [
     "rcq_ctx_launches", "rcq_ctx_stage_times", "rcq_top_gene_mask", "rcq_sample_create", "rcq_sample_free", "rcq_sample_info", "rcq_sample_download",
     "rcq_search_pair", "rcq_table_rows", "rcq_table_download", "rcq_table_free", "rcq_debug_last_hsps", "rcq_debug_keep_hsps",
     "rcq_length_adjustment", "rcq_evalue", "rcq_bitscore", "rcq_phase2_host", "rcq_phase2_tables",
-    "rcq_table_flat_words", "rcq_table_flatten", "rcq_table_from_flat",
+    "rcq_table_flat_words", "rcq_table_flatten", "rcq_table_from_flat", "rcq_sample_meta", "rcq_sample_export", "rcq_sample_import",
 ]
 
 
@@ -94,6 +94,9 @@ def lib():
         L.rcq_bitscore.restype = dbl
         L.rcq_phase2_host.argtypes = [vp, i32, i64, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, vp, vp, vp, vp]
         L.rcq_phase2_tables.argtypes = [vp, i32, i64, i32, vp, vp, vp, i32, vp, vp, vp, vp]
+        L.rcq_sample_meta.argtypes = [vp, vp]
+        L.rcq_sample_export.argtypes = [vp, vp, vp]
+        L.rcq_sample_import.argtypes = [vp, vp, vp, C.POINTER(vp)]
         L.rcq_table_flat_words.argtypes = [vp]
         L.rcq_table_flat_words.restype = i64
         L.rcq_table_flatten.argtypes = [vp, vp, vp]
@@ -195,6 +198,25 @@ class Sample:
         info = np.zeros(5, dtype=np.int64)
         check(lib().rcq_sample_info(self.h, info.ctypes.data))
         self.n_seq, self.total, self.arena, self.n_index, self.n_masked = (int(x) for x in info)
+
+    def meta(self) -> np.ndarray:
+        m = np.zeros(8, dtype=np.int64)
+        check(lib().rcq_sample_meta(self.h, m.ctypes.data))
+        return m
+
+    def export_flat(self, dev_ptr: int) -> None:
+        """Copies every device array of the sample into the flat device buffer at dev_ptr (meta()[7] bytes)."""
+        check(lib().rcq_sample_export(self.ctx.h, self.h, dev_ptr))
+
+    @classmethod
+    def import_flat(cls, ctx: "Context", meta: np.ndarray, dev_ptr: int, name: str = "") -> "Sample":
+        meta = np.ascontiguousarray(meta, dtype=np.int64)
+        h = C.c_void_p()
+        check(lib().rcq_sample_import(ctx.h, meta.ctypes.data, dev_ptr, C.byref(h)))
+        s = cls.__new__(cls)
+        s.ctx, s.name, s.h, s._keep = ctx, name, h, None
+        s.n_seq, s.total, s.arena, s.n_index, s.n_masked = (int(x) for x in meta[:5])
+        return s
 
     def download(self):
         fwd = np.zeros(self.arena // 16, dtype=np.uint32)

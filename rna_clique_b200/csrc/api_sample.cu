@@ -194,6 +194,73 @@ int rcq_sample_info(const rcq_sample* s, int64_t info[5]) {
     return 0;
 }
 
+// ---- multi-GPU: a built sample as one flat device buffer (the rank that built it broadcasts it) ----
+// meta: [0]=n_seq [1]=total [2]=arena [3]=n_index [4]=n_masked [5]=max_len [6]=n_genes [7]=flat bytes
+struct FlatPart { void** ptr; int64_t bytes; };
+static int flat_parts(rcq_sample* s, FlatPart* out) {
+    const int64_t w = s->arena / 16 * 4, m = s->arena / 32 * 4, n = (int64_t)s->n_seq * 4;
+    int k = 0;
+    out[k++] = {(void**)&s->fwd, w}; out[k++] = {(void**)&s->rc, w};
+    out[k++] = {(void**)&s->mask, m}; out[k++] = {(void**)&s->mask_rc, m};
+    out[k++] = {(void**)&s->sel, m}; out[k++] = {(void**)&s->blk2tx, m};
+    out[k++] = {(void**)&s->off, n}; out[k++] = {(void**)&s->len, n}; out[k++] = {(void**)&s->gene, n};
+    out[k++] = {(void**)&s->iso, n}; out[k++] = {(void**)&s->gidx, n}; out[k++] = {(void**)&s->ol, 2 * n};
+    out[k++] = {(void**)&s->index, s->n_index * 8}; out[k++] = {(void**)&s->fctx, s->n_index * 8};
+    out[k++] = {(void**)&s->dir, ((1ll << RCQ_DIRBITS) + 1) * 4};
+    return k;
+}
+static inline int64_t pad256(int64_t b) { return (b + 255) & ~255ll; }
+
+int rcq_sample_meta(const rcq_sample* s, int64_t meta[8]) {
+    if (!s || !meta) return rcq_fail(RCQ_ERR_ARG, "rcq_sample_meta: bad argument");
+    meta[0] = s->n_seq; meta[1] = s->total; meta[2] = s->arena; meta[3] = s->n_index; meta[4] = s->n_masked;
+    meta[5] = s->max_len; meta[6] = s->n_genes;
+    FlatPart parts[16];
+    const int k = flat_parts(const_cast<rcq_sample*>(s), parts);
+    int64_t tot = 0;
+    for (int i = 0; i < k; i++) tot += pad256(parts[i].bytes);
+    meta[7] = tot;
+    return 0;
+}
+
+int rcq_sample_export(rcq_ctx* ctx, const rcq_sample* s, uint8_t* dev_flat) {
+    if (!ctx || !s || !dev_flat) return rcq_fail(RCQ_ERR_ARG, "rcq_sample_export: bad argument");
+    CU(cudaSetDevice(ctx->device));
+    FlatPart parts[16];
+    const int k = flat_parts(const_cast<rcq_sample*>(s), parts);
+    int64_t at = 0;
+    for (int i = 0; i < k; i++) {
+        if (parts[i].bytes) CU(cudaMemcpyAsync(dev_flat + at, *parts[i].ptr, parts[i].bytes, cudaMemcpyDeviceToDevice, ctx->stream));
+        at += pad256(parts[i].bytes);
+    }
+    CU(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int rcq_sample_import(rcq_ctx* ctx, const int64_t meta[8], const uint8_t* dev_flat, rcq_sample** out) {
+    if (!ctx || !meta || !dev_flat || !out) return rcq_fail(RCQ_ERR_ARG, "rcq_sample_import: bad argument");
+    CU(cudaSetDevice(ctx->device));
+    rcq_sample* s = new rcq_sample();
+    s->ctx = ctx;
+    s->n_seq = (int32_t)meta[0]; s->total = meta[1]; s->arena = meta[2]; s->n_index = meta[3]; s->n_masked = meta[4];
+    s->max_len = (int32_t)meta[5]; s->n_genes = (int32_t)meta[6];
+    FlatPart parts[16];
+    const int k = flat_parts(s, parts);
+    int64_t at = 0;
+    for (int i = 0; i < k; i++) {
+        char* p = nullptr;
+        int rc = dalloc(ctx, &p, parts[i].bytes);
+        if (rc) { rcq_sample_free(s); return rc; }
+        *parts[i].ptr = p;
+        if (parts[i].bytes) CU(cudaMemcpyAsync(p, dev_flat + at, parts[i].bytes, cudaMemcpyDeviceToDevice, ctx->stream));
+        at += pad256(parts[i].bytes);
+    }
+    if (at != meta[7]) { rcq_sample_free(s); return rcq_fail(RCQ_ERR_ARG, "rcq_sample_import: meta does not match the flat size"); }
+    CU(cudaStreamSynchronize(ctx->stream));
+    *out = s;
+    return 0;
+}
+
 int rcq_sample_download(const rcq_sample* s, uint32_t* fwd, uint32_t* rc, uint32_t* mask,
                         int64_t* arena_off, uint64_t* index) {
     if (!s) return rcq_fail(RCQ_ERR_ARG, "rcq_sample_download: bad argument");

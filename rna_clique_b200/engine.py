@@ -212,12 +212,27 @@ class Engine:
         samples = [None] * n
         my_tables = [None] * len(mine)
         tasks = []
-        by_last = {}
-        for slot, k in enumerate(mine):
-            by_last.setdefault(max(pairs[k]), []).append(slot)
-        for k in range(n):
-            tasks.append(("u", k))
-            tasks.extend(("s", slot) for slot in by_last.get(k, []))
+        if world > 1:
+            # N ranks: every rank builds the samples k % N == rank (pack + index are not repeated on every
+            # GPU) and broadcasts them as flat device buffers over NCCL; then only searches remain
+            import torch
+            from .exchange import share_built
+            device = torch.device("cuda", self.device)
+            own = [k for k in range(n) if k % world == rank]
+            built = dict(zip(own, self._fan_out(len(own), lambda ctx, i: up(ctx, own[i]))))
+            S = len(self.ctxs)
+            samples = share_built(
+                dist, n, lambda k: built[k], lambda s: s.meta(),
+                lambda s, buf: s.export_flat(buf.data_ptr()),
+                lambda k, meta, buf: _native.Sample.import_flat(self.ctxs[k % S], meta, buf.data_ptr(), labels[k]), device)
+            tasks = [("s", slot) for slot in range(len(mine))]
+        else:
+            by_last = {}
+            for slot, k in enumerate(mine):
+                by_last.setdefault(max(pairs[k]), []).append(slot)
+            for k in range(n):
+                tasks.append(("u", k))
+                tasks.extend(("s", slot) for slot in by_last.get(k, []))
         self._run_tasks(tasks, samples, my_tables, up,
                         lambda ctx, slot: _native.search_pair(ctx, samples[pairs[mine[slot]][0]], samples[pairs[mine[slot]][1]],
                                                               evalue, top_n, keep_all),

@@ -38,21 +38,56 @@ def allgather_flat(dist, my_ids, my_chunks, n_total: int, device):
     all_ids = [torch.zeros_like(idv) for _ in range(world)]
     dist.all_gather(all_ids, idv)
     payload = torch.cat([c.reshape(-1) for c in my_chunks]) if my_chunks else torch.zeros(0, dtype=torch.int32, device=device)
-    totals = [int(sum(int(all_sizes[r][i].item()) for i in all_ids[r].tolist() if i >= 0)) for r in range(world)]
+    all_sizes = torch.stack(all_sizes).cpu().tolist()      # one device->host copy, then plain Python ints
+    all_ids = [v.cpu().tolist() for v in all_ids]
+    totals = [int(sum(all_sizes[r][i] for i in all_ids[r] if i >= 0)) for r in range(world)]
     pad = max(max(totals), 1)
     buf = torch.zeros(pad, dtype=torch.int32, device=device)
     buf[:payload.numel()] = payload
     gathered = [torch.zeros_like(buf) for _ in range(world)]
     dist.all_gather(gathered, buf)
+    if device.type == "cuda":
+        # the consumers (rcq_table_from_flat) run on the library's own streams, which are not ordered
+        # after torch's: finish the collective on the host before handing out views of `gathered`
+        torch.cuda.synchronize(device)
     out = [None] * n_total
     for r in range(world):
         off = 0
-        for i in all_ids[r].tolist():
+        for i in all_ids[r]:
             if i < 0:
                 continue
-            n = int(all_sizes[r][i].item())
+            n = int(all_sizes[r][i])
             out[i] = gathered[r][off:off + n]
             off += n
+    return out
+
+
+def share_built(dist, n_items: int, build, meta_of, export_to, import_from, device, meta_len: int = 8):
+    """Sharded build + broadcast.  Rank r builds the items k with k % world == r (`build(k)`), every rank
+    ends up with all n_items: `meta_of(obj)` -> int64[meta_len] whose last entry is the flat byte size,
+    `export_to(obj, uint8 tensor)` fills the flat buffer on the owner, `import_from(k, meta, uint8 tensor)`
+    rebuilds the object on the other ranks.  Collectives: one all-reduce of the metadata rows (disjoint,
+    so the sum is a gather) and one broadcast per item, all in flight together."""
+    world, rank = dist.get_world_size(), dist.get_rank()
+    mine = [k for k in range(n_items) if k % world == rank]
+    built = {k: build(k) for k in mine}
+    metas = torch.zeros((n_items, meta_len), dtype=torch.int64, device=device)
+    for k, obj in built.items():
+        metas[k] = torch.as_tensor(np.asarray(meta_of(obj), dtype=np.int64), device=device)
+    dist.all_reduce(metas)
+    metas = metas.cpu().numpy()
+    bufs, works = [], []
+    for k in range(n_items):
+        buf = torch.empty(max(int(metas[k, meta_len - 1]), 1), dtype=torch.uint8, device=device)
+        if k in built:
+            export_to(built[k], buf)
+        bufs.append(buf)
+        works.append(dist.broadcast(buf, src=k % world, async_op=True))
+    for w in works:
+        w.wait()
+    if device.type == "cuda":
+        torch.cuda.synchronize(device)
+    out = [built[k] if k in built else import_from(k, metas[k], bufs[k]) for k in range(n_items)]
     return out
 
 

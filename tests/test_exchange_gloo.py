@@ -29,6 +29,23 @@ def _worker(rank, world, port, q):
         make = lambda k: torch.arange(17 * ((k * 7) % 5 if k != 3 else 0), dtype=torch.int32) + 1000 * k
         got = allgather_flat(dist, mine, [make(k) for k in mine], len(pairs), torch.device("cpu"))
         ok = all(torch.equal(got[k], make(k)) for k in range(len(pairs)))
+        # sharded build + broadcast (engine: every rank builds samples k % world == rank)
+        from rna_clique_b200.exchange import share_built
+        built_here = []
+        payload = lambda k: (np.arange(100 * k + 3, dtype=np.int64) * (k + 1)).view(np.uint8).copy()
+
+        def build(k):
+            built_here.append(k)
+            return ("own", k, payload(k))
+
+        def export_to(obj, buf):
+            buf[:len(obj[2])] = torch.from_numpy(obj[2])
+
+        objs = share_built(dist, 5, build, lambda o: [o[1], 7, 0, 0, 0, 0, 0, len(o[2])], export_to,
+                           lambda k, meta, buf: ("imported", int(meta[0]), buf.numpy().copy()), torch.device("cpu"))
+        ok = ok and built_here == [k for k in range(5) if k % world == rank]
+        ok = ok and all(o[1] == k and np.array_equal(o[2], payload(k)) for k, o in enumerate(objs))
+        ok = ok and all((o[0] == "own") == (k % world == rank) for k, o in enumerate(objs))
         q.put((rank, ok, mine))
     finally:
         dist.destroy_process_group()

@@ -52,7 +52,7 @@ def test_configs0_tables_and_matrix_equal_the_oracle():
 
 def test_full_width_properties_do_not_depend_on_order_or_streams():
     """4 samples x 60,000 transcripts, top_genes = 50,000 (configs[1] per-sample size): the matrix is
-    symmetric with a zero diagonal, identical for 1 and 3 streams, and (to 2e-5) independent of the
+    symmetric with a zero diagonal, identical for 1 and 3 streams, and (to 1e-6) independent of the
     input order; every pair contributes exactly 2 x 50,000 rows and every gene is an ideal component."""
     from rna_clique_b200.engine import Engine
     inputs, labels = _inputs(4, 60000, 487)
@@ -67,8 +67,8 @@ def test_full_width_properties_do_not_depend_on_order_or_streams():
     # rows/cols are sorted by label.  Swapping which sample of a pair plays transcripts1 re-runs the greedy
     # extension with query and subject exchanged; its tie rules (mismatch before query gap before subject
     # gap) are not symmetric, so a handful of alignments trade two mismatches for a gap pair: the
-    # matrices agree to ~1e-6, not bit for bit (the reference's blastn runs have the same property).
-    assert c["labels"] == a["labels"] and np.abs(c["matrix"] - m).max() < 2e-5
+    # matrices agree to ~2e-8 (measured), not bit for bit (the reference's blastn runs have the same property).
+    assert c["labels"] == a["labels"] and np.abs(c["matrix"] - m).max() < 1e-6
     assert a["stats"]["n_rows"] == 6 * 2 * 50000 and a["counts"]["ideal"] == 50000 == a["counts"]["components"]
     assert a["stats"]["n_fwd"] == a["stats"]["n_bwd"] == 6 * 50000
     e3.close(); e1.close()

@@ -111,3 +111,24 @@ def test_search_minus_strand_and_masked_bases(ctx):
     cols = tab.download()
     got = np.stack([cols[c] for c in _native.TABLE_COLS] + [cols["minus"].astype(np.int32), cols["reverse"].astype(np.int32)], axis=1)
     assert np.array_equal(got, res.rows(2))
+
+
+def test_sample_export_import_round_trip(ctx):
+    """The flat device buffer a rank broadcasts (rcq_sample_export / rcq_sample_import) rebuilds a sample
+    that searches exactly like the original."""
+    import torch
+    from rna_clique_b200 import _native
+    _, raw = make_samples(taxa=2, count=120, seed=9, mutation_rate=0.03, indel_rate=0.002)
+    g = _gpu_samples(ctx, raw)
+    meta = g[1].meta()
+    buf = torch.empty(int(meta[7]), dtype=torch.uint8, device="cuda:0")
+    g[1].export_flat(buf.data_ptr())
+    torch.cuda.synchronize()
+    clone = _native.Sample.import_flat(ctx, meta, buf.data_ptr(), "clone")
+    assert (clone.n_seq, clone.total, clone.n_index) == (g[1].n_seq, g[1].total, g[1].n_index)
+    a = _native.search_pair(ctx, g[0], g[1])
+    b = _native.search_pair(ctx, g[0], clone)
+    ca, cb = a.download(), b.download()
+    assert len(a) > 0 and all(np.array_equal(ca[k], cb[k]) for k in ca)
+    d0, d1 = g[1].download(), clone.download()
+    assert all(np.array_equal(d0[k], d1[k]) for k in d0)
