@@ -38,7 +38,7 @@ def parse_args():
     ap.add_argument("--count", type=int, default=60000)
     ap.add_argument("--top", type=int, default=50000)
     ap.add_argument("--seed", type=int, default=487)
-    ap.add_argument("--cpu-sample", type=int, default=600, help="top-gene transcripts per sample in the CPU legs")
+    ap.add_argument("--cpu-sample", type=int, default=1500, help="top-gene transcripts per sample in the CPU legs")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--streams", type=int, default=3, help="CUDA streams (host threads) per GPU")
     ap.add_argument("--clock-interval", type=float, default=0.2, help="seconds between nvidia-smi/NVML clock samples (0 = off)")

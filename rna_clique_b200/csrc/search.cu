@@ -102,7 +102,7 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
         CU(cudaMemsetAsync(ctr, 0, 16 * sizeof(int64_t), ctx->stream));
         stage_tic(ctx, 1);
         stage_tic(ctx, 7);
-        LAUNCH(ctx, k_seed_probe, grid_for(s1->n_index, PROBE_TA), 256, 0, s1->index, s1->fctx, s1->n_index, s2->index,
+        LAUNCH(ctx, k_seed_probe, grid_for(s1->n_index, PROBE_TA), PROBE_THREADS, 0, s1->index, s1->fctx, s1->n_index, s2->index,
                s2->fctx, s2->dir, cand, ccap, ctr);
         stage_toc(ctx, 7);
         LAUNCH(ctx, k_seed_verify, RCQ_SMS * 16, 256, 0, cand, ccap, P, seeds, cap, ctr);

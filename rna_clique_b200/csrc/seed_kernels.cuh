@@ -70,14 +70,17 @@ __device__ __forceinline__ bool probe_keep(uint64_t cb, uint32_t oA, uint32_t wa
 // shared memory PROBE_TB entries (+ contexts) at a time with coalesced 8-byte loads.  Every global
 // access of the kernel is therefore a sequential stream (16 B per entry of A and of B, 8 B per
 // surviving candidate); the per-entry lookup is a binary search in shared memory.
-#define PROBE_TA 1024
-#define PROBE_TB 1536   // > PROBE_TA: the B range of a tile is ~PROBE_TA entries plus two buckets of slack
-__global__ void __launch_bounds__(256) k_seed_probe(
+#ifndef PROBE_THREADS
+#define PROBE_THREADS 64
+#endif
+#define PROBE_TA (4 * PROBE_THREADS)
+#define PROBE_TB (6 * PROBE_THREADS)   // > PROBE_TA: the B range of a tile is ~PROBE_TA entries plus two buckets of slack
+__global__ void __launch_bounds__(PROBE_THREADS) k_seed_probe(
     const uint64_t* __restrict__ idxA, const uint64_t* __restrict__ ctxA, int64_t nIdxA,
     const uint64_t* __restrict__ idxB, const uint64_t* __restrict__ ctxB, const uint32_t* __restrict__ dirB,
     uint2* __restrict__ cand, int64_t cap, unsigned long long* __restrict__ counters) {
     __shared__ uint64_t sB[PROBE_TB], sC[PROBE_TB];
-    __shared__ uint32_t wsum[8], wseen[8];
+    __shared__ uint32_t wsum[PROBE_THREADS / 32], wseen[PROBE_THREADS / 32];
     __shared__ unsigned long long bbase;
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t a0 = (int64_t)blockIdx.x * PROBE_TA;
@@ -103,7 +106,7 @@ __global__ void __launch_bounds__(256) k_seed_probe(
     const uint32_t blo = __ldg(dirB + (kfirst >> (32 - RCQ_DIRBITS))), bhi = __ldg(dirB + (klast >> (32 - RCQ_DIRBITS)) + 1);
     for (uint32_t b0 = blo; b0 < bhi; b0 += PROBE_TB) {
         const int nb = (int)min((uint32_t)PROBE_TB, bhi - b0);
-        for (int i = threadIdx.x; i < nb; i += 256) { sB[i] = __ldg(idxB + b0 + i); sC[i] = __ldg(ctxB + b0 + i); }
+        for (int i = threadIdx.x; i < nb; i += PROBE_THREADS) { sB[i] = __ldg(idxB + b0 + i); sC[i] = __ldg(ctxB + b0 + i); }
         __syncthreads();
         // ---- count survivors of this chunk
         int pos[4];
@@ -139,7 +142,7 @@ __global__ void __launch_bounds__(256) k_seed_probe(
         __syncthreads();
         if (threadIdx.x == 0) {
             uint32_t tot = 0, sn = 0;
-            for (int w = 0; w < 8; w++) { uint32_t v = wsum[w]; wsum[w] = tot; tot += v; sn += wseen[w]; }
+            for (int w = 0; w < PROBE_THREADS / 32; w++) { uint32_t v = wsum[w]; wsum[w] = tot; tot += v; sn += wseen[w]; }
             bbase = tot ? atomicAdd(counters + 1, (unsigned long long)tot) : 0ull;
             if (sn) atomicAdd(counters + 2, (unsigned long long)sn);
         }
