@@ -132,3 +132,33 @@ def test_sample_export_import_round_trip(ctx):
     assert len(a) > 0 and all(np.array_equal(ca[k], cb[k]) for k in ca)
     d0, d1 = g[1].download(), clone.download()
     assert all(np.array_equal(d0[k], d1[k]) for k in d0)
+
+
+@pytest.mark.parametrize("length", [4000, 6500])
+def test_drifting_band_uses_the_wide_fallback(ctx, length):
+    """One base of every 29 deleted in sample 2: exact blocks of 28 (just enough to seed) and a band that
+    drifts one diagonal per block, far beyond the 124-diagonal shared-memory rows — the extension
+    re-runs on the pooled global rows (staged strands for 4000-base transcripts, arena reads for 6500)."""
+    from rna_clique_b200 import _native
+    from oracle import oracle as O
+    rng = np.random.default_rng(length)
+    n = 12
+    seqs = [rng.integers(0, 4, size=length + int(rng.integers(0, 50))) for _ in range(n)]
+    letters = np.frombuffer(b"ACGT", dtype=np.uint8)
+    a1 = np.concatenate([letters[s] for s in seqs])
+    off1 = np.concatenate([[0], np.cumsum([len(s) for s in seqs])]).astype(np.int64)
+    cut = [np.delete(s, np.arange(28, len(s), 29)) for s in seqs]
+    a2 = np.concatenate([letters[s] for s in cut])
+    off2 = np.concatenate([[0], np.cumsum([len(s) for s in cut])]).astype(np.int64)
+    gene, iso = np.arange(n, dtype=np.int32), np.ones(n, dtype=np.int32)
+    raw = [(a1, off1, gene, iso), (a2, off2, gene, iso)]
+    g = _gpu_samples(ctx, raw)
+    o = _oracle_samples(raw)
+    tab = _native.search_pair(ctx, g[0], g[1])
+    res = O.search_pair(o[0], o[1])
+    assert tab.stats["band_retries"] > 0
+    assert np.array_equal(_native.debug_last_hsps(ctx), res.hsps())
+    cols = tab.download()
+    got = np.stack([cols[c] for c in _native.TABLE_COLS] + [cols["minus"].astype(np.int32), cols["reverse"].astype(np.int32)], axis=1)
+    assert np.array_equal(got, res.rows(2)) and len(tab) == 2 * n
+    assert (cols["gaps"] > 100).all()
