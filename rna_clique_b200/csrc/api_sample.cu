@@ -9,6 +9,19 @@ thread_local std::string g_rcq_err;
 int rcq_sample_build(rcq_ctx* ctx, rcq_sample* s, const uint8_t* d_ascii, int64_t ascii_len,
                      const int64_t* d_starts);  // sample.cu
 
+// small per-sample arrays out of mapped pinned host memory (no copy engine, see common.cuh)
+static __global__ void k_unstage(const char* __restrict__ h, int32_t n, int64_t* __restrict__ starts,
+                                 int32_t* __restrict__ gidx, int32_t* __restrict__ off, int32_t* __restrict__ len,
+                                 int32_t* __restrict__ gene, int32_t* __restrict__ iso) {
+    const int64_t* hs = (const int64_t*)h;
+    const int32_t* hi = (const int32_t*)(h + 8 * (size_t)n);
+    for (int32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        starts[i] = hs[i];
+        gidx[i] = hi[i]; off[i] = hi[(size_t)n + i]; len[i] = hi[2 * (size_t)n + i];
+        gene[i] = hi[3 * (size_t)n + i]; iso[i] = hi[4 * (size_t)n + i];
+    }
+}
+
 extern "C" {
 
 const char* rcq_last_error(void) { return g_rcq_err.c_str(); }
@@ -23,7 +36,8 @@ int rcq_ctx_create(int device, rcq_ctx** out) {
     rcq_ctx* c = new rcq_ctx();
     c->device = device;
     CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-    CU(cudaMallocHost((void**)&c->h_pin, 64 * sizeof(int64_t)));
+    CU(cudaHostAlloc((void**)&c->h_pin, 64 * sizeof(int64_t), cudaHostAllocMapped));
+    CU(cudaHostGetDevicePointer((void**)&c->h_pin_dev, c->h_pin, 0));
     CU(cudaMalloc((void**)&c->d_ctr, 64 * sizeof(int64_t)));
     for (int i = 0; i < 16; i++) CU(cudaEventCreate(&c->ev[i]));
     // one explicit pool per context: blocks freed on this stream are reused by this stream at once;
@@ -53,6 +67,7 @@ void rcq_ctx_destroy(rcq_ctx* c) {
     if (c->gs_locks) cudaFree(c->gs_locks);
     for (int i = 0; i < 16; i++) cudaEventDestroy(c->ev[i]);
     cudaFreeHost(c->h_pin);
+    if (c->h_stage) cudaFreeHost(c->h_stage);
     cudaFree(c->d_ctr);
     cudaStreamDestroy(c->stream);
     if (c->pool) cudaMemPoolDestroy(c->pool);
@@ -124,7 +139,6 @@ int rcq_sample_create(rcq_ctx* ctx, const uint8_t* ascii, int64_t ascii_len, int
         CU(cudaMemcpyAsync(own_ascii, ascii, ascii_len, cudaMemcpyHostToDevice, ctx->stream));
         d_ascii = own_ascii;
     }
-    if (n_seq) CU(cudaMemcpyAsync(d_starts, starts, n_seq * sizeof(int64_t), cudaMemcpyHostToDevice, ctx->stream));
     RC(dalloc(ctx, &s->off, n_seq));
     RC(dalloc(ctx, &s->len, n_seq));
     RC(dalloc(ctx, &s->gene, n_seq));
@@ -157,11 +171,19 @@ int rcq_sample_create(rcq_ctx* ctx, const uint8_t* ascii, int64_t ascii_len, int
     }
     lap("gene index");
     if (n_seq) {
-        CU(cudaMemcpyAsync(s->gidx, gidx.data(), n_seq * 4, cudaMemcpyHostToDevice, ctx->stream));
-        CU(cudaMemcpyAsync(s->off, aoff.data(), n_seq * 4, cudaMemcpyHostToDevice, ctx->stream));
-        CU(cudaMemcpyAsync(s->len, len.data(), n_seq * 4, cudaMemcpyHostToDevice, ctx->stream));
-        CU(cudaMemcpyAsync(s->gene, gene, n_seq * 4, cudaMemcpyHostToDevice, ctx->stream));
-        CU(cudaMemcpyAsync(s->iso, iso, n_seq * 4, cudaMemcpyHostToDevice, ctx->stream));
+        // starts | gidx | off | len | gene | iso through mapped pinned staging, read by one kernel
+        const size_t n = (size_t)n_seq;
+        RC(stage_reserve(ctx, 28 * n));
+        char* h = ctx->h_stage;
+        memcpy(h, starts, 8 * n);
+        memcpy(h + 8 * n, gidx.data(), 4 * n);
+        memcpy(h + 12 * n, aoff.data(), 4 * n);
+        memcpy(h + 16 * n, len.data(), 4 * n);
+        memcpy(h + 20 * n, gene, 4 * n);
+        memcpy(h + 24 * n, iso, 4 * n);
+        k_unstage<<<RCQ_SMS, 256, 0, ctx->stream>>>(ctx->h_stage_dev, n_seq, d_starts, s->gidx, s->off, s->len, s->gene, s->iso);
+        CU(cudaGetLastError());
+        ctx->launches++;
     }
     lap("h2d small");
     stage_tic(ctx, 0);

@@ -42,7 +42,11 @@ struct rcq_ctx {
     cudaMemPool_t pool = nullptr;   // this context's own stream-ordered pool (no cross-stream reuse stalls)
     int64_t launches = 0;
     // pinned staging for small device->host result reads
-    int64_t* h_pin = nullptr;  // 64 int64
+    int64_t* h_pin = nullptr;  // 64 int64 (pinned, mapped: written by k_publish, no copy engine involved)
+    int64_t* h_pin_dev = nullptr;  // device-side address of h_pin
+    char* h_stage = nullptr;   // pinned, mapped staging for the small per-sample host arrays
+    char* h_stage_dev = nullptr;
+    size_t h_stage_cap = 0;
     int64_t* d_ctr = nullptr;  // 64 int64 device counters
     // debug: gapped HSPs of the last search (device, 12 int32 each)
     int32_t* dbg_hsp = nullptr;
@@ -127,6 +131,31 @@ static inline int talloc(rcq_ctx* c, T** p, int64_t n) {
 }
 template <typename T>
 static inline void tfree(rcq_ctx*, T*) {}   // released wholesale by the next arena_reset
+
+// Small host<->device traffic bypasses the copy engines (a bulk host->device copy in flight would make
+// every small cudaMemcpyAsync wait its turn behind it): counters are published by a one-block kernel
+// into mapped pinned memory, small host arrays are read by kernels from mapped pinned staging.
+static __global__ void k_publish(const int64_t* __restrict__ src, volatile int64_t* dst, int n) {
+    if ((int)threadIdx.x < n) dst[threadIdx.x] = src[threadIdx.x];
+    __threadfence_system();
+}
+static inline int publish_counters(rcq_ctx* c, const int64_t* d_src, int n) {
+    k_publish<<<1, 64, 0, c->stream>>>(d_src, c->h_pin_dev, n);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+static inline int stage_reserve(rcq_ctx* c, size_t bytes) {
+    if (bytes <= c->h_stage_cap) return 0;
+    CU(cudaStreamSynchronize(c->stream));
+    if (c->h_stage) CU(cudaFreeHost(c->h_stage));
+    c->h_stage = nullptr; c->h_stage_cap = 0;
+    const size_t cap = bytes + bytes / 2 + (1u << 20);
+    CU(cudaHostAlloc((void**)&c->h_stage, cap, cudaHostAllocMapped));
+    CU(cudaHostGetDevicePointer((void**)&c->h_stage_dev, c->h_stage, 0));
+    c->h_stage_cap = cap;
+    return 0;
+}
 
 #define LAUNCH(ctx, kern, grid, block, smem, ...)                       \
     do {                                                                \

@@ -409,8 +409,7 @@ int rcq_sample_build(rcq_ctx* ctx, rcq_sample* s, const uint8_t* d_ascii, int64_
         if (s->n_seq)
             LAUNCH(ctx, k_minimizers, blocks, 32 * MZ_WARPS, 0, s->fwd, s->mask, s->off, s->len, s->n_seq, ctr + 1,
                    s->index, s->fctx, (unsigned long long)cap, s->sel);
-        CU(cudaMemcpyAsync(ctx->h_pin, ctr, 2 * sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
-        CU(cudaStreamSynchronize(ctx->stream));
+        RC(publish_counters(ctx, (const int64_t*)ctr, 2));
         s->n_masked = ctx->h_pin[0];
         s->n_index = ctx->h_pin[1];
         if (s->n_index <= cap) break;

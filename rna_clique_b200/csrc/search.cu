@@ -62,9 +62,7 @@ static int scratch_pool(rcq_ctx* ctx, int64_t per_slot, ScratchPool* sp) {
 }
 
 static int read_counters(rcq_ctx* ctx, int n) {
-    CU(cudaMemcpyAsync(ctx->h_pin, ctx->d_ctr, n * sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
-    CU(cudaStreamSynchronize(ctx->stream));
-    return 0;
+    return publish_counters(ctx, ctx->d_ctr, n);
 }
 
 extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sample* s2, double evalue,

@@ -72,6 +72,32 @@ class Engine:
                 f.result()
         return out
 
+    def _prefetch(self, inputs, which):
+        """Queues the host->device copy of every pinned `ascii` buffer among inputs[which] on the engine's
+        copy stream; returns {k: (device tensor, event)}.  Pageable buffers are left to the upload itself
+        (their copies would block this thread)."""
+        staged = {}
+        try:
+            import torch
+        except ImportError:
+            return staged
+        todo = [k for k in which if torch.is_tensor(inputs[k]["ascii"]) and not inputs[k]["ascii"].is_cuda
+                and inputs[k]["ascii"].is_pinned()]
+        if not todo:
+            return staged
+        dev = torch.device("cuda", self.device)
+        if getattr(self, "_copy_stream", None) is None:
+            self._copy_stream = torch.cuda.Stream(dev)
+        with torch.cuda.stream(self._copy_stream):
+            for k in todo:
+                src = inputs[k]["ascii"].reshape(-1)
+                dst = torch.empty(src.numel(), dtype=torch.uint8, device=dev)
+                dst.copy_(src, non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(self._copy_stream)
+                staged[k] = (dst, ev)
+        return staged
+
     def _run_tasks(self, tasks, samples, tables, do_upload, do_search, pair_of):
         """Workers (one per context) drain `tasks` in order, skipping searches whose samples are not
         resident yet; an exception in any worker is re-raised here."""
@@ -192,13 +218,22 @@ class Engine:
         rank = dist.get_rank() if dist is not None else 0
         t_start = time.perf_counter()
 
+        # pinned host buffers are prefetched: every host->device copy is queued on one copy stream right
+        # away (PCIe is the bottleneck of this leg: 1.24 GB per step at configs[1]), so all but the first
+        # copy hide behind the searches of earlier samples; an upload only waits for its own copy's event
+        staged = self._prefetch(inputs, [k for k in range(len(inputs)) if world == 1 or k % world == rank])
+
         def up(ctx, k):
             s = inputs[k]
             starts, lengths, gene, iso = (np.asarray(s[c]) for c in ("starts", "lengths", "gene", "iso"))
             if top_genes is not None:
                 keep = select_top_genes(s["coverage"], gene, top_genes)
                 starts, lengths, gene, iso = starts[keep], lengths[keep], gene[keep], iso[keep]
-            return self.upload(s["ascii"], starts, lengths, gene, iso, name=labels[k], ctx=ctx)
+            ascii_ = s["ascii"]
+            if k in staged:
+                ascii_, ev = staged.pop(k)
+                ev.synchronize()
+            return self.upload(ascii_, starts, lengths, gene, iso, name=labels[k], ctx=ctx)
 
         # One task list, dependency-driven: [upload 0, upload 1, search (0,1), upload 2, search (0,2), ...].
         # A worker (one per stream) takes the first task whose samples are resident, so host->device copies
