@@ -54,6 +54,18 @@ int rcq_ctx_stage_times(rcq_ctx* ctx, double ms[8], int64_t calls[8], int reset)
 int64_t rcq_top_gene_mask(const double* coverage, const int32_t* gene, int64_t n, int64_t top,
                           uint8_t* keep);
 
+/* ---- FASTA ingest (host only).  Replaces the two Bio.SeqIO.parse passes of select_top_genes.py:110-127
+ * and, for the default rnaSPAdes pattern (transcripts.py:8), the per-record regex of transcripts.py:69-126.
+ * rcq_fasta_scan counts records and letters; rcq_fasta_parse writes the letters (newlines, CR and spaces
+ * removed) into ascii_out[n_letters], offsets[n_records+1] and the byte span of every header line;
+ * rcq_parse_spades_ids decodes (coverage, gene, isoform) of every record id (first whitespace-separated
+ * token of the header) and returns -1, or the index of the first id the pattern does not match. */
+int rcq_fasta_scan(const uint8_t* raw, int64_t n, int64_t* n_records, int64_t* n_letters);
+int rcq_fasta_parse(const uint8_t* raw, int64_t n, uint8_t* ascii_out, int64_t* offsets,
+                    int64_t* hdr_start, int64_t* hdr_end);
+int64_t rcq_parse_spades_ids(const uint8_t* raw, const int64_t* hdr_start, const int64_t* hdr_end,
+                             int64_t n_records, double* coverage, int32_t* gene, int32_t* iso);
+
 /* ---- kernels (1)+(2): pack + seed index.  Replaces makeblastdb per sample
  * (find_all_pairs.py:120-159 make_one_db/make_all_dbs -> BlastDBCache.makedb).
  * ascii[ascii_len]: nucleotide letters (no newlines) holding at least the selected transcripts;

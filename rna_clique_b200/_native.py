@@ -19,7 +19,7 @@ HSP_COLS = ["tx1", "tx2", "minus", "a0", "a1", "b0", "b1", "score2", "mismatch",
 # every symbol include/rcq.h declares (checked by tests/test_abi.py)
 SYMBOLS = [
     "rcq_last_error", "rcq_version", "rcq_ctx_create", "rcq_ctx_destroy", "rcq_ctx_sync", "rcq_ctx_stream",
-    "rcq_ctx_launches", "rcq_ctx_stage_times", "rcq_top_gene_mask", "rcq_sample_create", "rcq_sample_free", "rcq_sample_info", "rcq_sample_download",
+    "rcq_ctx_launches", "rcq_ctx_stage_times", "rcq_top_gene_mask", "rcq_fasta_scan", "rcq_fasta_parse", "rcq_parse_spades_ids", "rcq_sample_create", "rcq_sample_free", "rcq_sample_info", "rcq_sample_download",
     "rcq_search_pair", "rcq_table_rows", "rcq_table_download", "rcq_table_free", "rcq_debug_last_hsps", "rcq_debug_keep_hsps",
     "rcq_length_adjustment", "rcq_evalue", "rcq_bitscore", "rcq_phase2_host", "rcq_phase2_tables",
     "rcq_table_flat_words", "rcq_table_flatten", "rcq_table_from_flat", "rcq_sample_meta", "rcq_sample_export", "rcq_sample_import",
@@ -82,6 +82,10 @@ def lib():
         L.rcq_table_free.restype = None
         L.rcq_debug_last_hsps.argtypes = [vp, vp, i64]
         L.rcq_debug_last_hsps.restype = i64
+        L.rcq_fasta_scan.argtypes = [vp, i64, vp, vp]
+        L.rcq_fasta_parse.argtypes = [vp, i64, vp, vp, vp, vp]
+        L.rcq_parse_spades_ids.argtypes = [vp, vp, vp, i64, vp, vp, vp]
+        L.rcq_parse_spades_ids.restype = i64
         L.rcq_top_gene_mask.argtypes = [vp, vp, i64, i64, vp]
         L.rcq_top_gene_mask.restype = i64
         L.rcq_debug_keep_hsps.argtypes = [vp, C.c_int]
@@ -277,6 +281,29 @@ def search_pair(ctx: Context, s1: Sample, s2: Sample, evalue: float = 1e-99, top
     check(lib().rcq_search_pair(ctx.h, s1.h, s2.h, float(evalue), int(top_n), int(bool(keep_all)),
                                 C.byref(h), C.byref(st)))
     return Table(ctx, h, st.as_dict())
+
+
+def fasta_parse(raw: np.ndarray):
+    """(ascii uint8[n_letters], offsets int64[n+1], hdr_start int64[n], hdr_end int64[n]) of FASTA bytes."""
+    raw = np.ascontiguousarray(raw, dtype=np.uint8)
+    cnt = np.zeros(2, dtype=np.int64)
+    check(lib().rcq_fasta_scan(raw.ctypes.data, len(raw), cnt.ctypes.data, cnt.ctypes.data + 8))
+    n, letters = int(cnt[0]), int(cnt[1])
+    ascii_ = np.empty(letters, dtype=np.uint8)
+    offsets = np.zeros(n + 1, dtype=np.int64)
+    hs, he = np.zeros(n, dtype=np.int64), np.zeros(n, dtype=np.int64)
+    check(lib().rcq_fasta_parse(raw.ctypes.data, len(raw), ascii_.ctypes.data, offsets.ctypes.data, hs.ctypes.data, he.ctypes.data))
+    return ascii_, offsets, hs, he
+
+
+def parse_spades_ids(raw: np.ndarray, hdr_start: np.ndarray, hdr_end: np.ndarray):
+    """(coverage, gene, iso, first_bad): the default rnaSPAdes id pattern over every header; first_bad = -1
+    when all ids matched."""
+    n = len(hdr_start)
+    cov, gene, iso = np.zeros(n, dtype=np.float64), np.zeros(n, dtype=np.int32), np.zeros(n, dtype=np.int32)
+    bad = lib().rcq_parse_spades_ids(raw.ctypes.data, hdr_start.ctypes.data, hdr_end.ctypes.data, n,
+                                     cov.ctypes.data, gene.ctypes.data, iso.ctypes.data)
+    return cov, gene, iso, int(bad)
 
 
 def top_gene_mask(coverage, gene, top: int) -> np.ndarray:

@@ -62,10 +62,42 @@ class GeneMatchGraph(nx.Graph):
         self._rcq_built = edges is None
 
     def _materialise(self):
+        """Fills networkx's own dictionaries directly (same content and node order as add_edges_from:
+        first appearance, u before v; one shared attribute dict per undirected edge).  Node tuples are
+        canonical objects, so the pickle memoises each node once."""
         if not self._rcq_built:
             self._rcq_built = True
+            node = object.__getattribute__(self, "_node")
+            adj = object.__getattribute__(self, "_adj")
+            canon = {}
+            import gc
+            gc_was_on = gc.isenabled()
+            gc.disable()          # millions of small dicts: the cyclic collector only adds passes over them
             for s, q, sg, qg in self._rcq_edges.groups:
-                super().add_edges_from(zip(zip([s] * len(sg), sg.tolist()), zip([q] * len(qg), qg.tolist())))
+                cs, cq = canon.setdefault(s, {}), canon.setdefault(q, {})
+                for a, b in zip(sg.tolist(), qg.tolist()):
+                    u = cs.get(a)
+                    if u is None:
+                        u = cs[a] = (s, a)
+                    v = cq.get(b)
+                    if v is None:
+                        v = cq[b] = (q, b)
+                    du = adj.get(u)
+                    if du is None:
+                        du = adj[u] = {}
+                        node[u] = {}
+                    dv = adj.get(v)
+                    if dv is None:
+                        dv = adj[v] = {}
+                        node[v] = {}
+                    if v not in du:
+                        du[v] = dv[u] = {}
+            for n in getattr(self._rcq_edges, "isolated", ()):
+                if n not in node:
+                    adj[n] = {}
+                    node[n] = {}
+            if gc_was_on:
+                gc.enable()
         return self
 
     @property

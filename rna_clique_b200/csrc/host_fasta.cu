@@ -1,0 +1,104 @@
+// host_fasta.cu — host-side FASTA ingest and rnaSPAdes id decoding (no device work).
+// Replaces the Bio.SeqIO.parse passes of select_top_genes.py:110-127 and the per-record regex of
+// transcripts.py:8,69-126 for the DEFAULT id pattern; any other pattern stays in Python.
+#include <stdlib.h>
+#include <string.h>
+#include "common.cuh"
+
+static inline bool is_skip(uint8_t c) { return c == '\n' || c == '\r' || c == ' '; }
+
+// Pass 1: number of records (lines starting with '>') and of sequence letters (every byte outside
+// header lines that is not LF, CR or space).
+extern "C" int rcq_fasta_scan(const uint8_t* raw, int64_t n, int64_t* n_records, int64_t* n_letters) {
+    if (n < 0 || (n > 0 && !raw) || !n_records || !n_letters) return rcq_fail(RCQ_ERR_ARG, "rcq_fasta_scan: bad argument");
+    int64_t rec = 0, let = 0, p = 0;
+    while (p < n) {
+        const uint8_t* nl = (const uint8_t*)memchr(raw + p, '\n', (size_t)(n - p));
+        const int64_t e = nl ? (int64_t)(nl - raw) : n;
+        if (raw[p] == '>') rec++;
+        else {
+            int64_t k = e - p;
+            for (int64_t i = p; i < e; i++) k -= (raw[i] == '\r' || raw[i] == ' ');
+            let += k;
+        }
+        p = e + 1;
+    }
+    *n_records = rec; *n_letters = let;
+    return 0;
+}
+
+// Pass 2: letters -> ascii_out (n_letters bytes), offsets[r] = letters before record r's header
+// (offsets[n_records] = n_letters), hdr_start/hdr_end[r] = byte span of the header line ('>' .. LF).
+extern "C" int rcq_fasta_parse(const uint8_t* raw, int64_t n, uint8_t* ascii_out, int64_t* offsets,
+                               int64_t* hdr_start, int64_t* hdr_end) {
+    if (n < 0 || (n > 0 && (!raw || !offsets))) return rcq_fail(RCQ_ERR_ARG, "rcq_fasta_parse: bad argument");
+    int64_t rec = 0, let = 0, p = 0;
+    while (p < n) {
+        const uint8_t* nl = (const uint8_t*)memchr(raw + p, '\n', (size_t)(n - p));
+        const int64_t e = nl ? (int64_t)(nl - raw) : n;
+        if (raw[p] == '>') {
+            offsets[rec] = let; hdr_start[rec] = p; hdr_end[rec] = e; rec++;
+        } else {
+            const uint8_t* a = raw + p;
+            const int64_t len = e - p;
+            if (!memchr(a, '\r', (size_t)len) && !memchr(a, ' ', (size_t)len)) { memcpy(ascii_out + let, a, (size_t)len); let += len; }
+            else for (int64_t i = 0; i < len; i++) if (!is_skip(a[i])) ascii_out[let++] = a[i];
+        }
+        p = e + 1;
+    }
+    offsets[rec] = let;
+    return 0;
+}
+
+// id = first whitespace-separated token of the header text raw[hdr_start+1 .. hdr_end)
+static inline void id_span(const uint8_t* raw, int64_t a, int64_t b, int64_t* s, int64_t* e) {
+    auto ws = [](uint8_t c) { return c == ' ' || (c >= 9 && c <= 13) || (c >= 28 && c <= 31); };
+    while (a < b && ws(raw[a])) a++;
+    int64_t q = a;
+    while (q < b && !ws(raw[q])) q++;
+    *s = a; *e = q;
+}
+static inline int64_t digits(const uint8_t* p, const uint8_t* end) {
+    int64_t k = 0;
+    while (p + k < end && p[k] >= '0' && p[k] <= '9') k++;
+    return k;
+}
+// The default pattern ^.*cov_([0-9]+(?:\.[0-9]+))_g([0-9]+)_i([0-9]+) with re.search semantics: the
+// greedy .* makes the LAST position where the rest matches win.  Returns -1 when every id matched,
+// else the index of the first id that did not (Python raises TranscriptIDParseError for it).
+extern "C" int64_t rcq_parse_spades_ids(const uint8_t* raw, const int64_t* hdr_start, const int64_t* hdr_end,
+                                        int64_t n_records, double* coverage, int32_t* gene, int32_t* iso) {
+    for (int64_t r = 0; r < n_records; r++) {
+        int64_t s, e;
+        id_span(raw, hdr_start[r] + 1, hdr_end[r], &s, &e);
+        const uint8_t* end = raw + e;
+        bool ok = false;
+        for (int64_t p = e - 4; p >= s && !ok; p--) {
+            if (memcmp(raw + p, "cov_", 4) != 0) continue;
+            const uint8_t* q = raw + p + 4;
+            const int64_t d1 = digits(q, end);
+            if (!d1 || q + d1 >= end || q[d1] != '.') continue;
+            const int64_t d2 = digits(q + d1 + 1, end);
+            if (!d2) continue;
+            const uint8_t* g = q + d1 + 1 + d2;
+            // [0-9]+ may give digits back to let "_g" match: it cannot (a digit is never '_'), so one try
+            if (g + 2 > end || g[0] != '_' || g[1] != 'g') continue;
+            const int64_t d3 = digits(g + 2, end);
+            if (!d3) continue;
+            const uint8_t* i = g + 2 + d3;
+            if (i + 2 > end || i[0] != '_' || i[1] != 'i') continue;
+            const int64_t d4 = digits(i + 2, end);
+            if (!d4 || d3 > 9 || d4 > 9 || d1 + d2 > 300) continue;
+            char buf[320];
+            memcpy(buf, q, (size_t)(d1 + 1 + d2)); buf[d1 + 1 + d2] = 0;
+            coverage[r] = strtod(buf, nullptr);
+            int64_t gv = 0, iv = 0;
+            for (int64_t k = 0; k < d3; k++) gv = gv * 10 + (g[2 + k] - '0');
+            for (int64_t k = 0; k < d4; k++) iv = iv * 10 + (i[2 + k] - '0');
+            gene[r] = (int32_t)gv; iso[r] = (int32_t)iv;
+            ok = true;
+        }
+        if (!ok) return r;
+    }
+    return -1;
+}

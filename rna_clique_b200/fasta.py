@@ -14,6 +14,9 @@ class Fasta:
     headers: list          # header lines without '>' (id = first whitespace-separated token)
     ascii: np.ndarray      # uint8, all sequence letters concatenated, newlines removed
     offsets: np.ndarray    # int64 [n+1]
+    raw: np.ndarray = None        # the file bytes and the byte span of every header line, kept so the
+    hdr_start: np.ndarray = None  # default id pattern can be decoded natively (parse_fasta_ids)
+    hdr_end: np.ndarray = None
 
     @property
     def ids(self):
@@ -24,6 +27,21 @@ class Fasta:
 
 
 def read_fasta(path: Path) -> Fasta:
+    """One native pass over the file bytes (rcq_fasta_scan / rcq_fasta_parse): letters with newlines, CR
+    and spaces removed, record offsets, header spans.  Letters in front of the first header are kept in
+    `ascii` (before offsets[0]) like the numpy statement below."""
+    from . import _native
+    raw = np.fromfile(str(path), dtype=np.uint8)
+    if raw.size == 0:
+        return Fasta([], np.zeros(0, np.uint8), np.zeros(1, np.int64))
+    ascii_, offsets, hs, he = _native.fasta_parse(raw)
+    buf = raw.tobytes()
+    headers = [buf[a + 1:b].decode().rstrip("\r") for a, b in zip(hs.tolist(), he.tolist())]
+    return Fasta(headers, ascii_, offsets, raw, hs, he)
+
+
+def read_fasta_numpy(path: Path) -> Fasta:
+    """The same parse written with numpy (tests compare the two)."""
     raw = np.fromfile(str(path), dtype=np.uint8)
     if raw.size == 0:
         return Fasta([], np.zeros(0, np.uint8), np.zeros(1, np.int64))

@@ -16,7 +16,7 @@ import pandas as pd
 
 from . import _native
 from .fasta import read_fasta
-from .transcripts import default_parser, parse_ids
+from .transcripts import default_parser, parse_fasta_ids
 
 COLUMNS = ["pident", "length", "mismatch", "gapopen", "qstart", "qend", "sstart", "send", "evalue", "bitscore",
            "gaps", "nident", "sstrand", "qgene", "qiso", "sgene", "siso", "reverse"]
@@ -48,7 +48,7 @@ class SampleCache:
         s = self._samples.get(key)
         if s is None:
             fa = read_fasta(path)
-            _, gene, iso = parse_ids(fa.ids, parser)
+            _, gene, iso = parse_fasta_ids(fa, parser)
             s = _native.Sample(self.ctx, fa.ascii, fa.offsets, gene, iso, name=str(path))
             self._samples[key] = s
         return s

@@ -10,7 +10,7 @@ from typing import Callable, Iterator
 import numpy as np
 
 from .fasta import Fasta, read_fasta, write_fasta
-from .transcripts import default_parser, parse_ids
+from .transcripts import default_parser, parse_fasta_ids
 
 
 def top_gene_mask(coverage: np.ndarray, gene: np.ndarray, top: int) -> np.ndarray:
@@ -49,7 +49,7 @@ class TopGeneSelector:
     def _load(self):
         if self._fa is None:
             self._fa = self.seqs_fun()
-            self._cov, self._gene, self._iso = parse_ids(self._fa.ids, self.parser)
+            self._cov, self._gene, self._iso = parse_fasta_ids(self._fa, self.parser)
             self._keep = top_gene_mask(self._cov, self._gene, self.top)
         return self._fa
 

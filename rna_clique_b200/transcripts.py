@@ -68,3 +68,16 @@ def parse_ids(ids, parser=default_parser):
         t = parser(s)
         cov[k], gene[k], iso[k] = t.coverage, t.gene, t.isoform
     return cov, gene, iso
+
+
+def parse_fasta_ids(fa, parser=default_parser):
+    """parse_ids over the records of a Fasta.  The default rnaSPAdes pattern is decoded natively from the
+    file bytes (rcq_parse_spades_ids, same re.search semantics: the last position that matches wins);
+    any other parser runs in Python."""
+    if parser is default_parser and getattr(fa, "raw", None) is not None and len(fa):
+        from . import _native
+        cov, gene, iso, bad = _native.parse_spades_ids(fa.raw, fa.hdr_start, fa.hdr_end)
+        if bad >= 0:
+            raise TranscriptIDParseError(f"Could not parse transcript ID {fa.ids[bad]}.")
+        return cov, gene, iso
+    return parse_ids(fa.ids, parser)
