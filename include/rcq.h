@@ -63,6 +63,10 @@ int64_t rcq_top_gene_mask(const double* coverage, const int32_t* gene, int64_t n
 int rcq_fasta_scan(const uint8_t* raw, int64_t n, int64_t* n_records, int64_t* n_letters);
 int rcq_fasta_parse(const uint8_t* raw, int64_t n, uint8_t* ascii_out, int64_t* offsets,
                     int64_t* hdr_start, int64_t* hdr_end);
+/* FASTA text of selected records ('>' header LF, `width` letters per line, as Bio.SeqIO.write does for
+ * od1/<sample>_top.fasta, select_top_genes_all.py:37-45); out == NULL returns the size only. */
+int64_t rcq_fasta_format(const uint8_t* ascii, const int64_t* starts, const int64_t* lengths, int64_t n,
+                         const uint8_t* hdr, const int64_t* hdr_off, int32_t width, uint8_t* out);
 int64_t rcq_parse_spades_ids(const uint8_t* raw, const int64_t* hdr_start, const int64_t* hdr_end,
                              int64_t n_records, double* coverage, int32_t* gene, int32_t* iso);
 

@@ -19,7 +19,7 @@ HSP_COLS = ["tx1", "tx2", "minus", "a0", "a1", "b0", "b1", "score2", "mismatch",
 # every symbol include/rcq.h declares (checked by tests/test_abi.py)
 SYMBOLS = [
     "rcq_last_error", "rcq_version", "rcq_ctx_create", "rcq_ctx_destroy", "rcq_ctx_sync", "rcq_ctx_stream",
-    "rcq_ctx_launches", "rcq_ctx_stage_times", "rcq_top_gene_mask", "rcq_fasta_scan", "rcq_fasta_parse", "rcq_parse_spades_ids", "rcq_sample_create", "rcq_sample_free", "rcq_sample_info", "rcq_sample_download",
+    "rcq_ctx_launches", "rcq_ctx_stage_times", "rcq_top_gene_mask", "rcq_fasta_scan", "rcq_fasta_parse", "rcq_parse_spades_ids", "rcq_fasta_format", "rcq_sample_create", "rcq_sample_free", "rcq_sample_info", "rcq_sample_download",
     "rcq_search_pair", "rcq_table_rows", "rcq_table_download", "rcq_table_free", "rcq_debug_last_hsps", "rcq_debug_keep_hsps",
     "rcq_length_adjustment", "rcq_evalue", "rcq_bitscore", "rcq_phase2_host", "rcq_phase2_tables",
     "rcq_table_flat_words", "rcq_table_flatten", "rcq_table_from_flat", "rcq_sample_meta", "rcq_sample_export", "rcq_sample_import",
@@ -86,6 +86,8 @@ def lib():
         L.rcq_fasta_parse.argtypes = [vp, i64, vp, vp, vp, vp]
         L.rcq_parse_spades_ids.argtypes = [vp, vp, vp, i64, vp, vp, vp]
         L.rcq_parse_spades_ids.restype = i64
+        L.rcq_fasta_format.argtypes = [vp, vp, vp, i64, vp, vp, C.c_int32, vp]
+        L.rcq_fasta_format.restype = i64
         L.rcq_top_gene_mask.argtypes = [vp, vp, i64, i64, vp]
         L.rcq_top_gene_mask.restype = i64
         L.rcq_debug_keep_hsps.argtypes = [vp, C.c_int]
@@ -294,6 +296,25 @@ def fasta_parse(raw: np.ndarray):
     hs, he = np.zeros(n, dtype=np.int64), np.zeros(n, dtype=np.int64)
     check(lib().rcq_fasta_parse(raw.ctypes.data, len(raw), ascii_.ctypes.data, offsets.ctypes.data, hs.ctypes.data, he.ctypes.data))
     return ascii_, offsets, hs, he
+
+
+def fasta_format(ascii_: np.ndarray, starts, lengths, headers, width: int = 60) -> np.ndarray:
+    """The FASTA text (uint8 array) of the given records."""
+    ascii_ = np.ascontiguousarray(ascii_, dtype=np.uint8)
+    starts = np.ascontiguousarray(starts, dtype=np.int64)
+    lengths = np.ascontiguousarray(lengths, dtype=np.int64)
+    hb = [h.encode() for h in headers]
+    hdr = np.frombuffer(b"".join(hb), dtype=np.uint8) if hb else np.zeros(0, np.uint8)
+    hdr_off = np.zeros(len(hb) + 1, dtype=np.int64)
+    np.cumsum([len(b) for b in hb], out=hdr_off[1:])
+    args = (ascii_.ctypes.data, starts.ctypes.data, lengths.ctypes.data, len(hb), hdr.ctypes.data if len(hdr) else None,
+            hdr_off.ctypes.data, int(width))
+    size = lib().rcq_fasta_format(*args, None)
+    if size < 0:
+        check(int(size))
+    out = np.empty(size, dtype=np.uint8)
+    lib().rcq_fasta_format(*args, out.ctypes.data)
+    return out
 
 
 def parse_spades_ids(raw: np.ndarray, hdr_start: np.ndarray, hdr_end: np.ndarray):

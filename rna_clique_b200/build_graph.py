@@ -102,7 +102,8 @@ class GeneMatchGraph(nx.Graph):
 
     @property
     def rcq_edges(self):
-        return self._rcq_edges
+        """The flat edge arrays, or None once the graph has been modified through the networkx API."""
+        return None if self.__dict__.get("_rcq_dirty") else self._rcq_edges
 
     def __reduce__(self):
         self._materialise()
@@ -112,6 +113,20 @@ class GeneMatchGraph(nx.Graph):
         if name in ("_node", "_adj", "nodes", "edges", "adj", "degree") and not object.__getattribute__(self, "__dict__").get("_rcq_built", True):
             object.__getattribute__(self, "_materialise")()
         return object.__getattribute__(self, name)
+
+
+def _mutator(name):
+    def method(self, *args, **kwargs):
+        self._materialise()
+        self.__dict__["_rcq_dirty"] = True
+        return getattr(nx.Graph, name)(self, *args, **kwargs)
+    method.__name__ = name
+    return method
+
+
+for _name in ("add_node", "add_nodes_from", "remove_node", "remove_nodes_from", "add_edge", "add_edges_from",
+              "add_weighted_edges_from", "remove_edge", "remove_edges_from", "update", "clear", "clear_edges"):
+    setattr(GeneMatchGraph, _name, _mutator(_name))
 
 
 def build_graph(dfs: Iterable[pd.DataFrame]) -> nx.Graph:

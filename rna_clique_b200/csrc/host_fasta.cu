@@ -102,3 +102,24 @@ extern "C" int64_t rcq_parse_spades_ids(const uint8_t* raw, const int64_t* hdr_s
     }
     return -1;
 }
+
+// FASTA text of the selected records, Biopython style: '>' header LF, then `width` letters per line
+// (select_top_genes_all.py:37-45 writes od1/<sample>_top.fasta with SeqIO.write).  hdr = all header
+// texts concatenated, record r's header = hdr[hdr_off[r] .. hdr_off[r+1]).  With out == NULL only the
+// size is returned; otherwise the bytes are written and the size returned.
+extern "C" int64_t rcq_fasta_format(const uint8_t* ascii, const int64_t* starts, const int64_t* lengths, int64_t n,
+                                    const uint8_t* hdr, const int64_t* hdr_off, int32_t width, uint8_t* out) {
+    if (n < 0 || width < 1 || (n > 0 && (!starts || !lengths || !hdr_off))) return rcq_fail(RCQ_ERR_ARG, "rcq_fasta_format: bad argument");
+    int64_t at = 0;
+    for (int64_t r = 0; r < n; r++) {
+        const int64_t hl = hdr_off[r + 1] - hdr_off[r], L = lengths[r];
+        if (out) { out[at] = '>'; memcpy(out + at + 1, hdr + hdr_off[r], (size_t)hl); out[at + 1 + hl] = '\n'; }
+        at += hl + 2;
+        for (int64_t p = 0; p < L; p += width) {
+            const int64_t k = L - p < width ? L - p : width;
+            if (out) { memcpy(out + at, ascii + starts[r] + p, (size_t)k); out[at + k] = '\n'; }
+            at += k + 1;
+        }
+    }
+    return at;
+}

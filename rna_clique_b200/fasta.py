@@ -67,7 +67,13 @@ def read_fasta_numpy(path: Path) -> Fasta:
 
 def write_fasta(path: Path, headers, ascii_: np.ndarray, starts, lengths, width: int = 60) -> None:
     """Biopython-style output (SeqIO.write(..., "fasta"): '>' + header, 60 letters per line), as
-    select_top_genes_all.py:37-45 writes od1/<sample>_top.fasta."""
+    select_top_genes_all.py:37-45 writes od1/<sample>_top.fasta.  Formatted natively in one buffer."""
+    from . import _native
+    _native.fasta_format(ascii_, starts, lengths, list(headers), width).tofile(str(path))
+
+
+def write_fasta_python(path: Path, headers, ascii_: np.ndarray, starts, lengths, width: int = 60) -> None:
+    """The same writer in Python (tests compare the two)."""
     with open(path, "wb") as f:
         for h, s, n in zip(headers, starts, lengths):
             seq = ascii_[int(s):int(s) + int(n)]

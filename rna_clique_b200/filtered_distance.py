@@ -105,8 +105,8 @@ class SampleSimilarity:
         tabs = self._tables
         edges = None
         extra_samples = set()
-        if isinstance(self.graph, GeneMatchGraph) and not self.graph._rcq_built:
-            edges = self.graph.rcq_edges
+        if isinstance(self.graph, GeneMatchGraph) and self.graph.rcq_edges is not None:
+            edges = self.graph.rcq_edges       # flat arrays, still exact: the graph was not modified
         elif self.graph is not None:
             edges = EdgeArrays.from_networkx(self.graph)
             extra_samples = {n[0] for n in getattr(edges, "isolated", [])}

@@ -57,3 +57,18 @@ def test_default_pattern_semantics(tmp_path):
     bad.write_text(">ok_cov_1.5_g1_i1\nAC\n>NODE_7_cov_12_g1_i1\nAC\n")          # integer coverage: no match upstream either
     with pytest.raises(TranscriptIDParseError, match="NODE_7_cov_12_g1_i1"):
         parse_fasta_ids(read_fasta(bad))
+
+
+def test_write_fasta_native_equals_python(tmp_path):
+    from rna_clique_b200.fasta import write_fasta, write_fasta_python
+    rng = np.random.default_rng(1)
+    lens = [0, 1, 59, 60, 61, 120, 121, 500]
+    ascii_ = rng.choice(np.frombuffer(b"ACGT", dtype=np.uint8), size=sum(lens) + 7)
+    starts = np.concatenate([[3], 3 + np.cumsum(lens)[:-1]])
+    headers = [f"NODE_{k}_cov_1.5_g{k}_i1 d" for k in range(len(lens))]
+    for w in (60, 7):
+        write_fasta(tmp_path / "a.fa", headers, ascii_, starts, lens, w)
+        write_fasta_python(tmp_path / "b.fa", headers, ascii_, starts, lens, w)
+        assert (tmp_path / "a.fa").read_bytes() == (tmp_path / "b.fa").read_bytes()
+    back = read_fasta(tmp_path / "a.fa")
+    assert back.headers == headers and np.array_equal(np.diff(back.offsets), lens)
