@@ -145,19 +145,21 @@ double rcq_bitscore(int32_t score);
  * count the samples present in the graph (filtered_distance.py:171-182).
  * Outputs: nident_sum/denom_sum int64[n_tables] (denom = sum(length) - sum(gaps) over
  * restricted rows); valid uint8[n_samples*stride] (may be NULL); counts[0]=#components,
- * [1]=#ideal components, [2]=sample_count used, [3]=#nodes, [4]=#unique edges.
+ * [1]=#ideal components, [2]=sample_count used, [3]=#nodes, [4]=#unique edges,
+ * [5]=#components with at least sample_count nodes (the --statistics line of plot_component_sizes.py:214-230
+ * is counts[2], counts[0], counts[5], counts[1]).
  * Returns RCQ_ERR_NO_IDEAL when some summed table's denom_sum is 0 (sums are still filled in). */
 int rcq_phase2_host(rcq_ctx* ctx, int32_t n_samples, int64_t stride, int32_t n_tables,
                     const int64_t* row_off, const int32_t* t_s, const int32_t* t_q,
                     const int32_t* sgene, const int32_t* qgene, const int32_t* nident,
                     const int32_t* length, const int32_t* gaps, const uint8_t* t_flags,
                     int32_t sample_count, int64_t* nident_sum, int64_t* denom_sum, uint8_t* valid,
-                    int64_t counts[5]);
+                    int64_t counts[6]);
 /* Same, fed from device-resident tables produced by rcq_search_pair (no host round trip). */
 int rcq_phase2_tables(rcq_ctx* ctx, int32_t n_samples, int64_t stride, int32_t n_tables,
                       const rcq_table* const* tables, const int32_t* t_s, const int32_t* t_q,
                       int32_t sample_count, int64_t* nident_sum, int64_t* denom_sum,
-                      uint8_t* valid, int64_t counts[5]);
+                      uint8_t* valid, int64_t counts[6]);
 
 /* ---- multi-GPU: a built sample as one flat device buffer.  With N ranks each rank builds the samples
  * k = rank mod N (kernels 1+2 are not repeated on every GPU) and broadcasts them over NCCL/NVLink; the

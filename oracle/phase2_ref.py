@@ -51,7 +51,8 @@ def phase2(n_samples, tables, sample_count=None):
         de = int(np.asarray(t["length"], dtype=np.int64)[keep].sum() - np.asarray(t["gaps"], dtype=np.int64)[keep].sum())
         sums.append((ni, de))
     return dict(valid=valid, sums=sums, sample_count=int(sample_count), n_ideal=int(ideal.sum()), stride=stride,
-                n_nodes=n, n_edges=len(uniq))
+                n_nodes=n, n_edges=len(uniq), n_components=int(len(vcount)),
+                n_ge_samples=int((vcount >= sample_count).sum()))   # plot_component_sizes.py:214-230 statistics
 
 
 def distance_matrix(names, tables, sums):

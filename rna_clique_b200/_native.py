@@ -360,14 +360,14 @@ def phase2_host(ctx: Context, n_samples: int, stride: int, row_off, t_s, t_q, sg
     ni = np.zeros(max(n_tables, 1), dtype=np.int64)
     de = np.zeros(max(n_tables, 1), dtype=np.int64)
     valid = np.zeros(n_samples * stride, dtype=np.uint8) if want_valid else None
-    counts = np.zeros(5, dtype=np.int64)
+    counts = np.zeros(6, dtype=np.int64)
     if t_flags is not None:
         t_flags = np.ascontiguousarray(t_flags, dtype=np.uint8)
         assert len(t_flags) == n_tables
     code = lib().rcq_phase2_host(ctx.h, n_samples, stride, n_tables, row_off.ctypes.data, *[a.ctypes.data for a in arrs],
                                  _ptr(t_flags), int(sample_count or 0), ni.ctypes.data, de.ctypes.data, _ptr(valid), counts.ctypes.data)
     res = dict(nident_sum=ni[:n_tables], denom_sum=de[:n_tables], valid=valid,
-               counts=dict(zip(["components", "ideal", "sample_count", "nodes", "edges"], counts.tolist())))
+               counts=dict(zip(["components", "ideal", "sample_count", "nodes", "edges", "ge_samples"], counts.tolist())))
     if code == -4:
         res["no_ideal"] = True
         return res
@@ -386,11 +386,11 @@ def phase2_tables(ctx: Context, n_samples: int, stride: int, tables, t_s, t_q, s
     ni = np.zeros(max(n_tables, 1), dtype=np.int64)
     de = np.zeros(max(n_tables, 1), dtype=np.int64)
     valid = np.zeros(n_samples * stride, dtype=np.uint8) if want_valid else None
-    counts = np.zeros(5, dtype=np.int64)
+    counts = np.zeros(6, dtype=np.int64)
     code = lib().rcq_phase2_tables(ctx.h, n_samples, stride, n_tables, hs, t_s.ctypes.data, t_q.ctypes.data,
                                    int(sample_count or 0), ni.ctypes.data, de.ctypes.data, _ptr(valid), counts.ctypes.data)
     res = dict(nident_sum=ni[:n_tables], denom_sum=de[:n_tables], valid=valid,
-               counts=dict(zip(["components", "ideal", "sample_count", "nodes", "edges"], counts.tolist())))
+               counts=dict(zip(["components", "ideal", "sample_count", "nodes", "edges", "ge_samples"], counts.tolist())))
     if code == -4:
         res["no_ideal"] = True
         return res

@@ -101,7 +101,7 @@ __global__ void k_p2_edges(P2View V, int64_t cap, unsigned long long* counts /* 
 }
 // valid[node] = node lies in an ideal component
 __global__ void k_p2_valid(P2View V, int64_t n_nodes, int32_t sample_count, uint8_t* valid,
-                           unsigned long long* counts /* [1]=#ideal */) {
+                           unsigned long long* counts /* [1]=#ideal [5]=#components with >= sample_count nodes */) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_nodes) return;
     uint8_t ok = 0;
@@ -110,6 +110,7 @@ __global__ void k_p2_valid(P2View V, int64_t n_nodes, int32_t sample_count, uint
         int64_t v = V.vcount[root], e = V.ecount[root];
         ok = (v == sample_count) && (2 * e == v * (v - 1));
         if (ok && root == i) atomicAdd(counts + 1, 1ull);
+        if (root == i && v >= sample_count) atomicAdd(counts + 5, 1ull);
     }
     valid[i] = ok;
 }
@@ -140,7 +141,7 @@ __global__ void k_p2_reduce(P2View V, const uint8_t* __restrict__ valid, unsigne
 
 // ---------------------------------------------------------------------------------------------
 static int phase2_run(rcq_ctx* ctx, P2View V, int32_t sample_count, int64_t* nident_sum, int64_t* denom_sum,
-                      uint8_t* valid_out, int64_t counts[5], const uint8_t* h_flags = nullptr) {
+                      uint8_t* valid_out, int64_t counts[6], const uint8_t* h_flags = nullptr) {
     const int64_t n_nodes = (int64_t)V.n_samples * V.stride;
     if (n_nodes >= (1ll << 31)) return rcq_fail(RCQ_ERR_CAPACITY, "rcq_phase2: n_samples*stride exceeds 2^31 nodes");
     unsigned long long* ctr = (unsigned long long*)ctx->d_ctr;
@@ -191,7 +192,7 @@ static int phase2_run(rcq_ctx* ctx, P2View V, int32_t sample_count, int64_t* nid
     stage_collect(ctx);
     if (counts) {
         counts[0] = ctx->h_pin[0]; counts[1] = ctx->h_pin[1]; counts[2] = sample_count;
-        counts[3] = ctx->h_pin[3]; counts[4] = ctx->h_pin[4];
+        counts[3] = ctx->h_pin[3]; counts[4] = ctx->h_pin[4]; counts[5] = ctx->h_pin[5];
     }
     dfree(ctx, V.parent); dfree(ctx, V.present); dfree(ctx, V.vcount); dfree(ctx, V.ecount);
     dfree(ctx, V.ekeys); dfree(ctx, valid); dfree(ctx, spresent); dfree(ctx, d_ni); dfree(ctx, d_de);
@@ -205,7 +206,7 @@ extern "C" int rcq_phase2_host(rcq_ctx* ctx, int32_t n_samples, int64_t stride, 
                                const int32_t* sgene, const int32_t* qgene, const int32_t* nident,
                                const int32_t* length, const int32_t* gaps, const uint8_t* t_flags,
                                int32_t sample_count, int64_t* nident_sum, int64_t* denom_sum, uint8_t* valid,
-                               int64_t counts[5]) {
+                               int64_t counts[6]) {
     if (!ctx || n_samples < 0 || stride < 1 || n_tables < 0 || (n_tables && (!row_off || !t_s || !t_q || !nident_sum || !denom_sum)))
         return rcq_fail(RCQ_ERR_ARG, "rcq_phase2_host: bad argument");
     CU(cudaSetDevice(ctx->device));
@@ -243,7 +244,7 @@ extern "C" int rcq_phase2_host(rcq_ctx* ctx, int32_t n_samples, int64_t stride, 
 extern "C" int rcq_phase2_tables(rcq_ctx* ctx, int32_t n_samples, int64_t stride, int32_t n_tables,
                                  const rcq_table* const* tables, const int32_t* t_s, const int32_t* t_q,
                                  int32_t sample_count, int64_t* nident_sum, int64_t* denom_sum,
-                                 uint8_t* valid, int64_t counts[5]) {
+                                 uint8_t* valid, int64_t counts[6]) {
     if (!ctx || n_samples < 0 || stride < 1 || n_tables < 0 || (n_tables && (!tables || !t_s || !t_q || !nident_sum || !denom_sum)))
         return rcq_fail(RCQ_ERR_ARG, "rcq_phase2_tables: bad argument");
     CU(cudaSetDevice(ctx->device));

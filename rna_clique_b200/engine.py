@@ -291,7 +291,7 @@ class Engine:
                                 exchange=(t_exchange - t_search) * 1e3, phase2=(t_phase2 - t_exchange) * 1e3),
                    pairs=pairs, nident_sum=res["nident_sum"], denom_sum=res["denom_sum"], counts=res["counts"],
                    stats=stats, no_ideal=res["no_ideal"], n_local_pairs=len(mine),
-                   lengths=[s.total for s in samples], n_index=[s.n_index for s in samples])
+                   lengths=[s.total for s in samples], n_index=[s.n_index for s in samples], stride=stride)
         if not res["no_ideal"]:
             out["labels"], out["matrix"] = self.matrix_from_sums(labels, pairs, res["nident_sum"], res["denom_sum"])
         if keep_tables:
@@ -301,6 +301,24 @@ class Engine:
                 t.close()
             for s in samples:
                 s.close()
+        return out
+
+    def subset_distances(self, result: dict, labels: Sequence[str], keep: Sequence[int], stride: Optional[int] = None):
+        """Phase 2 again on the device-resident tables of `result` (all_vs_all(..., keep_tables=True)),
+        restricted to the samples `keep`: the reference's subset analysis (make_subset.py:166-201 links the
+        tables of the kept samples and rebuilds the graph; subset_comparisons.py:45-73) without touching
+        the searches.  Returns dict(labels, matrix, pairs, nident_sum, denom_sum, counts, no_ideal)."""
+        keep_set = set(int(k) for k in keep)
+        sel = [k for k, (i, j) in enumerate(result["pairs"]) if i in keep_set and j in keep_set]
+        pairs = [result["pairs"][k] for k in sel]
+        tables = [result["tables"][k] for k in sel]
+        if stride is None:
+            stride = result["stride"]
+        res = self.phase2(len(labels), pairs, tables, stride)
+        out = dict(pairs=pairs, nident_sum=res["nident_sum"], denom_sum=res["denom_sum"], counts=res["counts"],
+                   no_ideal=res["no_ideal"])
+        if not res["no_ideal"]:
+            out["labels"], out["matrix"] = self.matrix_from_sums(labels, pairs, res["nident_sum"], res["denom_sum"])
         return out
 
     def close(self):

@@ -149,6 +149,13 @@ class SampleSimilarity:
     def ideal_component_count(self) -> int:
         return int(self._phase2["counts"]["ideal"])
 
+    def component_statistics(self):
+        """(samples, components, components with >= samples nodes, ideal components): the four numbers
+        `plot_component_sizes --statistics` prints (plot_component_sizes.py:214-230), from the union-find
+        counts of the device pass."""
+        c = self._phase2["counts"]
+        return int(c["sample_count"]), int(c["components"]), int(c["ge_samples"]), int(c["ideal"])
+
     def restricted(self, comp_df: pd.DataFrame) -> pd.DataFrame:
         p = self._phase2
         if len(comp_df) == 0:

@@ -60,6 +60,10 @@ def test_phase2_gpu_random_large(ctx):
     exp = phase2_ref.phase2(n_samples, tables)
     res = run_gpu(ctx, n_samples, tables)
     assert res["counts"]["ideal"] == exp["n_ideal"] and exp["n_ideal"] > 100
+    # the four numbers of `plot_component_sizes --statistics` (plot_component_sizes.py:214-230)
+    assert (res["counts"]["sample_count"], res["counts"]["components"], res["counts"]["ge_samples"]) == \
+        (exp["sample_count"], exp["n_components"], exp["n_ge_samples"])
+    assert exp["n_ge_samples"] > exp["n_ideal"]
     assert res["counts"]["nodes"] == exp["n_nodes"] and res["counts"]["edges"] == exp["n_edges"]
     got = {(int(i // res["stride"]), int(i % res["stride"])) for i in np.flatnonzero(res["valid"])}
     assert got == exp["valid"]

@@ -72,3 +72,28 @@ def test_full_width_properties_do_not_depend_on_order_or_streams():
     assert a["stats"]["n_rows"] == 6 * 2 * 50000 and a["counts"]["ideal"] == 50000 == a["counts"]["components"]
     assert a["stats"]["n_fwd"] == a["stats"]["n_bwd"] == 6 * 50000
     e3.close(); e1.close()
+
+
+def test_subset_rerun_on_cached_tables_equals_a_fresh_run():
+    """make_subset semantics: phase 2 restricted to a subset of the samples, from the device tables of the
+    full run, equals running the subset from scratch (and the numpy oracle on the downloaded tables)."""
+    from oracle import phase2_ref
+    from rna_clique_b200.engine import Engine
+    inputs, labels = _inputs(5, 1500, 12, mutation_rate=0.03, indel_rate=0.002)
+    eng = Engine(0)
+    full = eng.all_vs_all(inputs, labels, top_genes=1000, keep_tables=True)
+    keep = [0, 2, 3]
+    sub = eng.subset_distances(full, labels, keep)
+    fresh = eng.all_vs_all([inputs[k] for k in keep], [labels[k] for k in keep], top_genes=1000)
+    assert sub["labels"] == fresh["labels"] and np.array_equal(sub["matrix"], fresh["matrix"])
+    assert sub["counts"]["sample_count"] == 3 and sub["counts"]["ideal"] == fresh["counts"]["ideal"]
+    otables = []
+    for (i, j), t in zip(full["pairs"], full["tables"]):
+        if i in keep and j in keep:
+            c = t.download()
+            otables.append(dict(s=i, q=j, sgene=c["sgene"], qgene=c["qgene"], nident=c["nident"], length=c["length"], gaps=c["gaps"]))
+    exp = phase2_ref.phase2(5, otables)
+    assert list(zip(sub["nident_sum"].tolist(), sub["denom_sum"].tolist())) == exp["sums"]
+    # the full run has fewer ideal components than the subset never had more samples to satisfy
+    assert full["counts"]["ideal"] <= sub["counts"]["ideal"]
+    eng.close()
