@@ -117,3 +117,20 @@ def test_rna_clique_end_to_end(tmp_path):
     # phase-2-only entry on the files just written
     again = SampleSimilarity.from_filenames(tmp_path / "graph.pkl", sorted(get_table_files(od2)))
     assert np.array_equal(again.get_dissimilarity_df().to_numpy(), m)
+
+
+def test_run_analysis_from_yaml(tmp_path):
+    """config.yaml -> run_analysis (what the rna-clique command does, rna_clique.py:180-217): output layout,
+    matrix file and the finished config written back."""
+    from rna_clique_b200.config import RNACliqueConfig, run_analysis
+    from rna_clique_b200.simulate import simulate, write_dataset
+    _, ts = simulate(3, 120, seed=5, mutation_rate=0.02)
+    dirs = write_dataset(tmp_path / "in", ts)
+    cfg = RNACliqueConfig(input_dirs=dirs, output_dir=tmp_path / "out", top_genes=80)
+    cfg.yaml_save(tmp_path / "config.yaml")
+    cfg = RNACliqueConfig.yaml_load(tmp_path / "config.yaml")
+    sim, mat = run_analysis(cfg, tmp_path / "out" / "config.yaml")
+    assert mat.shape == (3, 3) and (np.diag(mat.to_numpy()) == 0).all() and sim.ideal_component_count > 40
+    assert (tmp_path / "out" / "graph.pkl").is_file() and cfg.matrix.is_file() and len(list((tmp_path / "out" / "od2").iterdir())) == 3
+    done = RNACliqueConfig.yaml_load(tmp_path / "out" / "config.yaml")
+    assert done.finished is not None and sorted(done.path_to_sample.values()) == ["T0", "T1", "T2"]
