@@ -139,6 +139,21 @@ __global__ void k_p2_reduce(P2View V, const uint8_t* __restrict__ valid, unsigne
     if (t >= 0 && leader && (a | b)) { atomicAdd(&nident_sum[t], a); atomicAdd(&denom_sum[t], b); }
 }
 
+// the five columns phase 2 reads, gathered from device-resident tables into one column-major block
+__global__ void k_p2_gather(const int64_t* __restrict__ row_off, const int32_t* const* __restrict__ tcols,
+                            int32_t n_tables, int64_t n, int32_t* __restrict__ out) {
+    const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n) return;
+    const int32_t t = table_of(row_off, n_tables, r);
+    const int64_t lo = __ldg(row_off + t), tn = __ldg(row_off + t + 1) - lo;
+    const int32_t* c = tcols[t] + (r - lo);
+    out[r] = __ldg(c + RCQ_COL_SGENE * tn);
+    out[n + r] = __ldg(c + RCQ_COL_QGENE * tn);
+    out[2 * n + r] = __ldg(c + RCQ_COL_NIDENT * tn);
+    out[3 * n + r] = __ldg(c + RCQ_COL_LENGTH * tn);
+    out[4 * n + r] = __ldg(c + RCQ_COL_GAPS * tn);
+}
+
 // ---------------------------------------------------------------------------------------------
 static int phase2_run(rcq_ctx* ctx, P2View V, int32_t sample_count, int64_t* nident_sum, int64_t* denom_sum,
                       uint8_t* valid_out, int64_t counts[6], const uint8_t* h_flags = nullptr) {
@@ -248,34 +263,31 @@ extern "C" int rcq_phase2_tables(rcq_ctx* ctx, int32_t n_samples, int64_t stride
     if (!ctx || n_samples < 0 || stride < 1 || n_tables < 0 || (n_tables && (!tables || !t_s || !t_q || !nident_sum || !denom_sum)))
         return rcq_fail(RCQ_ERR_ARG, "rcq_phase2_tables: bad argument");
     CU(cudaSetDevice(ctx->device));
-    std::vector<int64_t> off(n_tables + 1, 0);
+    // one host block [row offsets | table base pointers | t_s | t_q] -> one copy; the five columns the pass
+    // reads are then gathered from the tables by one kernel (not 5 copies per table)
+    const size_t words64 = (size_t)(n_tables + 1) + (size_t)n_tables;
+    std::vector<int64_t> host(words64 + (size_t)n_tables + 1, 0);      // + n_tables int32 pairs
+    int64_t* off = host.data();
     for (int t = 0; t < n_tables; t++) off[t + 1] = off[t] + tables[t]->n;
+    for (int t = 0; t < n_tables; t++) host[n_tables + 1 + t] = (int64_t)(uintptr_t)tables[t]->cols;
+    int32_t* h32 = (int32_t*)(host.data() + words64);
+    for (int t = 0; t < n_tables; t++) { h32[t] = t_s[t]; h32[n_tables + t] = t_q[t]; }
     const int64_t n = off[n_tables];
     P2View V;
     memset(&V, 0, sizeof V);
     V.n_samples = n_samples; V.n_tables = n_tables; V.stride = stride; V.n_rows = n;
-    int64_t* d_off = nullptr; int32_t *d_ts = nullptr, *d_tq = nullptr, *d_cols = nullptr;
-    RC(dalloc(ctx, &d_off, n_tables + 1));
-    RC(dalloc(ctx, &d_ts, n_tables));
-    RC(dalloc(ctx, &d_tq, n_tables));
+    int64_t* d_host = nullptr; int32_t* d_cols = nullptr;
+    RC(dalloc(ctx, &d_host, (int64_t)host.size()));
     RC(dalloc(ctx, &d_cols, 5 * n));
-    CU(cudaMemcpyAsync(d_off, off.data(), (size_t)(n_tables + 1) * 8, cudaMemcpyHostToDevice, ctx->stream));
-    if (n_tables) {
-        CU(cudaMemcpyAsync(d_ts, t_s, (size_t)n_tables * 4, cudaMemcpyHostToDevice, ctx->stream));
-        CU(cudaMemcpyAsync(d_tq, t_q, (size_t)n_tables * 4, cudaMemcpyHostToDevice, ctx->stream));
-    }
-    const int colid[5] = {RCQ_COL_SGENE, RCQ_COL_QGENE, RCQ_COL_NIDENT, RCQ_COL_LENGTH, RCQ_COL_GAPS};
-    for (int t = 0; t < n_tables; t++) {
-        const rcq_table* T = tables[t];
-        if (!T->n) continue;
-        for (int c = 0; c < 5; c++)
-            CU(cudaMemcpyAsync(d_cols + c * n + off[t], T->cols + (int64_t)colid[c] * T->n, (size_t)T->n * 4,
-                               cudaMemcpyDeviceToDevice, ctx->stream));
-    }
+    CU(cudaMemcpyAsync(d_host, host.data(), host.size() * 8, cudaMemcpyHostToDevice, ctx->stream));
+    const int64_t* d_off = d_host;
+    const int32_t* d_ts = (const int32_t*)(d_host + words64);
+    const int32_t* d_tq = d_ts + n_tables;
+    if (n) LAUNCH(ctx, k_p2_gather, grid_for(n, 256), 256, 0, d_off, (const int32_t* const*)(d_host + n_tables + 1), n_tables, n, d_cols);
     V.row_off = d_off; V.t_s = d_ts; V.t_q = d_tq;
     V.sgene = d_cols; V.qgene = d_cols + n; V.nident = d_cols + 2 * n; V.length = d_cols + 3 * n; V.gaps = d_cols + 4 * n;
     int rc = phase2_run(ctx, V, sample_count, nident_sum, denom_sum, valid, counts);
-    dfree(ctx, d_off); dfree(ctx, d_ts); dfree(ctx, d_tq); dfree(ctx, d_cols);
+    dfree(ctx, d_host); dfree(ctx, d_cols);
     return rc;
 }
 

@@ -98,22 +98,15 @@ class Engine:
                 staged[k] = (dst, ev)
         return staged
 
-    def _run_tasks(self, tasks, samples, tables, do_upload, do_search, pair_of):
-        """Workers (one per context) drain `tasks` in order, skipping searches whose samples are not
-        resident yet; an exception in any worker is re-raised here."""
+    def _run_tasks(self, tasks, ready, run):
+        """Workers (one per context) drain `tasks` in list order: worker w takes the first open task with
+        ready(task, w) (evaluated under the lock) and calls run(ctx, task), which stores its own result.
+        An exception in any worker is re-raised here."""
         import threading
         cv = threading.Condition()
         state = {"next": [True] * len(tasks), "left": len(tasks), "err": None}
 
         S = len(self.ctxs)
-
-        def ready(task, w):
-            if task[0] == "u":
-                # uploads are pinned to a context (sample k -> context k % S): every context's memory
-                # pool then sees the same allocation sequence each step and stops growing after warm-up
-                return task[1] % S == w
-            i, j = pair_of(task[1])
-            return samples[i] is not None and samples[j] is not None
 
         def work(w):
             ctx = self.ctxs[w]
@@ -136,19 +129,14 @@ class Engine:
                                 return
                             cv.wait()
                     state["next"][pick] = False
-                kind, x = tasks[pick]
                 try:
-                    r = do_upload(ctx, x) if kind == "u" else do_search(ctx, x)
+                    run(ctx, tasks[pick])
                 except BaseException as e:  # noqa: BLE001
                     with cv:
                         state["err"] = e
                         cv.notify_all()
                     return
                 with cv:
-                    if kind == "u":
-                        samples[x] = r
-                    else:
-                        tables[x] = r
                     state["left"] -= 1
                     cv.notify_all()
 
@@ -247,20 +235,26 @@ class Engine:
         samples = [None] * n
         my_tables = [None] * len(mine)
         tasks = []
+        S = len(self.ctxs)
+        share = None
         if world > 1:
             # N ranks: every rank builds the samples k % N == rank (pack + index are not repeated on every
-            # GPU) and broadcasts them as flat device buffers over NCCL; then only searches remain
+            # GPU) and broadcasts them as flat device buffers over NCCL, one round of N samples at a time:
+            # task ("b", j) builds this rank's sample of round j and issues the round's broadcasts (always on
+            # worker 0, so the collectives of all ranks line up), ("u", k) waits for sample k to arrive and
+            # unpacks it, and searches start as soon as their two samples are resident - the transfers of
+            # later rounds run behind the searches of earlier ones
             import torch
-            from .exchange import share_built
+            from .exchange import PipelinedShare
             device = torch.device("cuda", self.device)
-            own = [k for k in range(n) if k % world == rank]
-            built = dict(zip(own, self._fan_out(len(own), lambda ctx, i: up(ctx, own[i]))))
-            S = len(self.ctxs)
-            samples = share_built(
-                dist, n, lambda k: built[k], lambda s: s.meta(),
-                lambda s, buf: s.export_flat(buf.data_ptr()),
-                lambda k, meta, buf: _native.Sample.import_flat(self.ctxs[k % S], meta, buf.data_ptr(), labels[k]), device)
-            tasks = [("s", slot) for slot in range(len(mine))]
+            share = PipelinedShare(dist, n, device)
+            by_round = {}
+            for slot, k in enumerate(mine):
+                by_round.setdefault(max(pairs[k]) // world, []).append(slot)
+            tasks = [("b", j) for j in range(share.rounds)]
+            for j in range(share.rounds):
+                tasks.extend(("u", k) for k in range(j * world, min(n, (j + 1) * world)) if k % world != rank)
+                tasks.extend(("s", slot) for slot in by_round.get(j, []))
         else:
             by_last = {}
             for slot, k in enumerate(mine):
@@ -268,10 +262,42 @@ class Engine:
             for k in range(n):
                 tasks.append(("u", k))
                 tasks.extend(("s", slot) for slot in by_last.get(k, []))
-        self._run_tasks(tasks, samples, my_tables, up,
-                        lambda ctx, slot: _native.search_pair(ctx, samples[pairs[mine[slot]][0]], samples[pairs[mine[slot]][1]],
-                                                              evalue, top_n, keep_all),
-                        lambda slot: pairs[mine[slot]])
+
+        def ready(task, w):
+            kind, x = task
+            if kind == "b":
+                return w == 0
+            if kind == "u":
+                # uploads are pinned to a context (sample k -> context k % S): every context's memory
+                # pool then sees the same allocation sequence each step and stops growing after warm-up
+                if share is None:
+                    return x % S == w
+                # arrivals go to the workers that do not build (worker 0 is busy with its "b" tasks first)
+                return share.is_issued(x) and (S == 1 or 1 + x % (S - 1) == w)
+            i, j = pairs[mine[x]]
+            return samples[i] is not None and samples[j] is not None
+
+        def run(ctx, task):
+            kind, x = task
+            if kind == "b":
+                torch.cuda.set_device(self.device)
+                k = share.own_item(x)
+                obj = up(ctx, k) if k is not None else None
+                share.issue_round(x, obj, lambda s: s.meta(), lambda s, buf: s.export_flat(buf.data_ptr()))
+                if k is not None:
+                    samples[k] = obj
+            elif kind == "u" and share is not None:
+                torch.cuda.set_device(self.device)
+                samples[x] = share.fetch(x, lambda k, meta, buf: _native.Sample.import_flat(ctx, meta, buf.data_ptr(), labels[k]))
+            elif kind == "u":
+                samples[x] = up(ctx, x)
+            else:
+                i, j = pairs[mine[x]]
+                my_tables[x] = _native.search_pair(ctx, samples[i], samples[j], evalue, top_n, keep_all)
+
+        self._run_tasks(tasks, ready, run)
+        if share is not None:
+            share.finish()
         t_upload = time.perf_counter()
         stats = {}
         for t in my_tables:

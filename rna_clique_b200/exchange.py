@@ -17,35 +17,30 @@ NCOLS = 17
 def allgather_flat(dist, my_ids, my_chunks, n_total: int, device):
     """my_chunks[k]: 1-D int32 tensor owned by this rank for global item my_ids[k].
     Returns a list of n_total int32 tensors (every rank gets every item).
-    Two collectives: sizes (all_gather of an int64 vector), then one padded payload all_gather."""
-    world = dist.get_world_size()
-    sizes = torch.zeros(n_total, dtype=torch.int64, device=device)
+    Two collectives: one all-reduce of (size, owner + 1) per item - ids are disjoint across ranks, so the
+    sum is a gather - and one padded payload all_gather."""
+    world, rank = dist.get_world_size(), dist.get_rank()
+    info = np.zeros((2, n_total), dtype=np.int64)
     for i, c in zip(my_ids, my_chunks):
-        sizes[i] = c.numel()
-    all_sizes = [torch.zeros_like(sizes) for _ in range(world)]
-    dist.all_gather(all_sizes, sizes)
-    # owner of item i = the rank that reported it (ids are disjoint across ranks)
-    ids_by_rank = []
-    for r in range(world):
-        ids_by_rank.append(my_ids if r == dist.get_rank() else None)
-    id_count = torch.tensor([len(my_ids)], dtype=torch.int64, device=device)
-    counts = [torch.zeros_like(id_count) for _ in range(world)]
-    dist.all_gather(counts, id_count)
-    max_ids = int(max(int(c.item()) for c in counts))
-    idv = torch.full((max(max_ids, 1),), -1, dtype=torch.int64, device=device)
-    if my_ids:
-        idv[:len(my_ids)] = torch.tensor(list(my_ids), dtype=torch.int64, device=device)
-    all_ids = [torch.zeros_like(idv) for _ in range(world)]
-    dist.all_gather(all_ids, idv)
-    payload = torch.cat([c.reshape(-1) for c in my_chunks]) if my_chunks else torch.zeros(0, dtype=torch.int32, device=device)
-    all_sizes = torch.stack(all_sizes).cpu().tolist()      # one device->host copy, then plain Python ints
-    all_ids = [v.cpu().tolist() for v in all_ids]
-    totals = [int(sum(all_sizes[r][i] for i in all_ids[r] if i >= 0)) for r in range(world)]
+        info[0, i] = c.numel()
+        info[1, i] = rank + 1
+    info_t = torch.as_tensor(info, device=device)
+    dist.all_reduce(info_t)
+    info = info_t.cpu().numpy()                              # the one device->host copy of the exchange
+    sizes, owner = info[0], info[1] - 1
+    if (owner < 0).any() or (owner >= world).any():
+        raise RuntimeError("allgather_flat: an item is owned by no rank or by several")
+    ids_by_rank = [np.flatnonzero(owner == r) for r in range(world)]        # ascending ids per rank
+    totals = [int(sizes[ids].sum()) for ids in ids_by_rank]
     pad = max(max(totals), 1)
-    buf = torch.zeros(pad, dtype=torch.int32, device=device)
-    buf[:payload.numel()] = payload
-    gathered = [torch.zeros_like(buf) for _ in range(world)]
-    dist.all_gather(gathered, buf)
+    buf = torch.empty(pad, dtype=torch.int32, device=device)
+    off = 0
+    for i, c in sorted(zip(my_ids, my_chunks), key=lambda p: p[0]):
+        buf[off:off + c.numel()] = c.reshape(-1)
+        off += c.numel()
+    gathered = torch.empty((world, pad), dtype=torch.int32, device=device)
+    dist.all_gather_into_tensor(gathered, buf) if hasattr(dist, "all_gather_into_tensor") and device.type == "cuda" \
+        else dist.all_gather(list(gathered.unbind(0)), buf)
     if device.type == "cuda":
         # the consumers (rcq_table_from_flat) run on the library's own streams, which are not ordered
         # after torch's: finish the collective on the host before handing out views of `gathered`
@@ -53,41 +48,100 @@ def allgather_flat(dist, my_ids, my_chunks, n_total: int, device):
     out = [None] * n_total
     for r in range(world):
         off = 0
-        for i in all_ids[r]:
-            if i < 0:
-                continue
-            n = int(all_sizes[r][i])
-            out[i] = gathered[r][off:off + n]
+        for i in ids_by_rank[r]:
+            n = int(sizes[i])
+            out[int(i)] = gathered[r, off:off + n]
             off += n
     return out
 
 
+class PipelinedShare:
+    """Sharded build + broadcast, pipelined by rounds.  Item k belongs to rank k % world; round j covers the
+    items j*world .. (j+1)*world-1.  ONE thread per rank calls `issue_round(j, obj, ...)` for j = 0, 1, ...
+    with the item it built for that round (the collectives of all ranks therefore line up: per round one
+    all-reduce of the metadata rows - disjoint, so the sum is a gather - and one asynchronous broadcast per
+    item).  Any thread may then `fetch(k, import_from)`, which blocks until item k has arrived and rebuilds
+    the object, so consumers start on the first items while later rounds are still being built and sent.
+    meta_of(obj) -> int64[meta_len] whose last entry is the flat byte size; export_to(obj, uint8 tensor)
+    fills the flat buffer on the owner; import_from(k, meta, uint8 tensor) rebuilds it elsewhere."""
+
+    def __init__(self, dist, n_items: int, device, meta_len: int = 8):
+        import threading
+        self.dist, self.n, self.device, self.meta_len = dist, n_items, device, meta_len
+        self.world, self.rank = dist.get_world_size(), dist.get_rank()
+        self.rounds = (n_items + self.world - 1) // self.world
+        self.metas = [None] * n_items
+        self.bufs = [None] * n_items
+        self.works = [None] * n_items
+        self.issued = [threading.Event() for _ in range(n_items)]
+        self._side = threading.local()
+
+    def own_item(self, j: int):
+        k = j * self.world + self.rank
+        return k if k < self.n else None
+
+    def is_issued(self, k: int) -> bool:
+        return self.issued[k].is_set()
+
+    def issue_round(self, j: int, obj, meta_of, export_to) -> None:
+        lo, hi = j * self.world, min(self.n, (j + 1) * self.world)
+        own = self.own_item(j)
+        metas = torch.zeros((hi - lo, self.meta_len), dtype=torch.int64, device=self.device)
+        if own is not None:
+            metas[own - lo] = torch.as_tensor(np.asarray(meta_of(obj), dtype=np.int64), device=self.device)
+        self.dist.all_reduce(metas)
+        metas = metas.cpu().numpy()
+        for k in range(lo, hi):
+            buf = torch.empty(max(int(metas[k - lo, self.meta_len - 1]), 1), dtype=torch.uint8, device=self.device)
+            if k == own:
+                export_to(obj, buf)          # synchronous on the library's stream: the data is there before the send
+            self.metas[k], self.bufs[k] = metas[k - lo], buf
+            self.works[k] = self.dist.broadcast(buf, src=k % self.world, async_op=True)
+            self.issued[k].set()
+
+    def fetch(self, k: int, import_from):
+        self.issued[k].wait()
+        w = self.works[k]
+        if self.device.type == "cuda":
+            # the consumer runs on the library's own streams, which are not ordered after torch's: make a
+            # side stream wait for the collective and finish that stream on the host
+            side = getattr(self._side, "stream", None)
+            if side is None:
+                side = self._side.stream = torch.cuda.Stream(self.device)
+            with torch.cuda.stream(side):
+                w.wait()
+            side.synchronize()
+        else:
+            w.wait()
+        obj = import_from(k, self.metas[k], self.bufs[k])   # synchronous copy out of the flat buffer
+        self.bufs[k] = None
+        return obj
+
+    def finish(self) -> None:
+        """Owners keep their send buffers until every broadcast has completed."""
+        for k, w in enumerate(self.works):
+            if w is not None and self.bufs[k] is not None:
+                w.wait()
+        if self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
+        self.bufs = [None] * self.n
+
+
 def share_built(dist, n_items: int, build, meta_of, export_to, import_from, device, meta_len: int = 8):
-    """Sharded build + broadcast.  Rank r builds the items k with k % world == r (`build(k)`), every rank
-    ends up with all n_items: `meta_of(obj)` -> int64[meta_len] whose last entry is the flat byte size,
-    `export_to(obj, uint8 tensor)` fills the flat buffer on the owner, `import_from(k, meta, uint8 tensor)`
-    rebuilds the object on the other ranks.  Collectives: one all-reduce of the metadata rows (disjoint,
-    so the sum is a gather) and one broadcast per item, all in flight together."""
-    world, rank = dist.get_world_size(), dist.get_rank()
-    mine = [k for k in range(n_items) if k % world == rank]
-    built = {k: build(k) for k in mine}
-    metas = torch.zeros((n_items, meta_len), dtype=torch.int64, device=device)
-    for k, obj in built.items():
-        metas[k] = torch.as_tensor(np.asarray(meta_of(obj), dtype=np.int64), device=device)
-    dist.all_reduce(metas)
-    metas = metas.cpu().numpy()
-    bufs, works = [], []
+    """Sharded build + broadcast, eager form: rank r builds the items k with k % world == r (`build(k)`),
+    every rank returns all n_items (see PipelinedShare for the callbacks)."""
+    sh = PipelinedShare(dist, n_items, device, meta_len)
+    out = [None] * n_items
+    for j in range(sh.rounds):
+        k = sh.own_item(j)
+        obj = build(k) if k is not None else None
+        if k is not None:
+            out[k] = obj
+        sh.issue_round(j, obj, meta_of, export_to)
     for k in range(n_items):
-        buf = torch.empty(max(int(metas[k, meta_len - 1]), 1), dtype=torch.uint8, device=device)
-        if k in built:
-            export_to(built[k], buf)
-        bufs.append(buf)
-        works.append(dist.broadcast(buf, src=k % world, async_op=True))
-    for w in works:
-        w.wait()
-    if device.type == "cuda":
-        torch.cuda.synchronize(device)
-    out = [built[k] if k in built else import_from(k, metas[k], bufs[k]) for k in range(n_items)]
+        if out[k] is None:
+            out[k] = sh.fetch(k, import_from)
+    sh.finish()
     return out
 
 

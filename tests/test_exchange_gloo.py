@@ -46,6 +46,27 @@ def _worker(rank, world, port, q):
         ok = ok and built_here == [k for k in range(5) if k % world == rank]
         ok = ok and all(o[1] == k and np.array_equal(o[2], payload(k)) for k, o in enumerate(objs))
         ok = ok and all((o[0] == "own") == (k % world == rank) for k, o in enumerate(objs))
+        # pipelined form: one thread issues the rounds in order, another fetches items as they arrive
+        import threading
+        from rna_clique_b200.exchange import PipelinedShare
+        sh = PipelinedShare(dist, 5, torch.device("cpu"))
+        got2 = {}
+
+        def consumer():
+            for k in range(5):
+                if k % world != rank:
+                    got2[k] = sh.fetch(k, lambda k, meta, buf: ("imported", int(meta[0]), buf.numpy().copy()))
+
+        th = threading.Thread(target=consumer)
+        th.start()
+        for j in range(sh.rounds):
+            k = sh.own_item(j)
+            obj = ("own", k, payload(k)) if k is not None else None
+            sh.issue_round(j, obj, lambda o: [o[1], 7, 0, 0, 0, 0, 0, len(o[2])], export_to)
+        th.join(timeout=60)
+        sh.finish()
+        ok = ok and sh.rounds == 3 and sorted(got2) == [k for k in range(5) if k % world != rank]
+        ok = ok and all(o[1] == k and np.array_equal(o[2], payload(k)) for k, o in got2.items())
         q.put((rank, ok, mine))
     finally:
         dist.destroy_process_group()
