@@ -75,6 +75,7 @@ class PipelinedShare:
         self.works = [None] * n_items
         self.issued = [threading.Event() for _ in range(n_items)]
         self._side = threading.local()
+        self._keep = []
 
     def own_item(self, j: int):
         k = j * self.world + self.rank
@@ -91,10 +92,24 @@ class PipelinedShare:
             metas[own - lo] = torch.as_tensor(np.asarray(meta_of(obj), dtype=np.int64), device=self.device)
         self.dist.all_reduce(metas)
         metas = metas.cpu().numpy()
+        sizes = [max(int(metas[k - lo, self.meta_len - 1]), 1) for k in range(lo, hi)]
+        if hi - lo == self.world and self.world > 1 and self.device.type == "cuda":
+            # a full round: every rank contributes one item, so the round is ONE all-gather (all NVLink ports
+            # busy in both directions) instead of `world` broadcasts queued behind each other
+            pad = max(sizes)
+            out = torch.empty((self.world, pad), dtype=torch.uint8, device=self.device)
+            inp = torch.empty(pad, dtype=torch.uint8, device=self.device)
+            export_to(obj, inp)              # synchronous on the library's stream: the data is there before the send
+            work = self.dist.all_gather_into_tensor(out, inp, async_op=True)
+            for k in range(lo, hi):
+                self.metas[k], self.bufs[k], self.works[k] = metas[k - lo], out[k - lo, :sizes[k - lo]], work
+                self.issued[k].set()
+            self._keep.append(inp)
+            return
         for k in range(lo, hi):
-            buf = torch.empty(max(int(metas[k - lo, self.meta_len - 1]), 1), dtype=torch.uint8, device=self.device)
+            buf = torch.empty(sizes[k - lo], dtype=torch.uint8, device=self.device)
             if k == own:
-                export_to(obj, buf)          # synchronous on the library's stream: the data is there before the send
+                export_to(obj, buf)
             self.metas[k], self.bufs[k] = metas[k - lo], buf
             self.works[k] = self.dist.broadcast(buf, src=k % self.world, async_op=True)
             self.issued[k].set()
@@ -125,6 +140,7 @@ class PipelinedShare:
         if self.device.type == "cuda":
             torch.cuda.synchronize(self.device)
         self.bufs = [None] * self.n
+        self._keep = []
 
 
 def share_built(dist, n_items: int, build, meta_of, export_to, import_from, device, meta_len: int = 8):
