@@ -14,6 +14,29 @@ __device__ __forceinline__ uint32_t base_code(uint32_t c) {  // 0..3, or 4 = not
     return u == 'A' ? 0u : u == 'C' ? 1u : u == 'G' ? 2u : (u == 'T' || u == 'U') ? 3u : 4u;
 }
 
+// Four ASCII letters (one per byte of w) -> bits 0..7: their 2-bit codes, bits 8..11: "not A, C, G, T or U"
+// (either case).  With u = letter & 0xDF the code is Gray-decoded from bits 1-2 of u (A 00, C 01, G 11,
+// T/U 10), and the letter is valid iff the remaining bits say 0x41 with bits 1-2 != 10 (A, C, G) or
+// 0x50 / 0x51 with bits 1-2 == 10 (T, U).  Byte-parallel: no carries cross byte lanes.
+__device__ __forceinline__ uint32_t pack4(uint32_t w) {
+    const uint32_t u = w & 0xDFDFDFDFu;
+    const uint32_t r = (u >> 1) & 0x03030303u;
+    const uint32_t code = r ^ ((r >> 1) & 0x01010101u);
+    const uint32_t h = u & 0xF9F9F9F9u;
+    // per-byte zero tests (exact: 0x80 in a byte iff that byte of x is zero)
+#define ZB(x) (~((((x) & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | (x) | 0x7F7F7F7Fu))
+    const uint32_t is41 = ZB(h ^ 0x41414141u);
+    const uint32_t is5x = ZB((h & 0xFEFEFEFEu) ^ 0x50505050u);       // 0x50 or 0x51
+    const uint32_t r2 = ZB(r ^ 0x02020202u);
+#undef ZB
+    const uint32_t valid = (is41 & ~r2) | (is5x & r2);              // 0x80 per valid byte
+    const uint32_t bad = (~valid & 0x80808080u) >> 7;               // 0x01 per invalid byte
+    // gather: byte k of code -> bits 2k..2k+1, byte k of bad -> bit k (multiply = shifted adds, no overlaps)
+    const uint32_t c8 = (code * 0x01041040u) >> 24;
+    const uint32_t b4 = (bad * 0x10204080u) >> 28;
+    return (c8 & 0xFFu) | ((b4 & 0xFu) << 8);
+}
+
 // Warp per transcript.  Each lane turns 16 letters into one 2-bit word per iteration; the 16
 // letters come from two aligned 16-byte vector loads funnel-shifted to the transcript's byte
 // alignment (coalesced: a warp iteration reads one contiguous 512(+16)-byte span).
@@ -55,18 +78,25 @@ __global__ void k_pack(const uint8_t* __restrict__ ascii, int64_t ascii_len,
                         B |= (uint64_t)((a + 8 + k < ascii_len) ? ascii[a + 8 + k] : 'N') << (8 * k);
                     }
                 }
-                int lim = min(16, n - b0);
+                const int lim = min(16, n - b0);
+                // four letters per 32-bit lane of arithmetic (pack4): 8 code bits + 4 "not ACGTU" bits
+                const uint32_t q[4] = {(uint32_t)A, (uint32_t)(A >> 32), (uint32_t)B, (uint32_t)(B >> 32)};
 #pragma unroll
-                for (int k = 0; k < 16; k++) {
-                    uint32_t chk = (uint32_t)((k < 8 ? A >> (8 * k) : B >> (8 * (k - 8))) & 0xFF);
-                    uint32_t code = (k < lim) ? base_code(chk) : 4u;
-                    if (code > 3u) {
-                        mbits |= 1u << k;
-                        if (k < lim) masked++;
-                    } else {
-                        word |= code << (2 * k);
-                    }
+                for (int k = 0; k < 4; k++) {
+                    const uint32_t r = pack4(q[k]);
+                    word |= (r & 0xFFu) << (8 * k);
+                    mbits |= (r >> 8) << (4 * k);
                 }
+                const uint32_t inside = lim >= 16 ? 0xFFFFu : ((1u << lim) - 1u);
+                masked += __popc(mbits & inside);
+                mbits |= ~inside & 0xFFFFu;
+                // codes under a mask bit are zero, as before
+                uint32_t keep2 = ~mbits & 0xFFFFu;                      // spread 16 bits to 16 bit pairs
+                keep2 = (keep2 | (keep2 << 8)) & 0x00FF00FFu;
+                keep2 = (keep2 | (keep2 << 4)) & 0x0F0F0F0Fu;
+                keep2 = (keep2 | (keep2 << 2)) & 0x33333333u;
+                keep2 = (keep2 | (keep2 << 1)) & 0x55555555u;
+                word &= keep2 | (keep2 << 1);
                 fwd[(dst + b0) >> 4] = word;
             } else {
                 mbits = 0xFFFFu;

@@ -20,7 +20,8 @@ def _oracle_samples(raw):
 def test_pack_revcomp_mask(ctx):
     rng = np.random.default_rng(5)
     lens = [1, 15, 16, 17, 31, 32, 33, 100, 511, 512, 513, 2050, 0, 64]
-    letters = np.frombuffer(b"ACGTacgtNnRYU-", dtype=np.uint8)
+    # includes every letter that differs from a valid one in a single bit group (E P Q R S V W, @ ` [ {)
+    letters = np.frombuffer(b"ACGTacgtNnRYUu-EePpQqSsVvWw@`[{\x00\xff\x14\x95", dtype=np.uint8)
     ascii_ = letters[rng.integers(0, len(letters), size=sum(lens))]
     offsets = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
     from rna_clique_b200 import _native
