@@ -1,3 +1,4 @@
+"""Diagnostic: wall time of the reference-facing rna_clique() call on a simulated dataset (taxa count top)."""
 import sys, time, os, tempfile
 from pathlib import Path
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
