@@ -70,6 +70,17 @@ int64_t rcq_fasta_format(const uint8_t* ascii, const int64_t* starts, const int6
 int64_t rcq_parse_spades_ids(const uint8_t* raw, const int64_t* hdr_start, const int64_t* hdr_end,
                              int64_t n_records, double* coverage, int32_t* gene, int32_t* iso);
 
+/* ---- graph.pkl (host only).  Replaces build_graph (build_graph.py:40-68) + pickle.dump(graph, f,
+ * HIGHEST_PROTOCOL) (filtering_step.py:158-159) for the on-disk contract: writes the pickle stream of a
+ * plain networkx.Graph whose nodes are (sample_names[s], gene) tuples, one undirected edge per distinct
+ * (sgene, qgene) row of the groups (group g = rows [g_off[g], g_off[g+1]) between samples g_s[g] and
+ * g_q[g]), nodes in first-appearance order, neighbours in insertion order, plus isolated nodes.
+ * counts[0] = nodes, [1] = edges, [2] = bytes written. */
+int rcq_graph_pickle(const char* path, int32_t n_samples, const char* const* sample_names,
+                     int32_t n_groups, const int32_t* g_s, const int32_t* g_q, const int64_t* g_off,
+                     const int32_t* sgene, const int32_t* qgene, int64_t n_isolated,
+                     const int32_t* iso_sample, const int32_t* iso_gene, int64_t counts[3]);
+
 /* ---- kernels (1)+(2): pack + seed index.  Replaces makeblastdb per sample
  * (find_all_pairs.py:120-159 make_one_db/make_all_dbs -> BlastDBCache.makedb).
  * ascii[ascii_len]: nucleotide letters (no newlines) holding at least the selected transcripts;

@@ -19,7 +19,7 @@ HSP_COLS = ["tx1", "tx2", "minus", "a0", "a1", "b0", "b1", "score2", "mismatch",
 # every symbol include/rcq.h declares (checked by tests/test_abi.py)
 SYMBOLS = [
     "rcq_last_error", "rcq_version", "rcq_ctx_create", "rcq_ctx_destroy", "rcq_ctx_sync", "rcq_ctx_stream",
-    "rcq_ctx_launches", "rcq_ctx_stage_times", "rcq_top_gene_mask", "rcq_fasta_scan", "rcq_fasta_parse", "rcq_parse_spades_ids", "rcq_fasta_format", "rcq_sample_create", "rcq_sample_free", "rcq_sample_info", "rcq_sample_download",
+    "rcq_ctx_launches", "rcq_ctx_stage_times", "rcq_top_gene_mask", "rcq_fasta_scan", "rcq_fasta_parse", "rcq_parse_spades_ids", "rcq_fasta_format", "rcq_graph_pickle", "rcq_sample_create", "rcq_sample_free", "rcq_sample_info", "rcq_sample_download",
     "rcq_search_pair", "rcq_table_rows", "rcq_table_download", "rcq_table_free", "rcq_debug_last_hsps", "rcq_debug_keep_hsps",
     "rcq_length_adjustment", "rcq_evalue", "rcq_bitscore", "rcq_phase2_host", "rcq_phase2_tables",
     "rcq_table_flat_words", "rcq_table_flatten", "rcq_table_from_flat", "rcq_sample_meta", "rcq_sample_export", "rcq_sample_import",
@@ -87,6 +87,7 @@ def lib():
         L.rcq_parse_spades_ids.argtypes = [vp, vp, vp, i64, vp, vp, vp]
         L.rcq_parse_spades_ids.restype = i64
         L.rcq_fasta_format.argtypes = [vp, vp, vp, i64, vp, vp, C.c_int32, vp]
+        L.rcq_graph_pickle.argtypes = [C.c_char_p, C.c_int32, vp, C.c_int32, vp, vp, vp, vp, vp, i64, vp, vp, vp]
         L.rcq_fasta_format.restype = i64
         L.rcq_top_gene_mask.argtypes = [vp, vp, i64, i64, vp]
         L.rcq_top_gene_mask.restype = i64
@@ -315,6 +316,25 @@ def fasta_format(ascii_: np.ndarray, starts, lengths, headers, width: int = 60) 
     out = np.empty(size, dtype=np.uint8)
     lib().rcq_fasta_format(*args, out.ctypes.data)
     return out
+
+
+def graph_pickle(path, sample_names, groups, isolated=()) -> dict:
+    """rcq_graph_pickle: groups = [(s index, q index, sgene int32[], qgene int32[])], isolated = [(s index, gene)].
+    Writes the networkx.Graph pickle of the gene-matches graph; returns dict(nodes, edges, bytes)."""
+    names = [str(n).encode() for n in sample_names]
+    arr = (C.c_char_p * max(len(names), 1))(*names)
+    g_s = np.ascontiguousarray([g[0] for g in groups], dtype=np.int32)
+    g_q = np.ascontiguousarray([g[1] for g in groups], dtype=np.int32)
+    g_off = np.zeros(len(groups) + 1, dtype=np.int64)
+    np.cumsum([len(g[2]) for g in groups], out=g_off[1:])
+    cat = lambda k: np.ascontiguousarray(np.concatenate([np.asarray(g[k], dtype=np.int32) for g in groups]) if groups else np.zeros(0, np.int32), dtype=np.int32)
+    sg, qg = cat(2), cat(3)
+    iso_s = np.ascontiguousarray([i[0] for i in isolated], dtype=np.int32)
+    iso_g = np.ascontiguousarray([i[1] for i in isolated], dtype=np.int32)
+    counts = np.zeros(3, dtype=np.int64)
+    check(lib().rcq_graph_pickle(str(path).encode(), len(names), C.cast(arr, C.c_void_p), len(groups), _ptr(g_s), _ptr(g_q),
+                                 g_off.ctypes.data, _ptr(sg), _ptr(qg), len(iso_s), _ptr(iso_s), _ptr(iso_g), counts.ctypes.data))
+    return dict(nodes=int(counts[0]), edges=int(counts[1]), bytes=int(counts[2]))
 
 
 def parse_spades_ids(raw: np.ndarray, hdr_start: np.ndarray, hdr_end: np.ndarray):

@@ -25,6 +25,15 @@ class EdgeArrays:
     def add_frame(self, df: pd.DataFrame):
         if len(df) == 0:
             return
+        def only(col):   # the label, when the column holds one value (what find_homologs_and_save writes)
+            c = df[col]
+            if isinstance(c.dtype, pd.CategoricalDtype) and len(c.cat.categories) == 1 and not c.isna().any():
+                return str(c.cat.categories[0])
+            return None
+        s1, q1 = only("ssample"), only("qsample")
+        if s1 is not None and q1 is not None:
+            self.add(s1, q1, df["sgene"].to_numpy(), df["qgene"].to_numpy())
+            return
         ss, qs = df["ssample"].astype(str).to_numpy(), df["qsample"].astype(str).to_numpy()
         if (ss == ss[0]).all() and (qs == qs[0]).all():
             self.add(ss[0], qs[0], df["sgene"].to_numpy(), df["qgene"].to_numpy())
@@ -37,6 +46,17 @@ class EdgeArrays:
         for s, q, sg, qg in self.groups:
             g.add_edges_from(zip(zip([s] * len(sg), sg.tolist()), zip([q] * len(qg), qg.tolist())))
         return g
+
+    def write_pickle(self, path) -> dict:
+        """graph.pkl straight from the flat arrays (native writer, csrc/host_graph.cu): the same plain
+        nx.Graph pickle as pickle.dump(self.to_networkx(), f), without building the Python object."""
+        from . import _native
+        index = {}
+        for s, q, _, _ in self.groups:
+            index.setdefault(s, len(index))
+            index.setdefault(q, len(index))
+        isolated = [(index.setdefault(str(n[0]), len(index)), int(n[1])) for n in getattr(self, "isolated", ())]
+        return _native.graph_pickle(path, list(index), [(index[s], index[q], sg, qg) for s, q, sg, qg in self.groups], isolated)
 
     @classmethod
     def from_networkx(cls, g: nx.Graph) -> "EdgeArrays":
@@ -127,6 +147,18 @@ def _mutator(name):
 for _name in ("add_node", "add_nodes_from", "remove_node", "remove_nodes_from", "add_edge", "add_edges_from",
               "add_weighted_edges_from", "remove_edge", "remove_edges_from", "update", "clear", "clear_edges"):
     setattr(GeneMatchGraph, _name, _mutator(_name))
+
+
+def dump_graph(graph: nx.Graph, path) -> None:
+    """pickle.dump(graph, f, HIGHEST_PROTOCOL) of filtering_step.py:158-159.  A GeneMatchGraph nobody has
+    looked at through the networkx API yet is written natively from its edge arrays and stays lazy."""
+    import pickle
+    e = getattr(graph, "rcq_edges", None)
+    if e is not None and not graph.__dict__.get("_rcq_built", True) and not graph.graph:
+        e.write_pickle(path)
+        return
+    with open(path, "wb") as f:
+        pickle.dump(graph, f, pickle.HIGHEST_PROTOCOL)
 
 
 def build_graph(dfs: Iterable[pd.DataFrame]) -> nx.Graph:

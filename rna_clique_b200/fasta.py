@@ -35,8 +35,8 @@ def read_fasta(path: Path) -> Fasta:
     if raw.size == 0:
         return Fasta([], np.zeros(0, np.uint8), np.zeros(1, np.int64))
     ascii_, offsets, hs, he = _native.fasta_parse(raw)
-    buf = raw.tobytes()
-    headers = [buf[a + 1:b].decode().rstrip("\r") for a, b in zip(hs.tolist(), he.tolist())]
+    mv = memoryview(raw)          # header lines are decoded from views: the file bytes are not copied
+    headers = [str(mv[a + 1:b], "utf-8").rstrip("\r") for a, b in zip(hs.tolist(), he.tolist())]
     return Fasta(headers, ascii_, offsets, raw, hs, he)
 
 

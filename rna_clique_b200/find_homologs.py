@@ -25,12 +25,25 @@ _INT_COLS = ["length", "mismatch", "gapopen", "qstart", "qend", "sstart", "send"
              "qgene", "qiso", "sgene", "siso"]
 
 
+def _smallest_int(a: np.ndarray) -> np.ndarray:
+    """pd.to_numeric(..., downcast="unsigned" / "signed"): the smallest integer dtype holding the values."""
+    if a.size == 0 or a.dtype.kind not in "iu":
+        return a
+    lo, hi = int(a.min()), int(a.max())
+    kinds = (np.uint8, np.uint16, np.uint32, np.uint64) if lo >= 0 else (np.int8, np.int16, np.int32, np.int64)
+    for t in kinds:
+        i = np.iinfo(t)
+        if i.min <= lo and hi <= i.max:
+            return a if a.dtype == t else a.astype(t)
+    return a
+
+
 def shrink_df(df: pd.DataFrame) -> pd.DataFrame:
     """Down-cast integer columns to the smallest width holding their values
     (reference shrink_df, find_homologs.py:58-80)."""
     for c in _INT_COLS:
         if c in df and len(df):
-            df[c] = pd.to_numeric(df[c], downcast="unsigned" if df[c].min() >= 0 else "signed")
+            df[c] = _smallest_int(df[c].to_numpy())
     return df
 
 
@@ -52,6 +65,15 @@ class SampleCache:
             s = _native.Sample(self.ctx, fa.ascii, fa.offsets, gene, iso, name=str(path))
             self._samples[key] = s
         return s
+
+    def preload(self, path: Path, parser, ascii_, offsets, gene, iso, lengths=None) -> None:
+        """Builds the sample of a FASTA file this process has just written from the records it wrote, so
+        that `get` does not read and parse the file again (same letters, offsets and ids by construction)."""
+        path = Path(path)
+        st = path.stat()
+        key = (str(path.resolve()), st.st_mtime_ns, st.st_size, id(parser))
+        if key not in self._samples:
+            self._samples[key] = _native.Sample(self.ctx, ascii_, offsets, gene, iso, name=str(path), lengths=lengths)
 
     def close(self):
         for s in self._samples.values():
@@ -90,16 +112,18 @@ def table_to_frame(cols: dict, n_db_bases_fwd: int, n_db_seqs_fwd: int, n_db_bas
     evalue = KA_K * np.maximum(qlen - la, 1.0) * np.maximum(nb - ns * la, 1.0) * np.exp(-KA_LAMBDA * score.astype(np.float64))
     b = (KA_LAMBDA * score - np.log(KA_K)) / np.log(2.0)
     bits = np.where(b > 99.9, np.round(b), np.round(b, 1))
+    ic = {c: _smallest_int(np.asarray(cols[c])) for c in _INT_COLS}      # shrink_df, before the frame is built
+    strands = pd.Series(["plus", "minus"])                                  # the frame's own string dtype
     df = pd.DataFrame({
         "pident": np.round(100.0 * cols["nident"] / np.maximum(cols["length"], 1), 3),
-        "length": cols["length"], "mismatch": cols["mismatch"], "gapopen": cols["gapopen"],
-        "qstart": cols["qstart"], "qend": cols["qend"], "sstart": cols["sstart"], "send": cols["send"],
-        "evalue": evalue, "bitscore": bits, "gaps": cols["gaps"], "nident": cols["nident"],
-        "sstrand": np.where(cols["minus"].astype(bool), "minus", "plus"),
-        "qgene": cols["qgene"], "qiso": cols["qiso"], "sgene": cols["sgene"], "siso": cols["siso"],
+        "length": ic["length"], "mismatch": ic["mismatch"], "gapopen": ic["gapopen"],
+        "qstart": ic["qstart"], "qend": ic["qend"], "sstart": ic["sstart"], "send": ic["send"],
+        "evalue": evalue, "bitscore": bits, "gaps": ic["gaps"], "nident": ic["nident"],
+        "sstrand": strands.take(cols["minus"].astype(np.int64)).reset_index(drop=True),
+        "qgene": ic["qgene"], "qiso": ic["qiso"], "sgene": ic["sgene"], "siso": ic["siso"],
         "reverse": rev,
     }, columns=COLUMNS)
-    return shrink_df(df)
+    return df
 
 
 class HomologFinder:

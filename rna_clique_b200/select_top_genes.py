@@ -68,10 +68,17 @@ class TopGeneSelector:
         return cls(lambda: read_fasta(Path(path)), *args, **kwargs)
 
 
-def select_top_and_save(out_dir: Path, transcripts: str, x: Path, *args) -> tuple[Path, str]:
-    """Writes out_dir/<x.stem>_top.fasta and returns (path, x.stem) (select_top_genes_all.py:12-46)."""
+def select_top_and_save(out_dir: Path, transcripts: str, x: Path, *args, preload=None) -> tuple[Path, str]:
+    """Writes out_dir/<x.stem>_top.fasta and returns (path, x.stem) (select_top_genes_all.py:12-46).
+    preload: a find_homologs.SampleCache that receives the written records right away (the pipeline
+    searches them next; the file is then not read back)."""
     x = Path(x)
     out = Path(out_dir) / (x.stem + "_top.fasta")
-    fa, keep, _, _, _ = TopGeneSelector.from_path(x / transcripts, *args).get_top_gene_seqs()
-    write_fasta(out, [fa.headers[i] for i in keep], fa.ascii, fa.offsets[:-1][keep], np.diff(fa.offsets)[keep])
+    sel = TopGeneSelector.from_path(x / transcripts, *args)
+    fa, keep, _, gene, iso = sel.get_top_gene_seqs()
+    starts, lengths = fa.offsets[:-1][keep], np.diff(fa.offsets)[keep]
+    write_fasta(out, [fa.headers[i] for i in keep], fa.ascii, starts, lengths)
+    if preload is not None:
+        preload.preload(out, sel.parser, fa.ascii, starts, np.asarray(gene, dtype=np.int32), np.asarray(iso, dtype=np.int32),
+                        lengths=lengths.astype(np.int32))
     return out, x.stem

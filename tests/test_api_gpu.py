@@ -134,3 +134,25 @@ def test_run_analysis_from_yaml(tmp_path):
     assert (tmp_path / "out" / "graph.pkl").is_file() and cfg.matrix.is_file() and len(list((tmp_path / "out" / "od2").iterdir())) == 3
     done = RNACliqueConfig.yaml_load(tmp_path / "out" / "config.yaml")
     assert done.finished is not None and sorted(done.path_to_sample.values()) == ["T0", "T1", "T2"]
+
+
+def test_preloaded_sample_equals_the_one_read_back_from_od1(tmp_path):
+    """filtering_step hands the selected records to the device while writing od1/*_top.fasta; the sample
+    must be the one that parsing the written file gives (what make_all_dbs did before)."""
+    from rna_clique_b200.find_homologs import SampleCache
+    from rna_clique_b200.select_top_genes import select_top_and_save
+    from rna_clique_b200.simulate import simulate, write_dataset
+    from rna_clique_b200.transcripts import default_parser
+    _, ts = simulate(2, 300, seed=8, mutation_rate=0.02)
+    dirs = write_dataset(tmp_path / "in", ts)
+    (tmp_path / "od1").mkdir()
+    pre, plain = SampleCache(), SampleCache()
+    out, _ = select_top_and_save(tmp_path / "od1", "transcripts.fasta", dirs[0], 120, default_parser, preload=pre)
+    assert len(pre._samples) == 1
+    a, b = pre.get(out, default_parser), plain.get(out, default_parser)
+    assert len(pre._samples) == 1                      # served from the preloaded entry, no second build
+    assert (a.n_seq, a.total, a.n_index) == (b.n_seq, b.total, b.n_index) and a.n_seq == 120
+    da, db = a.download(), b.download()
+    for k in da:
+        assert np.array_equal(da[k], db[k]), k
+    pre.close(); plain.close()
