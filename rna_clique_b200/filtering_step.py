@@ -11,7 +11,7 @@ from typing import Callable, Iterable
 from .build_graph import build_graph, dump_graph
 from .filtered_distance import SampleSimilarity
 from .find_all_pairs import find_all_pairs
-from .select_top_genes import select_top_and_save
+from .select_top_genes import select_top_and_save, select_top_and_save_all
 from .transcripts import default_parser
 
 
@@ -22,8 +22,8 @@ def filtering_step(dirs: Iterable[Path], out_dir_1: Path, out_dir_2: Path, cache
     # the selected records go to the device as they are written (the role of make_all_dbs right after):
     # od1/*_top.fasta is not read back
     from .find_homologs import default_cache
-    path_to_sample = dict(select_top_and_save(Path(out_dir_1), transcripts, Path(x), top_genes, id_parser, preload=default_cache())
-                          for x in dirs)
+    path_to_sample = select_top_and_save_all(Path(out_dir_1), transcripts, dirs, top_genes, id_parser,
+                                             preload=default_cache(), jobs=jobs)
     tables, table_paths, num_tables = find_all_pairs(path_to_sample, out_dir_2, cache_dir, path_to_sample.__getitem__,
                                                      hf_args=[id_parser, top_matches, evalue, keep_all], jobs=jobs)
     graph = build_graph(tables)

@@ -68,17 +68,52 @@ class TopGeneSelector:
         return cls(lambda: read_fasta(Path(path)), *args, **kwargs)
 
 
-def select_top_and_save(out_dir: Path, transcripts: str, x: Path, *args, preload=None) -> tuple[Path, str]:
-    """Writes out_dir/<x.stem>_top.fasta and returns (path, x.stem) (select_top_genes_all.py:12-46).
-    preload: a find_homologs.SampleCache that receives the written records right away (the pipeline
-    searches them next; the file is then not read back)."""
+def _select_and_write(out_dir: Path, transcripts: str, x: Path, *args):
+    """Host half of select_top_and_save (thread-safe: no device work): returns (out path, x.stem, records),
+    records = (parser, letters, starts, gene, iso, lengths) of what was written."""
     x = Path(x)
     out = Path(out_dir) / (x.stem + "_top.fasta")
     sel = TopGeneSelector.from_path(x / transcripts, *args)
     fa, keep, _, gene, iso = sel.get_top_gene_seqs()
     starts, lengths = fa.offsets[:-1][keep], np.diff(fa.offsets)[keep]
     write_fasta(out, [fa.headers[i] for i in keep], fa.ascii, starts, lengths)
+    return out, x.stem, (sel.parser, fa.ascii, starts, np.asarray(gene, dtype=np.int32), np.asarray(iso, dtype=np.int32),
+                         lengths.astype(np.int32))
+
+
+def select_top_and_save(out_dir: Path, transcripts: str, x: Path, *args, preload=None) -> tuple[Path, str]:
+    """Writes out_dir/<x.stem>_top.fasta and returns (path, x.stem) (select_top_genes_all.py:12-46).
+    preload: a find_homologs.SampleCache that receives the written records right away (the pipeline
+    searches them next; the file is then not read back)."""
+    out, stem, rec = _select_and_write(out_dir, transcripts, x, *args)
     if preload is not None:
-        preload.preload(out, sel.parser, fa.ascii, starts, np.asarray(gene, dtype=np.int32), np.asarray(iso, dtype=np.int32),
-                        lengths=lengths.astype(np.int32))
-    return out, x.stem
+        preload.preload(out, rec[0], rec[1], rec[2], rec[3], rec[4], lengths=rec[5])
+    return out, stem
+
+
+def select_top_and_save_all(out_dir: Path, transcripts: str, dirs, *args, preload=None, jobs: int = 1) -> dict:
+    """{top-genes path: sample name} in `dirs` order (filtering_step.py:128-143 runs select_top_and_save over
+    the samples with joblib).  The host half (read, parse, select, format, write) runs on up to `jobs`
+    threads - the native calls release the GIL - with at most `jobs` + 2 parsed files in memory at a time; the device half (preload) stays on the calling thread, in order."""
+    from concurrent.futures import ThreadPoolExecutor
+    dirs = [Path(d) for d in dirs]
+    workers = max(1, min(int(jobs or 1), len(dirs), 8))
+    out = {}
+    if workers == 1:
+        for d in dirs:
+            p, stem = select_top_and_save(out_dir, transcripts, d, *args, preload=preload)
+            out[p] = stem
+        return out
+    with ThreadPoolExecutor(workers) as pool:
+        window = workers + 2          # samples submitted but not yet handed to the device
+        futs = [pool.submit(_select_and_write, out_dir, transcripts, d, *args) for d in dirs[:window]]
+        for k in range(len(dirs)):
+            p, stem, rec = futs[k].result()
+            futs[k] = None
+            if k + window < len(dirs):
+                futs.append(pool.submit(_select_and_write, out_dir, transcripts, dirs[k + window], *args))
+            if preload is not None:
+                preload.preload(p, rec[0], rec[1], rec[2], rec[3], rec[4], lengths=rec[5])
+            out[p] = stem
+            del rec
+    return out
