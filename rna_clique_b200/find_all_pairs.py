@@ -11,6 +11,7 @@ import os
 from pathlib import Path
 from typing import Any, Callable, Iterable, Iterator, Mapping, Optional
 
+import numpy as np
 import pandas as pd
 
 from .find_homologs import HomologFinder, SampleCache, default_cache
@@ -21,10 +22,15 @@ def find_homologs_and_save(transcripts1: Path, transcripts2: Path, out_path: Pat
                            hf_args: Optional[Iterable] = None, hf_kwargs: Optional[Mapping[str, Any]] = None
                            ) -> pd.DataFrame:
     finder = HomologFinder(*(hf_args or []), **(hf_kwargs or {}))
-    table = finder.get_match_table(transcripts1, transcripts2)
-    table["ssample"] = str(transcripts1)
-    table["qsample"] = str(transcripts2)
-    table[["ssample", "qsample"]] = table[["ssample", "qsample"]].astype("category")
+    return _label_and_save(finder.get_match_table(transcripts1, transcripts2), transcripts1, transcripts2, out_path)
+
+
+def _label_and_save(table: pd.DataFrame, transcripts1: Path, transcripts2: Path, out_path: Optional[Path]) -> pd.DataFrame:
+    # the same two category columns as assigning the strings and .astype("category") (find_all_pairs.py:82-86),
+    # built from codes instead of 2 x len(table) Python strings
+    codes = np.zeros(len(table), dtype=np.int8)
+    table["ssample"] = pd.Categorical.from_codes(codes, categories=[str(transcripts1)])
+    table["qsample"] = pd.Categorical.from_codes(codes, categories=[str(transcripts2)])
     if out_path is not None:
         write_table(table, out_path)
     return table
@@ -58,9 +64,27 @@ def find_all_pairs(inputs: Iterable[Path], output_dir: Path, cache_dir: Path, pa
     cache = make_all_dbs(cache_dir, inputs, parser=hf_args[0] if hf_args else None)
 
     def tables():
-        for t1, t2 in itertools.combinations(inputs, 2):
-            yield find_homologs_and_save(t1, t2, make_output_path(output_dir, t1, t2, path_to_sample, ext),
-                                         hf_args, {"db_cache": cache})
+        # one pair ahead: a helper thread runs the search and the device->host copy of pair k+1 (native
+        # calls, GIL released; it is the only user of the cache's context meanwhile) while this thread turns
+        # pair k into its DataFrame and saves it
+        from concurrent.futures import ThreadPoolExecutor
+        from .find_homologs import table_to_frame
+        pairs = list(itertools.combinations(inputs, 2))
+        finder = HomologFinder(*hf_args, db_cache=cache)
+
+        def device_part(t1, t2):
+            t = finder.get_device_table(t1, t2)
+            try:
+                return t.download(), t.db
+            finally:
+                t.close()
+
+        with ThreadPoolExecutor(1) as pool:
+            fut = pool.submit(device_part, *pairs[0]) if pairs else None
+            for k, (t1, t2) in enumerate(pairs):
+                cols, db = fut.result()
+                fut = pool.submit(device_part, *pairs[k + 1]) if k + 1 < len(pairs) else None
+                yield _label_and_save(table_to_frame(cols, *db), t1, t2, make_output_path(output_dir, t1, t2, path_to_sample, ext))
 
     paths = (make_output_path(output_dir, t1, t2, path_to_sample, ext) for t1, t2 in itertools.combinations(inputs, 2))
     return tables(), paths, math.comb(len(inputs), 2)
