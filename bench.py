@@ -40,6 +40,7 @@ def parse_args():
     ap.add_argument("--seed", type=int, default=487)
     ap.add_argument("--cpu-sample", type=int, default=1500, help="top-gene transcripts per sample in the CPU legs")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-api-leg", action="store_true", help="skip timing rna_clique() from FASTA directories (N = 1 only)")
     ap.add_argument("--streams", type=int, default=3, help="CUDA streams (host threads) per GPU")
     ap.add_argument("--clock-interval", type=float, default=0.2, help="seconds between nvidia-smi/NVML clock samples (0 = off)")
     return ap.parse_args()
@@ -98,7 +99,7 @@ def make_inputs(a, device):
         inputs.append(dict(ascii=t.ascii, starts=offs[:-1].copy(), lengths=np.diff(offs).astype(np.int32),
                            coverage=t.coverage, gene=t.gene, iso=t.iso))
         labels.append(f"od1/{t.name}_top.fasta")
-    return tree, inputs, labels
+    return tree, inputs, labels, ts
 
 
 def cpu_pair_job(args):
@@ -171,6 +172,34 @@ def solo_kernel_times(eng, resident, labels, reps=3):
             "gapped_ms": st["gapped_dp"]["ms"] / max(st["gapped_dp"]["calls"], 1)}
 
 
+def run_api_leg(transcriptomes, a, engine_matrix):
+    """The reference-facing call itself: rna_clique() from transcriptome directories (FASTA on disk) to
+    od1/, od2/, graph.pkl and the matrix file, one warm-up call and one timed call.  Returns
+    (seconds, matrix equals the engine's)."""
+    import shutil
+    import tempfile
+    from pathlib import Path
+    from rna_clique_b200.find_homologs import default_cache
+    from rna_clique_b200.rna_clique import rna_clique
+    from rna_clique_b200.simulate import write_dataset
+    tmp = Path(tempfile.mkdtemp(prefix="rcq_api_"))
+    try:
+        dirs = write_dataset(tmp / "in", transcriptomes)
+        secs, same = None, None
+        for rep in range(2):
+            for d in ("od1", "od2"):
+                shutil.rmtree(tmp / d, ignore_errors=True)
+                (tmp / d).mkdir()
+            t0 = time.perf_counter()
+            sim, _ = rna_clique(dirs, tmp / "od1", tmp / "od2", tmp / "db", tmp / "graph.pkl", tmp / "matrix.pkl", a.top)
+            secs = time.perf_counter() - t0
+            same = bool(np.array_equal(sim.get_dissimilarity_df().to_numpy(), engine_matrix))
+        default_cache().close()
+        return secs, same
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+
+
 def main():
     a = parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -181,7 +210,7 @@ def main():
         if rank != 0:
             return
         import torch
-        _, inputs, labels = make_inputs(a, "cpu" if not torch.cuda.is_available() else "cuda")
+        _, inputs, labels, _ = make_inputs(a, "cpu" if not torch.cuda.is_available() else "cuda")
         from rna_clique_b200.engine import select_top_genes
         lengths_full = [int(s["lengths"][select_top_genes(s["coverage"], s["gene"], a.top)].sum()) for s in inputs]
         t, cores, desc, gcups = run_cpu_leg(inputs, a, lengths_full, a.steps, min(a.warmup, 1))
@@ -214,7 +243,7 @@ def main():
     eng = Engine(local, streams=a.streams)
     stream = torch.cuda.ExternalStream(eng.ctx.stream, device=torch.device("cuda", local))
 
-    _, inputs_dev, labels = make_inputs(a, f"cuda:{local}")
+    _, inputs_dev, labels, transcriptomes = make_inputs(a, f"cuda:{local}")
     torch.cuda.synchronize()
     # HBM-resident variant: top-gene selection already applied (starts/lengths of the kept transcripts)
     resident = []
@@ -350,6 +379,10 @@ def main():
                                    "seconds_sample": t}
         else:
             out["cpu_baseline"] = None
+        if not a.no_api_leg and world == 1:
+            secs, same = run_api_leg(transcriptomes, a, res["matrix"])
+            out["seconds_to_matrix"]["rna_clique_api_from_fasta_dirs"] = secs
+            out["seconds_to_matrix"]["api_matrix_equals_engine"] = same
         print(json.dumps(out))
     if dist is not None:
         dist.destroy_process_group()
