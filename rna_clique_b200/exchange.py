@@ -14,6 +14,14 @@ from . import _native
 NCOLS = 17
 
 
+def _is_nccl(dist) -> bool:
+    """The single-tensor all-gather is NCCL's; gloo (CPU tests, and the two-ranks-on-one-GPU test) takes lists."""
+    try:
+        return str(dist.get_backend()).lower() == "nccl"
+    except Exception:  # noqa: BLE001
+        return False
+
+
 def allgather_flat(dist, my_ids, my_chunks, n_total: int, device):
     """my_chunks[k]: 1-D int32 tensor owned by this rank for global item my_ids[k].
     Returns a list of n_total int32 tensors (every rank gets every item).
@@ -39,8 +47,10 @@ def allgather_flat(dist, my_ids, my_chunks, n_total: int, device):
         buf[off:off + c.numel()] = c.reshape(-1)
         off += c.numel()
     gathered = torch.empty((world, pad), dtype=torch.int32, device=device)
-    dist.all_gather_into_tensor(gathered, buf) if hasattr(dist, "all_gather_into_tensor") and device.type == "cuda" \
-        else dist.all_gather(list(gathered.unbind(0)), buf)
+    if _is_nccl(dist):
+        dist.all_gather_into_tensor(gathered, buf)
+    else:
+        dist.all_gather(list(gathered.unbind(0)), buf)
     if device.type == "cuda":
         # the consumers (rcq_table_from_flat) run on the library's own streams, which are not ordered
         # after torch's: finish the collective on the host before handing out views of `gathered`
@@ -93,7 +103,7 @@ class PipelinedShare:
         self.dist.all_reduce(metas)
         metas = metas.cpu().numpy()
         sizes = [max(int(metas[k - lo, self.meta_len - 1]), 1) for k in range(lo, hi)]
-        if hi - lo == self.world and self.world > 1 and self.device.type == "cuda":
+        if hi - lo == self.world and self.world > 1 and _is_nccl(self.dist):
             # a full round: every rank contributes one item, so the round is ONE all-gather (all NVLink ports
             # busy in both directions) instead of `world` broadcasts queued behind each other
             pad = max(sizes)
