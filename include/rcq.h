@@ -137,8 +137,10 @@ void rcq_table_free(rcq_table* t);
  * score), mismatch, gaps, gapopen, nident.  Returns the count; copies min(count, cap) rows. */
 int64_t rcq_debug_last_hsps(rcq_ctx* ctx, int32_t* out, int64_t cap);
 /* the HSP set is kept only after rcq_debug_keep_hsps(ctx, 1) (off by default: it costs a device-wide
- * allocation per search) */
-void rcq_debug_keep_hsps(rcq_ctx* ctx, int on);
+ * allocation per search); returns the previous setting.  Besides the tests it serves the isoform
+ * orientation search (export_orthologs.py:285-329 blast_pairwise_get_strands), which needs every HSP of a
+ * small self-search rather than the per-gene table. */
+int rcq_debug_keep_hsps(rcq_ctx* ctx, int on);
 /* Karlin-Altschul helpers shared by the host layer (blastn 1/-2 linear-gap parameters):
  * length adjustment and evalue of a raw score for query length m against a db (n bases, nseq). */
 int32_t rcq_length_adjustment(int64_t m, int64_t n, int64_t nseq);

@@ -92,7 +92,7 @@ def lib():
         L.rcq_top_gene_mask.argtypes = [vp, vp, i64, i64, vp]
         L.rcq_top_gene_mask.restype = i64
         L.rcq_debug_keep_hsps.argtypes = [vp, C.c_int]
-        L.rcq_debug_keep_hsps.restype = None
+        L.rcq_debug_keep_hsps.restype = C.c_int
         L.rcq_length_adjustment.argtypes = [i64, i64, i64]
         L.rcq_length_adjustment.restype = i32
         L.rcq_evalue.argtypes = [i32, i64, i64, i64]
@@ -358,8 +358,9 @@ def top_gene_mask(coverage, gene, top: int) -> np.ndarray:
     return np.flatnonzero(keep)
 
 
-def debug_keep_hsps(ctx: Context, on: bool = True) -> None:
-    lib().rcq_debug_keep_hsps(ctx.h, int(on))
+def debug_keep_hsps(ctx: Context, on: bool = True) -> bool:
+    """Switches the per-search copy of the gapped HSP set on or off; returns the previous setting."""
+    return bool(lib().rcq_debug_keep_hsps(ctx.h, int(on)))
 
 
 def debug_last_hsps(ctx: Context) -> np.ndarray:

@@ -348,8 +348,11 @@ extern "C" int rcq_table_download(const rcq_table* t, rcq_table_cols* h) {
     return 0;
 }
 
-extern "C" void rcq_debug_keep_hsps(rcq_ctx* ctx, int on) {
-    if (ctx) ctx->dbg_keep = on;
+extern "C" int rcq_debug_keep_hsps(rcq_ctx* ctx, int on) {
+    if (!ctx) return 0;
+    const int before = ctx->dbg_keep ? 1 : 0;
+    ctx->dbg_keep = on;
+    return before;
 }
 
 extern "C" int64_t rcq_debug_last_hsps(rcq_ctx* ctx, int32_t* out, int64_t cap) {

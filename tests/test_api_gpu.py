@@ -156,3 +156,37 @@ def test_preloaded_sample_equals_the_one_read_back_from_od1(tmp_path):
     for k in da:
         assert np.array_equal(da[k], db[k]), k
     pre.close(); plain.close()
+
+
+def test_pairwise_strands_of_isoforms(ctx):
+    """export_orthologs.blast_pairwise_get_strands on the device search: orientation per isoform pair,
+    against the same reduction of the oracle's HSP set."""
+    from collections import namedtuple
+    from oracle import oracle as O
+    from rna_clique_b200.pairwise_strands import pairwise_get_strands
+    Rec = namedtuple("Rec", "id seq")
+    rng = np.random.default_rng(12)
+    comp = bytes.maketrans(b"ACGT", b"TGCA")
+    base = bytes(rng.choice(np.frombuffer(b"ACGT", dtype=np.uint8), size=1500))
+    other = bytes(rng.choice(np.frombuffer(b"ACGT", dtype=np.uint8), size=900))
+    recs = [(1, Rec("NODE_1_g5_i1", base.decode())),
+            (2, Rec("NODE_2_g5_i2", base[200:1300].translate(comp)[::-1].decode())),     # reverse complement of a part
+            (3, Rec("NODE_3_g5_i3", (base[:700] + base[760:]).decode())),                # an exon skipped
+            (4, Rec("NODE_4_g5_i4", other.decode()))]                                    # unrelated
+    got = list(pairwise_get_strands(recs, ctx=ctx))
+    assert got == [((2, "NODE_2_g5_i2"), (1, "NODE_1_g5_i1"), -1),
+                   ((3, "NODE_3_g5_i3"), (1, "NODE_1_g5_i1"), 1),
+                   ((3, "NODE_3_g5_i3"), (2, "NODE_2_g5_i2"), -1)]
+    # the oracle's HSPs through the same reduction
+    seqs = [r.seq.encode() for _, r in recs]
+    offs = np.concatenate([[0], np.cumsum([len(s) for s in seqs])]).astype(np.int64)
+    s = O.Sample(np.frombuffer(b"".join(seqs), dtype=np.uint8), offs, np.arange(4, dtype=np.int32), np.ones(4, dtype=np.int32))
+    hs = O.search_pair(s, s, evalue=1.0).hsps()
+    names = [r.id for _, r in recs]
+    best = {}
+    for row in hs.tolist():
+        q, t = names[row[1]], names[row[0]]
+        if q > t and (best.get((q, t)) is None or row[7] > best[(q, t)][0]):
+            best[(q, t)] = (row[7], row[2])
+    assert {k: (-1 if v[1] else 1) for k, v in best.items()} == {(a[1], b[1]): sgn for a, b, sgn in got}
+    assert list(pairwise_get_strands(recs[:1], ctx=ctx)) == []
