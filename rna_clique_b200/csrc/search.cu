@@ -111,6 +111,10 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
         st.n_verified = ctx->h_pin[1];
         st.n_candidates = ctx->h_pin[2];
         tfree(ctx, cand); cand = nullptr;
+        if (st.n_verified >= (1ll << 31) || n_seeds >= (1ll << 31))
+            return rcq_fail(RCQ_ERR_CAPACITY, "rcq_search_pair: more than 2^31 seed candidates in one pair - low-complexity "
+                            "stretches (poly-A tails, microsatellites) shared by many transcripts; there is no DUST filter "
+                            "yet (DESIGN.md section 3), trim or mask them before the search");
         if (n_seeds <= cap && st.n_verified <= ccap) break;
         tfree(ctx, seeds); seeds = nullptr;
         cap = std::max(cap, n_seeds);

@@ -163,3 +163,21 @@ def test_drifting_band_uses_the_wide_fallback(ctx, length):
     got = np.stack([cols[c] for c in _native.TABLE_COLS] + [cols["minus"].astype(np.int32), cols["reverse"].astype(np.int32)], axis=1)
     assert np.array_equal(got, res.rows(2)) and len(tab) == 2 * n
     assert (cols["gaps"] > 100).all()
+
+
+def test_shared_low_complexity_tails_fail_with_a_clear_message(ctx):
+    """No DUST filter yet: thousands of transcripts sharing a poly-A tail seed against each other
+    quadratically.  The search must stop with RCQ_ERR_CAPACITY and say why, not exhaust the device."""
+    from rna_clique_b200 import _native
+    rng = np.random.default_rng(2)
+    n, body, tail = 5000, 60, 40
+    letters = np.frombuffer(b"ACGT", dtype=np.uint8)
+    seqs = np.concatenate([np.concatenate([letters[rng.integers(0, 4, size=body)], np.full(tail, ord("A"), dtype=np.uint8)])
+                           for _ in range(n)])
+    offs = np.arange(n + 1, dtype=np.int64) * (body + tail)
+    ids = np.arange(n, dtype=np.int32)
+    a = _native.Sample(ctx, seqs, offs, ids, np.ones(n, dtype=np.int32))
+    b = _native.Sample(ctx, seqs[::1].copy(), offs, ids, np.ones(n, dtype=np.int32))
+    with pytest.raises(RuntimeError, match="low-complexity"):
+        _native.search_pair(ctx, a, b)
+    a.close(); b.close()
