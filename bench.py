@@ -237,7 +237,15 @@ def main():
             os.environ.pop("NCCL_DEBUG")
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         import torch.distributed as dist_mod
-        dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local))
+        # NCCL's kernels on a high-priority stream: the sample exchange runs behind the searches, and its thread
+        # blocks should be the first to get an SM when one frees up
+        opts = None
+        if os.environ.get("RCQ_NCCL_PRIORITY", "1") != "0":
+            try:
+                opts = dist_mod.ProcessGroupNCCL.Options(is_high_priority_stream=True)
+            except Exception:  # noqa: BLE001
+                opts = None
+        dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local), pg_options=opts)
         dist = dist_mod
     from rna_clique_b200.engine import Engine, select_top_genes
     eng = Engine(local, streams=a.streams)

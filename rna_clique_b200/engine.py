@@ -12,6 +12,7 @@ collective is an all-gather of the flat hit tables (torch.distributed, NCCL) bef
 from __future__ import annotations
 
 import itertools
+import os
 import time
 from concurrent.futures import ThreadPoolExecutor
 from fractions import Fraction
@@ -53,6 +54,7 @@ class Engine:
         self.ctx = self.ctxs[0]
         self.device = device
         self._pool = ThreadPoolExecutor(len(self.ctxs)) if len(self.ctxs) > 1 else None
+        self._meta_group = None       # second process group for the metadata of the N > 1 sample exchange
 
     def _fan_out(self, n_items: int, fn):
         """out[k] = fn(ctx, k) for k < n_items; item k runs on context k % streams, and each context
@@ -98,7 +100,7 @@ class Engine:
                 staged[k] = (dst, ev)
         return staged
 
-    def _run_tasks(self, tasks, ready, run):
+    def _run_tasks(self, tasks, ready, run, poll: Optional[float] = None):
         """Workers (one per context) drain `tasks` in list order: worker w takes the first open task with
         ready(task, w) (evaluated under the lock) and calls run(ctx, task), which stores its own result.
         An exception in any worker is re-raised here."""
@@ -107,6 +109,10 @@ class Engine:
         state = {"next": [True] * len(tasks), "left": len(tasks), "err": None}
 
         S = len(self.ctxs)
+        # RCQ_TRACE_TASKS=1: (worker, task, start ms, end ms) of every task of the last call in self.task_trace
+        trace = [] if os.environ.get("RCQ_TRACE_TASKS") else None
+        self.task_trace = trace
+        t_base = time.perf_counter()
 
         def work(w):
             ctx = self.ctxs[w]
@@ -127,10 +133,14 @@ class Engine:
                         if pick is None:
                             if not pending:
                                 return
-                            cv.wait()
+                            cv.wait(poll)     # poll: readiness may change without a notify (a collective finishing)
                     state["next"][pick] = False
                 try:
+                    if trace is not None:
+                        t0 = time.perf_counter()
                     run(ctx, tasks[pick])
+                    if trace is not None:
+                        trace.append((w, tasks[pick], t0 - t_base, time.perf_counter() - t_base))
                 except BaseException as e:  # noqa: BLE001
                     with cv:
                         state["err"] = e
@@ -247,14 +257,14 @@ class Engine:
             import torch
             from .exchange import PipelinedShare
             device = torch.device("cuda", self.device)
-            share = PipelinedShare(dist, n, device)
-            by_round = {}
-            for slot, k in enumerate(mine):
-                by_round.setdefault(max(pairs[k]) // world, []).append(slot)
+            if getattr(self, "_meta_group", None) is None:
+                self._meta_group = dist.new_group()      # collective: every rank makes its first N > 1 call here
+            share = PipelinedShare(dist, n, device, meta_group=self._meta_group)
+            # list order is priority: builds, then arrivals (cheap, and they unlock searches), then searches by
+            # the round of their later sample
             tasks = [("b", j) for j in range(share.rounds)]
-            for j in range(share.rounds):
-                tasks.extend(("u", k) for k in range(j * world, min(n, (j + 1) * world)) if k % world != rank)
-                tasks.extend(("s", slot) for slot in by_round.get(j, []))
+            tasks.extend(("u", k) for k in range(n) if k % world != rank)
+            tasks.extend(("s", slot) for slot in sorted(range(len(mine)), key=lambda x: (max(pairs[mine[x]]) // world, x)))
         else:
             by_last = {}
             for slot, k in enumerate(mine):
@@ -273,7 +283,8 @@ class Engine:
                 if share is None:
                     return x % S == w
                 # arrivals go to the workers that do not build (worker 0 is busy with its "b" tasks first)
-                return share.is_issued(x) and (S == 1 or 1 + x % (S - 1) == w)
+                # (taken only once the data is there: a worker never sits in a wait while searches are ready)
+                return share.arrived(x) and (S == 1 or 1 + x % (S - 1) == w)
             i, j = pairs[mine[x]]
             return samples[i] is not None and samples[j] is not None
 
@@ -295,7 +306,7 @@ class Engine:
                 i, j = pairs[mine[x]]
                 my_tables[x] = _native.search_pair(ctx, samples[i], samples[j], evalue, top_n, keep_all)
 
-        self._run_tasks(tasks, ready, run)
+        self._run_tasks(tasks, ready, run, poll=0.0003 if share is not None else None)
         if share is not None:
             share.finish()
         t_upload = time.perf_counter()

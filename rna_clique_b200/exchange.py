@@ -75,9 +75,12 @@ class PipelinedShare:
     meta_of(obj) -> int64[meta_len] whose last entry is the flat byte size; export_to(obj, uint8 tensor)
     fills the flat buffer on the owner; import_from(k, meta, uint8 tensor) rebuilds it elsewhere."""
 
-    def __init__(self, dist, n_items: int, device, meta_len: int = 8):
+    def __init__(self, dist, n_items: int, device, meta_len: int = 8, meta_group=None):
         import threading
         self.dist, self.n, self.device, self.meta_len = dist, n_items, device, meta_len
+        # the metadata all-reduce may run on its own process group (own NCCL stream): on the default one it
+        # would queue behind the payload of the previous round and hold back the next round's sends
+        self.meta_group = meta_group
         self.world, self.rank = dist.get_world_size(), dist.get_rank()
         self.rounds = (n_items + self.world - 1) // self.world
         self.metas = [None] * n_items
@@ -94,13 +97,17 @@ class PipelinedShare:
     def is_issued(self, k: int) -> bool:
         return self.issued[k].is_set()
 
+    def arrived(self, k: int) -> bool:
+        """Item k's collective has finished on the device (non-blocking): `fetch(k)` will not wait."""
+        return self.issued[k].is_set() and bool(self.works[k].is_completed())
+
     def issue_round(self, j: int, obj, meta_of, export_to) -> None:
         lo, hi = j * self.world, min(self.n, (j + 1) * self.world)
         own = self.own_item(j)
         metas = torch.zeros((hi - lo, self.meta_len), dtype=torch.int64, device=self.device)
         if own is not None:
             metas[own - lo] = torch.as_tensor(np.asarray(meta_of(obj), dtype=np.int64), device=self.device)
-        self.dist.all_reduce(metas)
+        self.dist.all_reduce(metas, group=self.meta_group)
         metas = metas.cpu().numpy()
         sizes = [max(int(metas[k - lo, self.meta_len - 1]), 1) for k in range(lo, hi)]
         if hi - lo == self.world and self.world > 1 and _is_nccl(self.dist):
