@@ -11,7 +11,9 @@
 // dicts are memoised, because nothing else is referenced twice.
 #include <cstdio>
 #include <cstring>
+#include <new>
 #include <string>
+#include <unordered_map>
 #include <vector>
 #include "common.cuh"
 
@@ -42,10 +44,10 @@ struct PickleOut {
 // Groups g = 0..n_groups-1 hold rows [g_off[g], g_off[g+1]) of (sgene, qgene) between samples g_s[g] and
 // g_q[g] (indices into sample_names); isolated nodes (degree 0) follow the edges.  counts[0] = nodes,
 // counts[1] = distinct undirected edges, counts[2] = bytes written.
-extern "C" int rcq_graph_pickle(const char* path, int32_t n_samples, const char* const* sample_names,
-                                int32_t n_groups, const int32_t* g_s, const int32_t* g_q, const int64_t* g_off,
-                                const int32_t* sgene, const int32_t* qgene, int64_t n_isolated,
-                                const int32_t* iso_sample, const int32_t* iso_gene, int64_t counts[3]) {
+static int graph_pickle_impl(const char* path, int32_t n_samples, const char* const* sample_names,
+                             int32_t n_groups, const int32_t* g_s, const int32_t* g_q, const int64_t* g_off,
+                             const int32_t* sgene, const int32_t* qgene, int64_t n_isolated,
+                             const int32_t* iso_sample, const int32_t* iso_gene, int64_t counts[3]) {
     if (!path || n_samples < 0 || n_groups < 0 || n_isolated < 0 || (n_samples && !sample_names) ||
         (n_groups && (!g_s || !g_q || !g_off)) || (n_isolated && (!iso_sample || !iso_gene)))
         return rcq_fail(RCQ_ERR_ARG, "rcq_graph_pickle: bad argument");
@@ -67,12 +69,27 @@ extern "C" int rcq_graph_pickle(const char* path, int32_t n_samples, const char*
             return rcq_fail(RCQ_ERR_ARG, "rcq_graph_pickle: bad isolated node");
         if (iso_gene[i] > max_gene[iso_sample[i]]) max_gene[iso_sample[i]] = iso_gene[i];
     }
+    // (sample, gene) -> node id: dense tables when the gene ids are compact (rnaSPAdes numbering), a hash map
+    // when a custom id parser produces large sparse ids
+    int64_t span = 0;
+    for (int32_t s = 0; s < n_samples; s++) span += (int64_t)max_gene[s] + 1;
+    const bool dense = span <= 16 * (n_rows + n_isolated) + (1 << 20);
     std::vector<std::vector<int32_t>> id((size_t)n_samples);
-    for (int32_t s = 0; s < n_samples; s++) id[s].assign((size_t)(max_gene[s] + 1), -1);
+    std::unordered_map<uint64_t, int32_t> sparse;
+    if (dense) for (int32_t s = 0; s < n_samples; s++) id[s].assign((size_t)(max_gene[s] + 1), -1);
+    else sparse.reserve((size_t)(2 * n_rows + n_isolated));
     std::vector<int32_t> node_sample, node_gene;
     auto node_of = [&](int32_t s, int32_t gene) {
-        int32_t& x = id[s][gene];
-        if (x < 0) { x = (int32_t)node_sample.size(); node_sample.push_back(s); node_gene.push_back(gene); }
+        if (dense) {
+            int32_t& x = id[s][gene];
+            if (x < 0) { x = (int32_t)node_sample.size(); node_sample.push_back(s); node_gene.push_back(gene); }
+            return x;
+        }
+        auto it = sparse.find(((uint64_t)(uint32_t)s << 32) | (uint32_t)gene);
+        if (it != sparse.end()) return it->second;
+        const int32_t x = (int32_t)node_sample.size();
+        sparse.emplace(((uint64_t)(uint32_t)s << 32) | (uint32_t)gene, x);
+        node_sample.push_back(s); node_gene.push_back(gene);
         return x;
     };
     // ---- distinct undirected edges in insertion order (open-addressing set of (min, max) node pairs)
@@ -150,4 +167,16 @@ extern "C" int rcq_graph_pickle(const char* path, int32_t n_samples, const char*
     if (fclose(f) != 0 || w != P.b.size()) return rcq_fail(RCQ_ERR_ARG, "rcq_graph_pickle: short write");
     if (counts) { counts[0] = n_nodes; counts[1] = n_edges; counts[2] = (int64_t)P.b.size(); }
     return 0;
+}
+
+extern "C" int rcq_graph_pickle(const char* path, int32_t n_samples, const char* const* sample_names,
+                                int32_t n_groups, const int32_t* g_s, const int32_t* g_q, const int64_t* g_off,
+                                const int32_t* sgene, const int32_t* qgene, int64_t n_isolated,
+                                const int32_t* iso_sample, const int32_t* iso_gene, int64_t counts[3]) {
+    try {   // no C++ exception may cross the C ABI
+        return graph_pickle_impl(path, n_samples, sample_names, n_groups, g_s, g_q, g_off, sgene, qgene, n_isolated,
+                                 iso_sample, iso_gene, counts);
+    } catch (const std::bad_alloc&) {
+        return rcq_fail(RCQ_ERR_CAPACITY, "rcq_graph_pickle: out of host memory");
+    }
 }

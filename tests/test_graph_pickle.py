@@ -84,3 +84,9 @@ def test_dump_graph_keeps_the_graph_lazy_and_falls_back(tmp_path):
     loop.write_pickle(tmp_path / "l.pkl")
     lg = pickle.load(open(tmp_path / "l.pkl", "rb"))
     assert list(lg.edges) == [(("s", 5), ("s", 5)), (("s", 5), ("s", 6))] and list(lg.adj[("s", 5)]) == [("s", 5), ("s", 6)]
+    # large sparse gene ids (a custom id parser): the hash-map node table
+    sp = EdgeArrays()
+    sp.add("a", "b", [2_000_000_000, 5, 2_000_000_000], [1_999_999_999, 5, 1_999_999_999])
+    sp.write_pickle(tmp_path / "s.pkl")
+    sg = pickle.load(open(tmp_path / "s.pkl", "rb"))
+    assert list(sg.nodes) == [("a", 2_000_000_000), ("b", 1_999_999_999), ("a", 5), ("b", 5)] and sg.number_of_edges() == 2
