@@ -39,7 +39,7 @@ def build_native(force: bool = False, verbose: bool = False) -> Path:
         if verbose:
             print(out)
     if force or procs or _stale(LIB, objs):
-        cmd = [NVCC, "-shared", "-o", str(LIB), *map(str, objs), "-lcudart"]
+        cmd = [NVCC, *FLAGS[:2], "-shared", "-o", str(LIB), *map(str, objs), "-lcudart"]
         subprocess.run(cmd, check=True)
     return LIB
 
