@@ -91,6 +91,31 @@ def default_cache() -> SampleCache:
     return _default_cache
 
 
+def blast_printed_bitscore(b: np.ndarray) -> np.ndarray:
+    """Bit scores as blastn's tabular output prints them (and simple_blast parses them back): above 99.9
+    the value is TRUNCATED to an integer ("%3.0ld" of (long)bit_score), otherwise one decimal ("%4.1lf").
+    Pinned by the real rows of the reference's docs/formats.md:260-273 (tests/golden/blast_rows_formats_md.json):
+    nident 2309 / mismatch 19 -> 4194.86 bits -> printed 4194."""
+    b = np.asarray(b, dtype=np.float64)
+    return np.where(b > 99.9, np.floor(b), np.round(b, 1))
+
+
+def blast_printed_evalue(e: np.ndarray) -> np.ndarray:
+    """E-values as blastn's tabular output prints them: "0.0" below 1e-180, three significant digits
+    ("%.2le") for small values (docs/formats.md:271 shows 8.75e-152), BLAST's fixed formats from 0.0009 up."""
+    e = np.asarray(e, dtype=np.float64)
+    out = e.copy()
+    small = (e >= 1e-180) & (e < 0.0009)
+    # round-trip through the decimal string: exactly what parsing BLAST's text yields
+    if small.any():
+        out[small] = [float(f"{x:.2e}") for x in e[small]]
+    out[e < 1e-180] = 0.0
+    for lo, hi, nd in ((0.0009, 0.1, 3), (0.1, 1.0, 2), (1.0, 10.0, 1), (10.0, np.inf, 0)):
+        m = (e >= lo) & (e < hi)
+        out[m] = np.round(e[m], nd)
+    return out
+
+
 def table_to_frame(cols: dict, n_db_bases_fwd: int, n_db_seqs_fwd: int, n_db_bases_bwd: int,
                    n_db_seqs_bwd: int) -> pd.DataFrame:
     """Device columns -> the reference's DataFrame.  pident / evalue / bitscore are derived here in
@@ -110,8 +135,8 @@ def table_to_frame(cols: dict, n_db_bases_fwd: int, n_db_seqs_fwd: int, n_db_bas
     nb = np.where(rev, n_db_bases_bwd, n_db_bases_fwd).astype(np.float64)
     ns = np.where(rev, n_db_seqs_bwd, n_db_seqs_fwd).astype(np.float64)
     evalue = KA_K * np.maximum(qlen - la, 1.0) * np.maximum(nb - ns * la, 1.0) * np.exp(-KA_LAMBDA * score.astype(np.float64))
-    b = (KA_LAMBDA * score - np.log(KA_K)) / np.log(2.0)
-    bits = np.where(b > 99.9, np.round(b), np.round(b, 1))
+    evalue = blast_printed_evalue(evalue)
+    bits = blast_printed_bitscore((KA_LAMBDA * score - np.log(KA_K)) / np.log(2.0))
     ic = {c: _smallest_int(np.asarray(cols[c])) for c in _INT_COLS}      # shrink_df, before the frame is built
     strands = pd.Series(["plus", "minus"])                                  # the frame's own string dtype
     df = pd.DataFrame({
