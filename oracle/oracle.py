@@ -37,6 +37,8 @@ def lib():
         L.orc_sample_free.argtypes = [C.c_void_p]
         L.orc_search_pair.restype = C.c_void_p
         L.orc_search_pair.argtypes = [C.c_void_p, C.c_void_p, C.c_double, C.c_int, C.c_int]
+        L.orc_search_pair_directions.restype = C.c_void_p
+        L.orc_search_pair_directions.argtypes = [C.c_void_p, C.c_void_p, C.c_double, C.c_int, C.c_int]
         L.orc_match_table_from_rows.restype = C.c_void_p
         L.orc_match_table_from_rows.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int, C.c_int]
         L.orc_result_free.argtypes = [C.c_void_p]
@@ -94,8 +96,12 @@ class Result:
             self.h = None
 
 
-def search_pair(s1: Sample, s2: Sample, evalue: float = 1e-99, top_n: int = 1, keep_all: bool = True) -> Result:
-    return Result(lib().orc_search_pair(s1.h, s2.h, evalue, top_n, int(keep_all)))
+def search_pair(s1: Sample, s2: Sample, evalue: float = 1e-99, top_n: int = 1, keep_all: bool = True,
+                independent_directions: bool = False) -> Result:
+    """independent_directions: run the two blastn directions of find_homologs.py:229-239 as two searches with
+    their own query roles instead of deriving both frames from one search (see rcq_oracle.c)."""
+    fn = lib().orc_search_pair_directions if independent_directions else lib().orc_search_pair
+    return Result(fn(s1.h, s2.h, evalue, top_n, int(keep_all)))
 
 
 def match_table_from_rows(fwd: np.ndarray, bwd: np.ndarray, top_n: int = 1, keep_all: bool = True) -> Result:

@@ -699,6 +699,40 @@ orc_result* orc_search_pair(const orc_sample* s1, const orc_sample* s2, double e
     res->n_seeds = g_seeds - sd0;
     return res;
 }
+/* The two blastn runs of find_homologs.py:229-239 as two INDEPENDENT searches, each with its own query
+ * role: forward = query sample 2 against database sample 1, backward = query sample 1 against
+ * database sample 2.  In each the query transcript plays the part of `q` in the extensions (gap tie
+ * rule, start point, diagonal rule run in the query's own orientation), exactly as in the backward
+ * search of orc_search_pair.  orc_search_pair derives BOTH frames from the one search with sample 1 as
+ * the query (the product's shortcut: one search per unordered pair); this entry measures what the
+ * shortcut changes (tools/direction_asymmetry.py, DESIGN.md section 3 "Not modelled"). */
+orc_result* orc_search_pair_directions(const orc_sample* s1, const orc_sample* s2, double evalue, int top_n,
+                                       int keep_all) {
+    orc_result* res = calloc(1, sizeof *res);
+    int64_t c0 = g_dp_cells, sd0 = g_seeds;
+    double log_cut = evalue > 0 ? log(evalue) : -INFINITY;
+    uvec_t U = find_ungapped(s1, s2);
+    res->n_ungapped = U.n;
+    res->G = find_gapped(s1, s2, &U);          /* backward search: query = sample 1 */
+    free(U.v);
+    res->B = direction_rows(s1, s2, &res->G, 1, log_cut);
+    uvec_t U2 = find_ungapped(s2, s1);         /* forward search: query = sample 2 */
+    gvec_t Gf = find_gapped(s2, s1, &U2);
+    free(U2.v);
+    res->F = direction_rows(s2, s1, &Gf, 1, log_cut);   /* rows with q = sample 2, s = sample 1 */
+    for (int64_t i = 0; i < res->F.n; i++) res->F.v[i].reverse = 0;
+    free(Gf.v);
+    select_topn(&res->F, 0, top_n, 1);
+    select_topn(&res->B, 0, top_n, 1);
+    rvec_t Fc = res->F, Bc = res->B;
+    Fc.v = malloc(sizeof(row_t) * (Fc.n + 1)); memcpy(Fc.v, res->F.v, sizeof(row_t) * Fc.n);
+    Bc.v = malloc(sizeof(row_t) * (Bc.n + 1)); memcpy(Bc.v, res->B.v, sizeof(row_t) * Bc.n);
+    res->T = match_table(&Fc, &Bc, top_n, keep_all);
+    free(Fc.v); free(Bc.v);
+    res->dp_cells = g_dp_cells - c0;
+    res->n_seeds = g_seeds - sd0;
+    return res;
+}
 void orc_result_free(orc_result* r) {
     if (!r) return;
     free(r->G.v); free(r->F.v); free(r->B.v); free(r->T.v); free(r);

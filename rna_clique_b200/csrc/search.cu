@@ -68,8 +68,7 @@ static int read_counters(rcq_ctx* ctx, int n) {
 extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sample* s2, double evalue,
                                int32_t top_n, int32_t keep_all, rcq_table** out, rcq_search_stats* stats) {
     if (!ctx || !s1 || !s2 || !out) return rcq_fail(RCQ_ERR_ARG, "rcq_search_pair: bad argument");
-    if (top_n != 1)
-        return rcq_fail(RCQ_ERR_ARG, "rcq_search_pair: only top_n == 1 (the reference default) is implemented on the device");
+    if (top_n < 1) return rcq_fail(RCQ_ERR_ARG, "rcq_search_pair: top_n must be >= 1");
     if (s1->n_genes >= (1 << 20) || s2->n_genes >= (1 << 20))
         return rcq_fail(RCQ_ERR_CAPACITY, "rcq_search_pair: more than 2^20 genes in a sample");
     CU(cudaSetDevice(ctx->device));
@@ -85,16 +84,22 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
     P.nA = s1->n_seq; P.nB = s2->n_seq; P.selA = s1->sel; P.selB = s2->sel;
     P.blkA = s1->blk2tx; P.blkB = s2->blk2tx; P.olA = s1->ol; P.olB = s2->ol;
     unsigned long long* ctr = (unsigned long long*)ctx->d_ctr;
-    rcq_table* T = new rcq_table();
+    // the table handle reaches the caller only on success: every error return below frees it
+    struct TableGuard {
+        rcq_table* t;
+        ~TableGuard() { if (t) { dfree(t->ctx, t->cols); delete t; } }
+    } guard{new rcq_table()};
+    rcq_table* T = guard.t;
     T->ctx = ctx;
-    *out = T;
+    *out = nullptr;
 
     // ---- seeds: probe (index join) -> candidate list -> verify
     Seed* seeds = nullptr;
     uint2* cand = nullptr;
     int64_t n_seeds = 0, cap = std::max<int64_t>(1 << 20, 48ll * std::max(s1->n_seq, s2->n_seq));
     int64_t ccap = std::max<int64_t>(1 << 20, s1->n_index / 2);
-    for (int attempt = 0; attempt < 3 && s1->n_index && s2->n_index; attempt++) {
+    bool seeded = !(s1->n_index && s2->n_index);
+    for (int attempt = 0; attempt < 3 && !seeded; attempt++) {
         RC(talloc(ctx, &seeds, cap));
         RC(talloc(ctx, &cand, ccap));
         CU(cudaMemsetAsync(ctr, 0, 16 * sizeof(int64_t), ctx->stream));
@@ -115,12 +120,13 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
             return rcq_fail(RCQ_ERR_CAPACITY, "rcq_search_pair: more than 2^31 seed candidates in one pair - low-complexity "
                             "stretches (poly-A tails, microsatellites) shared by many transcripts; there is no DUST filter "
                             "yet (DESIGN.md section 3), trim or mask them before the search");
-        if (n_seeds <= cap && st.n_verified <= ccap) break;
+        if (n_seeds <= cap && st.n_verified <= ccap) { seeded = true; break; }
         tfree(ctx, seeds); seeds = nullptr;
         cap = std::max(cap, n_seeds);
         ccap = std::max(ccap, st.n_verified);
         n_seeds = 0;
     }
+    if (!seeded) return rcq_fail(RCQ_ERR_CAPACITY, "rcq_search_pair: the seed lists kept growing between attempts");
     st.n_seeds = n_seeds;
     if (n_seeds >= (1ll << 31)) return rcq_fail(RCQ_ERR_CAPACITY, "rcq_search_pair: too many seeds");
     int64_t n_gapped = 0;
@@ -215,7 +221,7 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
         CU(cudaMemsetAsync(G, 0xFF, n_slots * sizeof(Gapped), ctx->stream));
         const int threads = 128;
         const bool masked = s1->n_masked || s2->n_masked;
-        static int occ[2] = {0, 0};   // resident blocks per SM of the two variants
+        int* occ = ctx->gapped_occ;   // resident blocks per SM of the two variants (per context: contexts run on their own threads)
         if (!occ[masked]) {
             int nb = 0;
             if (masked) CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_gapped<true>, threads, 0));
@@ -270,6 +276,7 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
         V.lenA = s1->len; V.lenB = s2->len; V.gidxA = s1->gidx; V.gidxB = s2->gidx;
         V.totalA = s1->total; V.totalB = s2->total; V.nA = s1->n_seq; V.nB = s2->n_seq;
         V.log_cut = evalue > 0 ? log(evalue) : -INFINITY;
+        V.top_n = top_n;
         int64_t hcap = 1024;
         while (hcap < 4 * n_gapped) hcap <<= 1;
         V.hmask = (uint32_t)(hcap - 1);
@@ -295,6 +302,16 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
         int g = grid_for(n_gapped, 256);
         stage_tic(ctx, 5);
         LAUNCH(ctx, k_sel_best, g, 256, 0, V);
+        if (top_n > 1) {
+            // n-largest per query gene (find_homologs.py:135-164 with n > 1): rows sorted by (gene, score desc),
+            // the n-th row of every gene is its threshold.  rkeys/rdesc are free until k_sel_emit.
+            for (int backward = 0; backward < 2; backward++) {
+                uint64_t* tk = rkeys; uint32_t* tv = rdesc;
+                LAUNCH(ctx, k_sel_topn_keys, g, 256, 0, V, backward, tk, tv);
+                RC(sort_pairs_u64_u32(ctx, &tk, &tv, n_gapped, 64));
+                LAUNCH(ctx, k_sel_topn_thr, g, 256, 0, tk, n_gapped, top_n, backward ? V.bestB : V.bestF);
+            }
+        }
         LAUNCH(ctx, k_sel_pairs, g, 256, 0, V);
         LAUNCH(ctx, k_sel_pairbest, g, 256, 0, V);
         LAUNCH(ctx, k_sel_genebest, g, 256, 0, V);
@@ -321,6 +338,8 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
     CU(cudaStreamSynchronize(ctx->stream));
     stage_collect(ctx);
     if (stats) *stats = st;
+    guard.t = nullptr;
+    *out = T;
     return 0;
 }
 

@@ -4,9 +4,12 @@
 // Input: the symmetric gapped-HSP list G of one sample pair (A = sample 1 = transcripts1 =
 // "ssample" side, B = sample 2 = "qsample" side).  forward search: query B, subject A;
 // backward search: query A, subject B.  After the backward frame's q/s rename every row has
-// qgene in B and sgene in A.  top_n == 1 (the reference default, rna_clique.py:37):
-//   F  = forward rows whose score equals the best of their query gene (ties kept)
-//   Bk = backward rows whose score equals the best of THEIR query gene (a gene of A)
+// qgene in B and sgene in A.
+//   F  = forward rows holding the top_n largest scores of their query gene, every row tied with the
+//        n-th kept (pandas nlargest(n, keep="all"), find_homologs.py:135-164); top_n = 1 (the reference
+//        default, rna_clique.py:37) is a per-gene atomicMax, top_n > 1 a sort by (gene, score desc) whose
+//        n-th row of every gene gives that gene's threshold
+//   Bk = the same for the backward rows, grouped by THEIR query gene (a gene of A)
 //   keep rows whose (qgene, sgene) pair occurs in both; then per pair the best score (ties kept),
 //   then per qgene the best score (keep_all) or the first such row (keep="first").
 // An HSP that qualifies in both directions yields two rows (reverse = 0 and 1) — the duplicate
@@ -69,8 +72,9 @@ struct SelView {
     const int32_t *lenA, *lenB, *gidxA, *gidxB;
     int64_t totalA, totalB; int32_t nA, nB;
     double log_cut;
+    int32_t top_n;
     uint8_t* pass;       // bit0 forward passes e-value, bit1 backward
-    int32_t *bestF, *bestB, *bestQ;   // per gene of B / A / B
+    int32_t *bestF, *bestB, *bestQ;   // per gene of B / A / B; bestF/bestB = lowest score still inside the gene's top_n
     uint64_t* hkeys; uint32_t* hflags; int32_t* hbest; uint32_t hmask;  // (qgene,sgene) pair set
     unsigned long long* firstkey;     // per gene of B (keep="first")
 };
@@ -97,16 +101,43 @@ __global__ void k_sel_best(SelView V) {
     int32_t raw = g.score2 >> 1;
     int32_t la = V.lenA[g.ta], lb = V.lenB[g.tb];
     uint8_t p = 0;
-    if (log_evalue(raw, lb, V.totalA, V.nA) <= V.log_cut) { p |= 1; atomicMax(&V.bestF[V.gidxB[g.tb]], raw); }
-    if (log_evalue(raw, la, V.totalB, V.nB) <= V.log_cut) { p |= 2; atomicMax(&V.bestB[V.gidxA[g.ta]], raw); }
+    if (log_evalue(raw, lb, V.totalA, V.nA) <= V.log_cut) { p |= 1; if (V.top_n == 1) atomicMax(&V.bestF[V.gidxB[g.tb]], raw); }
+    if (log_evalue(raw, la, V.totalB, V.nB) <= V.log_cut) { p |= 2; if (V.top_n == 1) atomicMax(&V.bestB[V.gidxA[g.ta]], raw); }
     V.pass[x] = p;
+}
+// top_n > 1: sort keys (query gene, score descending) of one direction's rows; rows that failed the e-value
+// cut sort behind every gene
+__global__ void k_sel_topn_keys(SelView V, int backward, uint64_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+    int64_t x = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= V.n) return;
+    const Gapped g = V.G[x];
+    const uint32_t gene = backward ? (uint32_t)V.gidxA[g.ta] : (uint32_t)V.gidxB[g.tb];
+    const bool in = V.pass[x] & (backward ? 2 : 1);
+    keys[x] = in ? (((uint64_t)gene << 32) | (uint32_t)(0x7fffffff - (g.score2 >> 1))) : EMPTY64;
+    vals[x] = (uint32_t)x;
+}
+// threshold of every gene = score of its top_n-th row (or of its last row when it has fewer)
+__global__ void k_sel_topn_thr(const uint64_t* __restrict__ keys, int64_t n, int32_t top_n, int32_t* __restrict__ thr) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint64_t k = keys[i];
+    if (k == EMPTY64) return;
+    const uint64_t first = k & 0xFFFFFFFF00000000ull;
+    int64_t lo = 0, hi = i;                       // first row of this gene
+    while (lo < hi) {
+        const int64_t mid = (lo + hi) >> 1;
+        if (keys[mid] < first) lo = mid + 1; else hi = mid;
+    }
+    const int64_t rank = i - lo;
+    const bool last = i + 1 == n || (keys[i + 1] >> 32) != (k >> 32);
+    if (rank == top_n - 1 || (last && rank < top_n - 1)) thr[k >> 32] = 0x7fffffff - (int32_t)(uint32_t)k;
 }
 // membership of HSP x in F (bit0) / Bk (bit1)
 __device__ __forceinline__ uint32_t membership(const SelView& V, int64_t x, const Gapped& g, int32_t raw) {
     uint8_t p = V.pass[x];
     uint32_t mem = 0;
-    if ((p & 1) && raw == V.bestF[V.gidxB[g.tb]]) mem |= 1;
-    if ((p & 2) && raw == V.bestB[V.gidxA[g.ta]]) mem |= 2;
+    if ((p & 1) && raw >= V.bestF[V.gidxB[g.tb]]) mem |= 1;
+    if ((p & 2) && raw >= V.bestB[V.gidxA[g.ta]]) mem |= 2;
     return mem;
 }
 __device__ __forceinline__ uint64_t pair_key(const SelView& V, const Gapped& g) {

@@ -181,3 +181,56 @@ def test_shared_low_complexity_tails_fail_with_a_clear_message(ctx):
     with pytest.raises(RuntimeError, match="low-complexity"):
         _native.search_pair(ctx, a, b)
     a.close(); b.close()
+
+
+def _table_matrix(tab):
+    from rna_clique_b200 import _native
+    cols = tab.download()
+    return np.stack([cols[c] for c in _native.TABLE_COLS] + [cols["minus"].astype(np.int32), cols["reverse"].astype(np.int32)], axis=1)
+
+
+@pytest.mark.parametrize("top_n", [1, 2, 3])
+@pytest.mark.parametrize("keep_all", [True, False])
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_selection_on_isoforms_paralogs_and_sparse_ids(ctx, seed, keep_all, top_n):
+    """The table assembly where it has decisions to take (helpers.make_family_samples): several isoforms per
+    gene, paralog families with exact copies (equal scores across subject genes), copies present in one
+    sample only (non-reciprocal best hits), chimeras, sparse sample-specific gene ids — for keep="all" and
+    keep="first" (k_sel_first) and for top_n 1, 2, 3 (k_sel_topn_*), every table equal to the oracle's, whose
+    assembly is pinned to the reference's HomologFinder.get_match_table (tests/golden/match_table_*.json)."""
+    from helpers import make_family_samples
+    from rna_clique_b200 import _native
+    from oracle import oracle as O
+    raw = make_family_samples(seed=seed)
+    g = _gpu_samples(ctx, raw)
+    o = _oracle_samples(raw)
+    tab = _native.search_pair(ctx, g[0], g[1], top_n=top_n, keep_all=keep_all)
+    res = O.search_pair(o[0], o[1], top_n=top_n, keep_all=keep_all)
+    assert np.array_equal(_native.debug_last_hsps(ctx), res.hsps())
+    got, want = _table_matrix(tab), res.rows(2)
+    assert np.array_equal(got, want)
+    assert tab.stats["n_fwd"] == res.counts["fwd"] and tab.stats["n_bwd"] == res.counts["bwd"]
+    # the inputs do what they were built for
+    q, s = want[:, 10], want[:, 12]
+    assert len(want) > 40 and (q != s).all()                         # ids differ between the samples
+    pairs = np.unique(np.stack([q, s], axis=1), axis=0)
+    if keep_all:
+        assert len(np.unique(pairs[:, 0])) < len(pairs)              # a query gene with several subject genes
+    else:
+        assert len(np.unique(q)) == len(want)                        # keep="first": one row per query gene
+    assert len(np.unique(want[:, 11])) > 1                           # several isoform numbers in the rows
+    if top_n > 1:
+        assert res.counts["fwd"] > O.search_pair(o[0], o[1]).counts["fwd"]
+
+
+def test_selection_role_swap_on_family_data(ctx):
+    """Swapping the two samples swaps q and s of every reciprocal pair: the (gene, gene) edge set is the same."""
+    from helpers import make_family_samples
+    from rna_clique_b200 import _native
+    raw = make_family_samples(seed=5, genes=40)
+    g = _gpu_samples(ctx, raw)
+    a = _table_matrix(_native.search_pair(ctx, g[0], g[1]))
+    b = _table_matrix(_native.search_pair(ctx, g[1], g[0]))
+    ea = {(int(r[12]), int(r[10])) for r in a}      # (gene of sample 0, gene of sample 1)
+    eb = {(int(r[10]), int(r[12])) for r in b}
+    assert len(ea) > 20 and len(ea ^ eb) <= max(1, len(ea) // 50)
