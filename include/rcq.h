@@ -99,6 +99,17 @@ int rcq_sample_info(const rcq_sample* s, int64_t info[5]);
 int rcq_sample_download(const rcq_sample* s, uint32_t* fwd, uint32_t* rc, uint32_t* mask,
                         int64_t* arena_off, uint64_t* index);
 
+/* Low-complexity filter.  blastn soft-masks every query with symmetric DUST (default "-dust 20 64 1") before
+ * the search the reference starts at find_homologs.py:124: masked stretches (poly-A tails, microsatellites)
+ * take no part in seeding, extensions run through them.  rcq_sample_create computes the same mask on the
+ * device (csrc/dust_kernels.cuh) into the sample's seeding mask; one search serves both blastn directions, so
+ * a seed needs a 28-base window clean in BOTH samples.  rcq_ctx_set_dust(ctx, 0) switches the filter off for
+ * samples created afterwards on ctx (blastn -dust no); returns the previous setting.
+ * rcq_sample_seed_mask (test hook): the seeding mask = not-ACGT | DUST | padding, arena_bases/32 uint32, and
+ * the number of bases only DUST masks.  Either pointer may be NULL. */
+int rcq_ctx_set_dust(rcq_ctx* ctx, int on);
+int rcq_sample_seed_mask(const rcq_sample* s, uint32_t* smask, int64_t* n_dust);
+
 /* ---- kernel (3) + table assembly.  One UNORDERED sample pair: both blastn directions
  * (find_homologs.py:82-133 gene_matches, :124 TabularBlastnSearch), the per-query-gene
  * best-bitscore reduction (:135-164) and HomologFinder.get_match_table (:215-302).
@@ -116,6 +127,11 @@ typedef struct {
     int64_t n_verified;     /* key matches that survived the flank filter and were verified on the sequences */
 } rcq_search_stats;
 
+/* top_n >= 1: rows per query gene kept in each direction before the reciprocal filter (the reference's
+ * top_matches, rna_clique.py:37; nlargest(n, keep="all"), find_homologs.py:135-164).  keep_all = 0 keeps the
+ * first best row per query gene only (keep="first").  On error *out is NULL and nothing is left allocated.
+ * Limits (RCQ_ERR_CAPACITY, with a message): < 2^20 genes and < 2^21 transcripts per sample, a sample's
+ * arena < 2^31 bases, < 2^31 seed candidates and < 2^22 gapped HSPs per pair. */
 int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sample* s2, double evalue,
                     int32_t top_n, int32_t keep_all, rcq_table** out, rcq_search_stats* stats);
 

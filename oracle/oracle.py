@@ -35,6 +35,8 @@ def lib():
         L.orc_sample_new.restype = C.c_void_p
         L.orc_sample_new.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32]
         L.orc_sample_free.argtypes = [C.c_void_p]
+        L.orc_sample_dust.argtypes = [C.c_void_p, C.c_void_p]
+        L.orc_set_dust.argtypes = [C.c_int]
         L.orc_search_pair.restype = C.c_void_p
         L.orc_search_pair.argtypes = [C.c_void_p, C.c_void_p, C.c_double, C.c_int, C.c_int]
         L.orc_search_pair_directions.restype = C.c_void_p
@@ -65,6 +67,12 @@ class Sample:
         self.iso = np.ascontiguousarray(iso, dtype=np.int32)
         self.h = lib().orc_sample_new(self.ascii.ctypes.data, self.offsets.ctypes.data,
                                       self.gene.ctypes.data, self.iso.ctypes.data, len(self.gene))
+
+    def dust(self) -> np.ndarray:
+        """Symmetric-DUST mask (level 20, window 64), one byte per base of the concatenated transcripts."""
+        out = np.zeros(int(self.offsets[-1] - self.offsets[0]) if len(self.offsets) else 0, dtype=np.uint8)
+        lib().orc_sample_dust(self.h, out.ctypes.data)
+        return out
 
     def __del__(self):
         if getattr(self, "h", None) and _lib is not None:
@@ -113,6 +121,11 @@ def match_table_from_rows(fwd: np.ndarray, bwd: np.ndarray, top_n: int = 1, keep
     lib().orc_result_counts(r.h, c.ctypes.data)
     r.counts = dict(zip(["gapped", "fwd", "bwd", "rows", "seeds", "ungapped", "dp_cells"], c.tolist()))
     return r
+
+
+def set_dust(on: bool) -> None:
+    """DUST soft-masking of seeds for samples created AFTER the call (default on, as in blastn)."""
+    lib().orc_set_dust(int(bool(on)))
 
 
 def set_gapped_mode(greedy: bool) -> None:

@@ -45,7 +45,56 @@ typedef struct {
     uint8_t* fwd;     /* 0..3 = ACGT, 4 = anything else */
     uint8_t* rc;      /* per-transcript reverse complement, same offsets */
     int32_t *gene, *iso;
+    uint8_t* dust;    /* 1 = base inside a symmetric-DUST perfect interval (seeding only), fwd coordinates */
+    uint8_t* dust_rc; /* the same mask in reverse-complement coordinates */
 } orc_sample;
+
+/* ---------- symmetric DUST (Morgulis, Gertz, Schaffer, Agarwala 2006), blastn's default query filter
+ * "-dust 20 64 1": level 20 (score threshold 2.0), window 64, linker 1.  Stated by its definition, not by the
+ * streaming algorithm: over the triplets t_0 .. t_{m-1} of a maximal run of ACGT bases, an interval of
+ * l >= 2 consecutive triplets has score r / (l - 1), r = sum over triplet values of c (c - 1) / 2; it is
+ * PERFECT when it spans at most 62 triplets (64 bases), its score exceeds 2 and no interval inside it has a
+ * higher score.  The mask is the union of the bases of all perfect intervals; linker 1 only joins masked
+ * ranges that already touch, so it does not change the mask.  Soft masking: the mask keeps seeds out
+ * (find_ungapped), extensions never look at it.  Pure function of the sequence, symmetric under reverse
+ * complement.  Cost: a 62-step suffix scan per position; the full triangle only where a suffix scores > 2. */
+#define DUST_MAXT 62
+static int g_dust_on = 1;
+void orc_set_dust(int on) { g_dust_on = on; }
+static void dust_mask(const uint8_t* s, int32_t n, uint8_t* out) {
+    memset(out, 0, n > 0 ? n : 0);
+    if (!g_dust_on || n < 3) return;
+    int32_t m = n - 2;
+    int16_t* trip = malloc(sizeof(int16_t) * m);
+    for (int32_t i = 0; i < m; i++)
+        trip[i] = (s[i] > 3 || s[i + 1] > 3 || s[i + 2] > 3) ? -1 : (int16_t)(s[i] << 4 | s[i + 1] << 2 | s[i + 2]);
+    uint8_t c[64];
+    for (int32_t e = 1; e < m; e++) {
+        if (trip[e] < 0) continue;
+        /* suffixes [i, e]: does any score more than 2? */
+        memset(c, 0, 64);
+        int32_t r = 0, lo = -1;
+        for (int32_t i = e; i >= 0 && e - i < DUST_MAXT && trip[i] >= 0; i--) {
+            r += c[trip[i]]++;
+            if (r > 2 * (e - i)) lo = i;       /* l - 1 = e - i */
+        }
+        if (lo < 0) continue;
+        /* rows i = e-1 .. lo: best score of any interval inside [i, e] (bests_r / bests_l), and whether the
+         * suffix [i, e] itself reaches it */
+        int32_t best_r = 0, best_l = 1;
+        for (int32_t i = e - 1; i >= lo; i--) {
+            memset(c, 0, 64);
+            r = 0;
+            for (int32_t j = i; j <= e; j++) {
+                r += c[trip[j]]++;
+                if (j > i && r * best_l > best_r * (j - i)) { best_r = r; best_l = j - i; }
+            }
+            if (r > 2 * (e - i) && r * best_l >= best_r * (e - i))
+                for (int32_t b = i; b <= e + 2; b++) out[b] = 1;
+        }
+    }
+    free(trip);
+}
 
 static uint8_t code_of(uint8_t c) {
     c &= 0xDF;
@@ -64,6 +113,8 @@ orc_sample* orc_sample_new(const uint8_t* ascii, const int64_t* offsets, const i
     s->total = s->off[n_seq];
     s->fwd = malloc(s->total + 1);
     s->rc = malloc(s->total + 1);
+    s->dust = malloc(s->total + 1);
+    s->dust_rc = malloc(s->total + 1);
     for (int t = 0; t < n_seq; t++) {
         s->gene[t] = gene[t];
         s->iso[t] = iso[t];
@@ -73,12 +124,16 @@ orc_sample* orc_sample_new(const uint8_t* ascii, const int64_t* offsets, const i
             uint8_t c = s->fwd[o + n - 1 - i];
             s->rc[o + i] = c > 3 ? 4 : (uint8_t)(3 - c);
         }
+        dust_mask(s->fwd + o, (int32_t)n, s->dust + o);
+        for (int64_t i = 0; i < n; i++) s->dust_rc[o + i] = s->dust[o + n - 1 - i];
     }
     return s;
 }
+/* test hook: the DUST mask of the whole sample, one byte per base (fwd coordinates) */
+void orc_sample_dust(const orc_sample* s, uint8_t* out) { memcpy(out, s->dust, s->total); }
 void orc_sample_free(orc_sample* s) {
     if (!s) return;
-    free(s->off); free(s->fwd); free(s->rc); free(s->gene); free(s->iso); free(s);
+    free(s->off); free(s->fwd); free(s->rc); free(s->gene); free(s->iso); free(s->dust); free(s->dust_rc); free(s);
 }
 
 static inline int is_match(uint8_t a, uint8_t b) { return a == b && a < 4; }
@@ -391,12 +446,12 @@ static int cmp_ungapped_order(const void* x, const void* y) {
     return 0;
 }
 
-/* rolling 28-mer keys of one sequence; valid[i] = window [i, i+28) has no masked base */
-static void kmer_keys(const uint8_t* s, int32_t n, uint64_t* key, uint8_t* valid) {
+/* rolling 28-mer keys of one sequence; valid[i] = window [i, i+28) has no N and no DUST-masked base */
+static void kmer_keys(const uint8_t* s, const uint8_t* dust, int32_t n, uint64_t* key, uint8_t* valid) {
     uint64_t k = 0; int32_t good = 0;
     const uint64_t maskk = (1ull << (2 * WORD)) - 1;
     for (int32_t i = 0; i < n; i++) {
-        if (s[i] > 3) { good = 0; k = 0; } else { good++; k = ((k << 2) | s[i]) & maskk; }
+        if (s[i] > 3) { good = 0; k = 0; } else { good = dust[i] ? 0 : good + 1; k = ((k << 2) | s[i]) & maskk; }
         if (i >= WORD - 1) { key[i - WORD + 1] = k; valid[i - WORD + 1] = good >= WORD; }
     }
 }
@@ -408,7 +463,9 @@ static void upush(uvec_t* u, ungapped_t x) {
 }
 
 static int64_t g_seeds = 0;
-/* All maximal exact runs >= WORD between transcripts of s1 (plus) and s2 (both strands),
+/* Seeds: all maximal exact runs >= WORD between transcripts of s1 (plus) and s2 (both strands) that hold
+ * at least one window of WORD bases free of DUST-masked bases in BOTH samples (blastn masks the query of
+ * each direction; one search serves both directions here, so both masks apply).  Each seed is then
  * extended without gaps under BLAST's diagonal rule (below); duplicates removed. */
 static uvec_t find_ungapped(const orc_sample* s1, const orc_sample* s2) {
     int64_t cap = 2 * s2->total + 1, nk = 0;
@@ -423,19 +480,22 @@ static uvec_t find_ungapped(const orc_sample* s1, const orc_sample* s2) {
         for (int minus = 0; minus < 2; minus++) {
             const uint8_t* b = (minus ? s2->rc : s2->fwd) + s2->off[t];
             if (n < WORD) continue;
-            kmer_keys(b, n, key, valid);
+            kmer_keys(b, (minus ? s2->dust_rc : s2->dust) + s2->off[t], n, key, valid);
             for (int32_t j = 0; j + WORD <= n; j++)
                 if (valid[j]) { idx[nk].key = key[j]; idx[nk].tb = t; idx[nk].pos = j; idx[nk].minus = minus; nk++; }
         }
     }
     qsort(idx, nk, sizeof(kent_t), cmp_kent);
-    /* pass 1: every seed = maximal exact run >= WORD, as (ta, tb, minus, diag, [rs, re)) */
+    /* pass 1: every seed = maximal exact run holding a clean window, as (ta, tb, minus, diag, [rs, re)):
+     * each stretch of consecutive clean matching windows reports its run once; a run with several
+     * stretches is reported several times and collapses in the sort below */
     uvec_t seeds = {0, 0, 0};
     for (int ta = 0; ta < s1->n_seq; ta++) {
         const uint8_t* a = s1->fwd + s1->off[ta];
+        const uint8_t* da = s1->dust + s1->off[ta];
         int32_t la = (int32_t)(s1->off[ta + 1] - s1->off[ta]);
         if (la < WORD) continue;
-        kmer_keys(a, la, key, valid);
+        kmer_keys(a, da, la, key, valid);
         for (int32_t i = 0; i + WORD <= la; i++) {
             if (!valid[i]) continue;
             int64_t lo = 0, hi = nk;
@@ -443,13 +503,15 @@ static uvec_t find_ungapped(const orc_sample* s1, const orc_sample* s2) {
             for (int64_t e = lo; e < nk && idx[e].key == key[i]; e++) {
                 int32_t tb = idx[e].tb, j = idx[e].pos, minus = idx[e].minus;
                 const uint8_t* b = (minus ? s2->rc : s2->fwd) + s2->off[tb];
+                const uint8_t* db = (minus ? s2->dust_rc : s2->dust) + s2->off[tb];
                 int32_t lb = (int32_t)(s2->off[tb + 1] - s2->off[tb]);
-                if (i > 0 && j > 0 && is_match(a[i - 1], b[j - 1])) continue; /* not a run start */
-                int32_t re = i + WORD;
+                /* the window one base to the left also matches and is clean: not the first of its stretch */
+                if (i > 0 && j > 0 && is_match(a[i - 1], b[j - 1]) && !da[i - 1] && !db[j - 1]) continue;
+                int32_t rs = i, re = i + WORD;
+                while (rs > 0 && rs + (j - i) > 0 && is_match(a[rs - 1], b[rs - 1 + (j - i)])) rs--;
                 while (re < la && re + (j - i) < lb && is_match(a[re], b[re + (j - i)])) re++;
-                g_seeds++;
                 ungapped_t u;
-                u.ta = ta; u.tb = tb; u.minus = minus; u.diag = j - i; u.a0 = i; u.a1 = re; u.score = 0;
+                u.ta = ta; u.tb = tb; u.minus = minus; u.diag = j - i; u.a0 = rs; u.a1 = re; u.score = 0;
                 upush(&seeds, u);
             }
         }
@@ -458,7 +520,14 @@ static uvec_t find_ungapped(const orc_sample* s1, const orc_sample* s2) {
     /* pass 2 (BLAST's diagonal rule): along each diagonal, seeds in ascending position; a seed that
      * starts inside the ungapped HSP extended from an earlier seed of the diagonal is skipped */
     uvec_t out = {0, 0, 0};
-    if (seeds.n) qsort(seeds.v, seeds.n, sizeof(ungapped_t), cmp_ungapped_id);
+    if (seeds.n) {
+        qsort(seeds.v, seeds.n, sizeof(ungapped_t), cmp_ungapped_id);
+        int64_t w = 1;
+        for (int64_t r = 1; r < seeds.n; r++)
+            if (cmp_ungapped_id(&seeds.v[r], &seeds.v[w - 1]) != 0) seeds.v[w++] = seeds.v[r];
+        seeds.n = w;
+    }
+    g_seeds += seeds.n;
     int32_t last_end = -1;
     for (int64_t r = 0; r < seeds.n; r++) {
         const ungapped_t* sd = &seeds.v[r];

@@ -20,6 +20,7 @@ HSP_COLS = ["tx1", "tx2", "minus", "a0", "a1", "b0", "b1", "score2", "mismatch",
 SYMBOLS = [
     "rcq_last_error", "rcq_version", "rcq_ctx_create", "rcq_ctx_destroy", "rcq_ctx_sync", "rcq_ctx_stream",
     "rcq_ctx_launches", "rcq_ctx_stage_times", "rcq_top_gene_mask", "rcq_fasta_scan", "rcq_fasta_parse", "rcq_parse_spades_ids", "rcq_fasta_format", "rcq_graph_pickle", "rcq_sample_create", "rcq_sample_free", "rcq_sample_info", "rcq_sample_download",
+    "rcq_ctx_set_dust", "rcq_sample_seed_mask",
     "rcq_search_pair", "rcq_table_rows", "rcq_table_download", "rcq_table_free", "rcq_debug_last_hsps", "rcq_debug_keep_hsps",
     "rcq_length_adjustment", "rcq_evalue", "rcq_bitscore", "rcq_phase2_host", "rcq_phase2_tables",
     "rcq_table_flat_words", "rcq_table_flatten", "rcq_table_from_flat", "rcq_sample_meta", "rcq_sample_export", "rcq_sample_import",
@@ -74,6 +75,8 @@ def lib():
         L.rcq_sample_free.restype = None
         L.rcq_sample_info.argtypes = [vp, vp]
         L.rcq_sample_download.argtypes = [vp, vp, vp, vp, vp, vp]
+        L.rcq_ctx_set_dust.argtypes = [vp, C.c_int]
+        L.rcq_sample_seed_mask.argtypes = [vp, vp, vp]
         L.rcq_search_pair.argtypes = [vp, vp, vp, dbl, i32, i32, C.POINTER(vp), C.POINTER(SearchStats)]
         L.rcq_table_rows.argtypes = [vp]
         L.rcq_table_rows.restype = i64
@@ -152,6 +155,11 @@ class Context:
         check(lib().rcq_ctx_stage_times(self.h, ms.ctypes.data, calls.ctypes.data, int(reset)))
         return {n: dict(ms=float(ms[i]), calls=int(calls[i])) for i, n in enumerate(self.STAGES)}
 
+    def set_dust(self, on: bool) -> bool:
+        """DUST soft-masking of seeds for samples created on this context from now on (default on, as in
+        blastn); returns the previous setting."""
+        return bool(lib().rcq_ctx_set_dust(self.h, int(bool(on))))
+
     def close(self):
         if self.h:
             lib().rcq_ctx_destroy(self.h)
@@ -224,6 +232,13 @@ class Sample:
         s.ctx, s.name, s.h, s._keep = ctx, name, h, None
         s.n_seq, s.total, s.arena, s.n_index, s.n_masked = (int(x) for x in meta[:5])
         return s
+
+    def seed_mask(self):
+        """(seeding mask words uint32[arena/32], bases masked by DUST alone)."""
+        m = np.zeros(self.arena // 32, dtype=np.uint32)
+        nd = np.zeros(1, dtype=np.int64)
+        check(lib().rcq_sample_seed_mask(self.h, m.ctypes.data, nd.ctypes.data))
+        return m, int(nd[0])
 
     def download(self):
         fwd = np.zeros(self.arena // 16, dtype=np.uint32)

@@ -206,7 +206,7 @@ void rcq_sample_free(rcq_sample* s) {
     dfree(c, s->fwd); dfree(c, s->rc); dfree(c, s->mask); dfree(c, s->mask_rc);
     dfree(c, s->off); dfree(c, s->len); dfree(c, s->gene); dfree(c, s->iso);
     dfree(c, s->index); dfree(c, s->fctx); dfree(c, s->dir); dfree(c, s->sel); dfree(c, s->gidx);
-    dfree(c, s->blk2tx); dfree(c, s->ol);
+    dfree(c, s->blk2tx); dfree(c, s->ol); dfree(c, s->smask); dfree(c, s->smask_rc);
     delete s;
 }
 
@@ -225,6 +225,7 @@ static int flat_parts(rcq_sample* s, FlatPart* out) {
     out[k++] = {(void**)&s->fwd, w}; out[k++] = {(void**)&s->rc, w};
     out[k++] = {(void**)&s->mask, m}; out[k++] = {(void**)&s->mask_rc, m};
     out[k++] = {(void**)&s->sel, m}; out[k++] = {(void**)&s->blk2tx, m};
+    out[k++] = {(void**)&s->smask, m}; out[k++] = {(void**)&s->smask_rc, m};
     out[k++] = {(void**)&s->off, n}; out[k++] = {(void**)&s->len, n}; out[k++] = {(void**)&s->gene, n};
     out[k++] = {(void**)&s->iso, n}; out[k++] = {(void**)&s->gidx, n}; out[k++] = {(void**)&s->ol, 2 * n};
     out[k++] = {(void**)&s->index, s->n_index * 8}; out[k++] = {(void**)&s->fctx, s->n_index * 8};
@@ -237,7 +238,7 @@ int rcq_sample_meta(const rcq_sample* s, int64_t meta[8]) {
     if (!s || !meta) return rcq_fail(RCQ_ERR_ARG, "rcq_sample_meta: bad argument");
     meta[0] = s->n_seq; meta[1] = s->total; meta[2] = s->arena; meta[3] = s->n_index; meta[4] = s->n_masked;
     meta[5] = s->max_len; meta[6] = s->n_genes;
-    FlatPart parts[16];
+    FlatPart parts[24];
     const int k = flat_parts(const_cast<rcq_sample*>(s), parts);
     int64_t tot = 0;
     for (int i = 0; i < k; i++) tot += pad256(parts[i].bytes);
@@ -248,7 +249,7 @@ int rcq_sample_meta(const rcq_sample* s, int64_t meta[8]) {
 int rcq_sample_export(rcq_ctx* ctx, const rcq_sample* s, uint8_t* dev_flat) {
     if (!ctx || !s || !dev_flat) return rcq_fail(RCQ_ERR_ARG, "rcq_sample_export: bad argument");
     CU(cudaSetDevice(ctx->device));
-    FlatPart parts[16];
+    FlatPart parts[24];
     const int k = flat_parts(const_cast<rcq_sample*>(s), parts);
     int64_t at = 0;
     for (int i = 0; i < k; i++) {
@@ -266,7 +267,7 @@ int rcq_sample_import(rcq_ctx* ctx, const int64_t meta[8], const uint8_t* dev_fl
     s->ctx = ctx;
     s->n_seq = (int32_t)meta[0]; s->total = meta[1]; s->arena = meta[2]; s->n_index = meta[3]; s->n_masked = meta[4];
     s->max_len = (int32_t)meta[5]; s->n_genes = (int32_t)meta[6];
-    FlatPart parts[16];
+    FlatPart parts[24];
     const int k = flat_parts(s, parts);
     int64_t at = 0;
     for (int i = 0; i < k; i++) {
@@ -280,6 +281,23 @@ int rcq_sample_import(rcq_ctx* ctx, const int64_t meta[8], const uint8_t* dev_fl
     if (at != meta[7]) { rcq_sample_free(s); return rcq_fail(RCQ_ERR_ARG, "rcq_sample_import: meta does not match the flat size"); }
     CU(cudaStreamSynchronize(ctx->stream));
     *out = s;
+    return 0;
+}
+
+int rcq_ctx_set_dust(rcq_ctx* ctx, int on) {
+    if (!ctx) return 0;
+    const int before = ctx->dust_on;
+    ctx->dust_on = on ? 1 : 0;
+    return before;
+}
+
+int rcq_sample_seed_mask(const rcq_sample* s, uint32_t* smask, int64_t* n_dust) {
+    if (!s) return rcq_fail(RCQ_ERR_ARG, "rcq_sample_seed_mask: bad argument");
+    rcq_ctx* c = s->ctx;
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    if (smask) CU(cudaMemcpy(smask, s->smask, s->arena / 32 * 4, cudaMemcpyDeviceToHost));
+    if (n_dust) *n_dust = s->n_dust;
     return 0;
 }
 

@@ -5,6 +5,7 @@
 //   index  : 0.25 B/nt read, 8 B per selected minimizer written, then an 8-B-key radix sort.
 #include <cub/cub.cuh>
 #include "sample.cuh"
+#include "dust_kernels.cuh"
 
 #define GUARD_FRONT 64
 #define GUARD_BACK 128
@@ -419,8 +420,12 @@ int rcq_sample_build(rcq_ctx* ctx, rcq_sample* s, const uint8_t* d_ascii, int64_
     RC(dalloc(ctx, &s->ol, s->n_seq));
     CU(cudaMemsetAsync(s->blk2tx, 0, mwords * 4, ctx->stream));
     CU(cudaMemsetAsync(s->sel, 0, mwords * 4, ctx->stream));
+    RC(dalloc(ctx, &s->smask, mwords));
+    RC(dalloc(ctx, &s->smask_rc, mwords));
+    CU(cudaMemsetAsync(s->smask, 0, mwords * 4, ctx->stream));
+    CU(cudaMemsetAsync(s->smask_rc, 0xFF, mwords * 4, ctx->stream));
     unsigned long long* ctr = (unsigned long long*)ctx->d_ctr;
-    CU(cudaMemsetAsync(ctr, 0, 2 * sizeof(unsigned long long), ctx->stream));
+    CU(cudaMemsetAsync(ctr, 0, 8 * sizeof(unsigned long long), ctx->stream));
     int blocks = RCQ_SMS * 8;
     if (s->n_seq) {
         LAUNCH(ctx, k_pack, blocks, 256, 0, d_ascii, ascii_len, d_starts, s->off, s->len, s->n_seq, s->fwd,
@@ -428,6 +433,19 @@ int rcq_sample_build(rcq_ctx* ctx, rcq_sample* s, const uint8_t* d_ascii, int64_
         LAUNCH(ctx, k_tx_tables, blocks, 256, 0, s->off, s->len, s->n_seq, s->blk2tx, s->ol);
         LAUNCH(ctx, k_revcomp, blocks, 256, 0, s->fwd, s->mask, s->off, s->len, s->n_seq, s->rc,
                s->mask_rc);
+        // seeding mask: N mask | symmetric DUST (what blastn's default query filter hides from seeding)
+        if (ctx->dust_on) {
+            uint8_t* trip = nullptr; uint32_t* flag = nullptr;
+            RC(talloc(ctx, &trip, s->arena));
+            RC(talloc(ctx, &flag, mwords));
+            LAUNCH(ctx, k_dust_triplets, grid_for(words, 256), 256, 0, s->fwd, s->mask, s->arena, trip);
+            LAUNCH(ctx, k_dust_flag, grid_for((s->arena + DUST_SEG - 1) / DUST_SEG, DUST_FLAG_THREADS), DUST_FLAG_THREADS, 0,
+                   trip, s->arena, flag);
+            LAUNCH(ctx, k_dust_eval, RCQ_SMS * 8, DUST_EVAL_THREADS, 0, trip, flag, s->arena, s->smask, ctr);
+            tfree(ctx, trip); tfree(ctx, flag);
+        }
+        LAUNCH(ctx, k_dust_or, grid_for(mwords, 256), 256, 0, s->mask, s->smask, mwords, ctr);
+        LAUNCH(ctx, k_revmask, blocks, 256, 0, s->smask, s->off, s->len, s->n_seq, s->smask_rc);
     }
     // minimizer entries: one pass into a buffer sized for the usual density (2/14 per base);
     // a denser sample is re-run once with the exact count
@@ -437,11 +455,12 @@ int rcq_sample_build(rcq_ctx* ctx, rcq_sample* s, const uint8_t* d_ascii, int64_
         RC(dalloc(ctx, &s->fctx, cap));
         CU(cudaMemsetAsync(ctr + 1, 0, sizeof(unsigned long long), ctx->stream));
         if (s->n_seq)
-            LAUNCH(ctx, k_minimizers, blocks, 32 * MZ_WARPS, 0, s->fwd, s->mask, s->off, s->len, s->n_seq, ctr + 1,
+            LAUNCH(ctx, k_minimizers, blocks, 32 * MZ_WARPS, 0, s->fwd, s->smask, s->off, s->len, s->n_seq, ctr + 1,
                    s->index, s->fctx, (unsigned long long)cap, s->sel);
-        RC(publish_counters(ctx, (const int64_t*)ctr, 2));
+        RC(publish_counters(ctx, (const int64_t*)ctr, 5));
         s->n_masked = ctx->h_pin[0];
         s->n_index = ctx->h_pin[1];
+        s->n_dust = ctx->h_pin[4];
         if (s->n_index <= cap) break;
         dfree(ctx, s->index); s->index = nullptr;
         dfree(ctx, s->fctx); s->fctx = nullptr;

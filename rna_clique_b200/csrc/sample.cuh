@@ -14,6 +14,9 @@
 //                   canonical strand (low / high word; bit 31 = unavailable, bit 30 low = palindrome)
 //   dir[2^DIRBITS+1] uint32 first index entry of each hash-prefix bucket
 //   sel[arena/32]   uint32  bitmap of indexed positions;  gidx[n_seq] dense gene index
+//   smask[arena/32], smask_rc[arena/32]  uint32  seeding mask = mask | symmetric-DUST low-complexity mask
+//                   (dust_kernels.cuh): 16-mers touching it are not indexed, seeds need a clean 28-base window;
+//                   extensions keep reading `mask` (soft masking)
 //   blk2tx[arena/32] int32  transcript owning each 32-base block (transcripts start on block
 //                   boundaries);  ol[n_seq] int2 {off, len} for one-load transcript bounds
 #pragma once
@@ -28,7 +31,9 @@ struct rcq_sample {
     int64_t arena = 0;      // padded arena length in bases (multiple of 64, + guard)
     int64_t n_index = 0;
     int64_t n_masked = 0;
+    int64_t n_dust = 0;     // bases masked by DUST and not by `mask`
     int32_t max_len = 0;
+    uint32_t *smask = nullptr, *smask_rc = nullptr;
     uint32_t *fwd = nullptr, *rc = nullptr, *mask = nullptr, *mask_rc = nullptr;
     int32_t *off = nullptr, *len = nullptr, *gene = nullptr, *iso = nullptr;
     uint64_t* index = nullptr;

@@ -83,6 +83,7 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
     P.offA = s1->off; P.lenA = s1->len; P.offB = s2->off; P.lenB = s2->len;
     P.nA = s1->n_seq; P.nB = s2->n_seq; P.selA = s1->sel; P.selB = s2->sel;
     P.blkA = s1->blk2tx; P.blkB = s2->blk2tx; P.olA = s1->ol; P.olB = s2->ol;
+    P.smA = s1->smask; P.smB = s2->smask; P.smBr = s2->smask_rc;
     unsigned long long* ctr = (unsigned long long*)ctx->d_ctr;
     // the table handle reaches the caller only on success: every error return below frees it
     struct TableGuard {

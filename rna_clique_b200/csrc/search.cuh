@@ -14,6 +14,7 @@ struct PairView {
     const uint32_t *selA, *selB;
     const int32_t *blkA, *blkB;   // 32-base block -> transcript
     const int2 *olA, *olB;        // {off, len} per transcript
+    const uint32_t *smA, *smB, *smBr;   // seeding masks (N | DUST): A forward, B forward, B reverse complement
 };
 
 struct rcq_table {

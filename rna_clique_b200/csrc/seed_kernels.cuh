@@ -169,6 +169,41 @@ __global__ void __launch_bounds__(PROBE_THREADS) k_seed_probe(
 // reaches 13 or more bases to the left of the anchor always holds an earlier joint position: such
 // candidates are rejected after one 32-base compare, the others check the two index bitmaps over
 // the (< 13) bases to the left.
+// selected-in-both bits of the positions [p0, p0 + 32) of A (bit i <-> p0 + i) on diagonal d
+__device__ __forceinline__ uint32_t joint_sel32(const PairView& P, int64_t ba, int64_t bb, int32_t lb, int32_t p0,
+                                                int32_t d, int minus) {
+    const uint32_t wa = fetchmask32(P.selA, ba + p0);
+    uint32_t wb;
+    if (!minus) wb = fetchmask32(P.selB, bb + p0 + d);
+    else wb = __brev(fetchmask32(P.selB, bb + lb - d - RCQ_KMER - p0 - 31));
+    return wa & wb;
+}
+// does [rs, re) hold RCQ_WORD consecutive positions with no seeding-mask bit in either sample?  (mB is the
+// seeding mask of B on the strand of the hit, indexed like the bases: position p of A <-> p + d of B)
+__device__ __forceinline__ bool clean_window(const uint32_t* __restrict__ mA, int64_t ba, const uint32_t* __restrict__ mB,
+                                             int64_t bb, int32_t d, int32_t rs, int32_t re) {
+    int32_t zr = 0;                       // clean positions ending at the current scan position
+    for (int32_t p = rs; p < re; p += 32) {
+        uint32_t w = fetchmask32(mA, ba + p) | fetchmask32(mB, bb + p + d);
+        const int32_t nb = re - p;
+        if (nb < 32) w |= ~0u << nb;
+        if (w == 0u) { zr += 32; if (zr >= RCQ_WORD) return true; continue; }
+        if (zr + (__ffs(w) - 1) >= RCQ_WORD) return true;
+        uint32_t y = ~w;                  // a run of 28 clean positions inside this word
+        y &= y >> 1; y &= y >> 2; y &= y >> 4; y &= y >> 8;
+        if (y & (y >> 12)) return true;
+        zr = __clz(w);
+    }
+    return false;
+}
+
+// A candidate becomes the seed of its exact run when it is the LEFTMOST position of the run indexed in both
+// samples ("joint anchor") and the run qualifies: >= 28 bases with a 28-base window clean in both seeding
+// masks.  Inside such a window all 13 16-mers are indexed candidates in both samples and share their minimum,
+// so every qualifying run has a joint anchor.  Is there a joint anchor further left?  When the run reaches
+// fewer than 13 bases to the left the two index bitmaps answer directly; when it reaches 13 or more and the
+// 28 bases [ia - 13, ia + 15) are clean in both samples that window's minimum is an earlier joint anchor (the
+// common case: one 32-base compare); only next to masked bases the bitmaps are scanned down the whole run.
 __device__ __forceinline__ bool verify_anchor(const PairView& P, int32_t pA, int32_t pB, int minus, Seed* out) {
     const int32_t ta = __ldg(P.blkA + (pA >> 5)), tb = __ldg(P.blkB + (pB >> 5));
     const int2 a = __ldg(P.olA + ta), b = __ldg(P.olB + tb);
@@ -176,29 +211,39 @@ __device__ __forceinline__ bool verify_anchor(const PairView& P, int32_t pA, int
     const int32_t ia = pA - oa, jf = pB - ob;
     const int32_t j = minus ? lb - jf - RCQ_KMER : jf;
     const SeqArena& B = minus ? P.Br : P.Bf;
+    const uint32_t* smB = minus ? P.smBr : P.smB;
     const int64_t ba = oa, bb = ob;
     if ((match32(P.Af, ba + ia, B, bb + j) & 0xFFFFu) != 0xFFFFu) return false;
-    // left: at most 13 bases matter
+    const int32_t d = j - ia;
     int32_t left = 0;
     const int32_t llim = min(ia, j);
     if (llim > 0) {
         uint32_t m = match32_back(P.Af, ba + ia - 1, B, bb + j - 1);
         left = (m == 0xFFFFFFFFu) ? 32 : (__ffs(~m) - 1);
         if (left > llim) left = llim;
-        if (left >= RCQ_WIN) return false;
-    }
-    const int32_t d = j - ia;
-    if (left > 0) {
-        const int32_t p0 = ia - left;      // bits for positions [p0, ia)
-        uint32_t wa = fetchmask32(P.selA, ba + p0), wb;
-        if (!minus) wb = fetchmask32(P.selB, bb + p0 + d);
-        else wb = __brev(fetchmask32(P.selB, bb + lb - d - RCQ_KMER - p0 - 31));
-        if (wa & wb & ((1u << left) - 1u)) return false;
+        if (left >= RCQ_WIN) {
+            const uint32_t W28 = (1u << RCQ_WORD) - 1u;
+            if (!((fetchmask32(P.smA, ba + ia - RCQ_WIN) | fetchmask32(smB, bb + j - RCQ_WIN)) & W28)) return false;
+            // masked bases nearby: walk the run to its start, looking for an earlier joint anchor
+            int32_t pos = ia, rem = llim;
+            left = 0;
+            while (rem > 0) {
+                m = match32_back(P.Af, ba + pos - 1, B, bb + pos + d - 1);
+                int32_t z = (m == 0xFFFFFFFFu) ? 32 : (__ffs(~m) - 1);
+                if (z > rem) z = rem;
+                if (z > 0 && (joint_sel32(P, ba, bb, lb, pos - z, d, minus) & (z == 32 ? 0xFFFFFFFFu : ((1u << z) - 1u)))) return false;
+                left += z; pos -= z; rem -= z;
+                if (z < 32) break;
+            }
+        } else if (left > 0) {
+            if (joint_sel32(P, ba, bb, lb, ia - left, d, minus) & ((1u << left) - 1u)) return false;
+        }
     }
     const int32_t right = run_fwd(P.Af, ba + ia + RCQ_KMER, B, bb + j + RCQ_KMER,
                                   min(la - ia - RCQ_KMER, lb - j - RCQ_KMER));
     const int32_t rs = ia - left, re = ia + RCQ_KMER + right;
     if (re - rs < RCQ_WORD) return false;
+    if (!clean_window(P.smA, ba, smB, bb, d, rs, re)) return false;
     out->ta = ta; out->tb = tb; out->minus = minus; out->rs = rs; out->re = re; out->diag = d;
     return true;
 }

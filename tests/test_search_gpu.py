@@ -165,22 +165,142 @@ def test_drifting_band_uses_the_wide_fallback(ctx, length):
     assert (cols["gaps"] > 100).all()
 
 
-def test_shared_low_complexity_tails_fail_with_a_clear_message(ctx):
-    """No DUST filter yet: thousands of transcripts sharing a poly-A tail seed against each other
-    quadratically.  The search must stop with RCQ_ERR_CAPACITY and say why, not exhaust the device."""
+def test_dust_mask_equals_the_oracle(ctx):
+    """Seeding mask of the sample build (k_dust_*) = not-ACGT | symmetric DUST of the oracle, base for base, on
+    transcripts mixing random stretches, homopolymers, di-/tri-nucleotide repeats, AT-rich stretches, N's, very
+    short transcripts and one of 15 kb."""
     from rna_clique_b200 import _native
+    from oracle import oracle as O
+    from test_dust_oracle import LET, low_complexity_mix
+    rng = np.random.default_rng(11)
+    lens = [1, 2, 3, 7, 8, 20, 63, 64, 65, 130, 700, 2050, 15000] + [int(x) for x in rng.integers(30, 1500, size=60)]
+    seqs = []
+    for k, n in enumerate(lens):
+        a = LET[low_complexity_mix(rng, n)] if k % 4 else LET[rng.integers(0, 4, size=n)]
+        a = a.copy()
+        if k % 5 == 0 and n > 10:
+            a[rng.integers(0, n, size=3)] = ord("N")
+        seqs.append(a)
+    ascii_ = np.concatenate(seqs)
+    offsets = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    ids = np.arange(len(lens), dtype=np.int32)
+    s = _native.Sample(ctx, ascii_, offsets, ids, np.ones(len(lens), dtype=np.int32))
+    words, n_dust = s.seed_mask()
+    off = s.download()["off"]
+    want = O.Sample(ascii_, offsets, ids, np.ones(len(lens), dtype=np.int32)).dust()
+    codes = np_pack(ascii_, offsets)
+    total_dust = 0
+    for t, n in enumerate(lens):
+        got = unpack_mask(words, off[t], n)
+        exp = want[offsets[t]:offsets[t + 1]] | (codes[offsets[t]:offsets[t + 1]] > 3)
+        assert np.array_equal(got, exp.astype(np.uint8)), f"transcript {t} (length {n})"
+        total_dust += int((want[offsets[t]:offsets[t + 1]] & (codes[offsets[t]:offsets[t + 1]] < 4)).sum())
+    assert n_dust == total_dust and total_dust > 5000
+    # filter off: the seeding mask is the N mask
+    was = ctx.set_dust(False)
+    try:
+        s2 = _native.Sample(ctx, ascii_, offsets, ids, np.ones(len(lens), dtype=np.int32))
+        w2, nd2 = s2.seed_mask()
+        assert nd2 == 0
+        for t, n in enumerate(lens):
+            assert np.array_equal(unpack_mask(w2, off[t], n), (codes[offsets[t]:offsets[t + 1]] > 3).astype(np.uint8))
+    finally:
+        ctx.set_dust(was)
+
+
+def test_shared_low_complexity_tails_are_masked_not_fatal(ctx):
+    """Thousands of transcripts sharing a poly-A tail: without the filter every tail seeds against every other
+    one (9 million runs here, quadratic in the sample size: the round-1 library stopped with RCQ_ERR_CAPACITY
+    at 50,000 genes).  With DUST the tails take no part in seeding and the table is the oracle's."""
+    from rna_clique_b200 import _native
+    from oracle import oracle as O
     rng = np.random.default_rng(2)
-    n, body, tail = 5000, 60, 40
+    n, body, tail = 3000, 300, 40
     letters = np.frombuffer(b"ACGT", dtype=np.uint8)
     seqs = np.concatenate([np.concatenate([letters[rng.integers(0, 4, size=body)], np.full(tail, ord("A"), dtype=np.uint8)])
                            for _ in range(n)])
     offs = np.arange(n + 1, dtype=np.int64) * (body + tail)
     ids = np.arange(n, dtype=np.int32)
-    a = _native.Sample(ctx, seqs, offs, ids, np.ones(n, dtype=np.int32))
-    b = _native.Sample(ctx, seqs[::1].copy(), offs, ids, np.ones(n, dtype=np.int32))
-    with pytest.raises(RuntimeError, match="low-complexity"):
-        _native.search_pair(ctx, a, b)
+    iso = np.ones(n, dtype=np.int32)
+    a = _native.Sample(ctx, seqs, offs, ids, iso)
+    b = _native.Sample(ctx, seqs.copy(), offs, ids, iso)
+    tab = _native.search_pair(ctx, a, b)
+    res = O.search_pair(O.Sample(seqs, offs, ids, iso), O.Sample(seqs, offs, ids, iso))
+    assert tab.stats["n_seeds"] == res.counts["seeds"] == n
+    assert np.array_equal(_native.debug_last_hsps(ctx), res.hsps())
+    assert np.array_equal(_table_matrix(tab), res.rows(2)) and len(tab) == 2 * n
+    was = ctx.set_dust(False)
+    try:
+        a2 = _native.Sample(ctx, seqs, offs, ids, iso)
+        t2 = _native.search_pair(ctx, a2, a2)
+        assert t2.stats["n_seeds"] >= n * n          # every tail against every tail
+        a2.close()
+    finally:
+        ctx.set_dust(was)
     a.close(); b.close()
+
+
+@pytest.mark.parametrize("seed", [1, 2])
+def test_real_assembly_shapes_tails_microsatellites_long_transcripts(ctx, seed):
+    """Isoform / paralog families where a third of the transcripts end in a poly-A tail or a (CA)n stretch, plus
+    15-kb transcripts: HSPs, seed count and table equal to the oracle's."""
+    from helpers import make_family_samples
+    from rna_clique_b200 import _native
+    from oracle import oracle as O
+    raw = make_family_samples(seed=seed, genes=45, tails=30)
+    rng = np.random.default_rng(seed)
+    letters = np.frombuffer(b"ACGT", dtype=np.uint8)
+    long_root = rng.integers(0, 4, size=15000)
+    out = []
+    for k, (a, offs, gene, iso) in enumerate(raw):
+        x = long_root.copy()
+        hit = rng.random(len(x)) < 0.02
+        x[hit] = (x[hit] + rng.integers(1, 4, size=int(hit.sum()))) & 3
+        x = np.delete(x, rng.integers(0, len(x), size=20))
+        a = np.concatenate([a, letters[x], np.full(50, ord("A"), dtype=np.uint8)])
+        offs = np.concatenate([offs, [offs[-1] + len(x) + 50]]).astype(np.int64)
+        out.append((a, offs, np.concatenate([gene, [7 + k]]).astype(np.int32), np.concatenate([iso, [1]]).astype(np.int32)))
+    g = _gpu_samples(ctx, out)
+    o = _oracle_samples(out)
+    assert g[0].seed_mask()[1] > 500
+    tab = _native.search_pair(ctx, g[0], g[1])
+    res = O.search_pair(o[0], o[1])
+    assert tab.stats["n_seeds"] == res.counts["seeds"]
+    assert np.array_equal(_native.debug_last_hsps(ctx), res.hsps())
+    assert np.array_equal(_table_matrix(tab), res.rows(2)) and len(tab) > 40
+    assert (res.rows(2)[:, 0] > 14000).any()                      # the 15-kb pair is in the table
+
+
+def test_poly_a_on_a_third_of_50000_genes_does_not_overflow(ctx):
+    """The failure the round-1 library had on real assemblies: 50,000 genes, 30 % with a 40-base poly-A tail.
+    Every gene still finds its ortholog and nothing else."""
+    import torch
+    from rna_clique_b200 import _native
+    n, body, tail = 50_000, 400, 40
+    g = torch.Generator().manual_seed(3)
+    base = torch.randint(0, 4, (n, body), generator=g, dtype=torch.uint8)
+    letters = torch.tensor([65, 67, 71, 84], dtype=torch.uint8)
+    with_tail = (torch.arange(n) % 10) < 3
+
+    def sample(mut_seed):
+        gg = torch.Generator().manual_seed(mut_seed)
+        x = base.clone()
+        hit = torch.rand((n, body), generator=gg) < 0.01
+        x[hit] = (x[hit] + torch.randint(1, 4, (int(hit.sum()),), generator=gg, dtype=torch.uint8)) & 3
+        rows = torch.cat([letters[x.long()], torch.full((n, tail), 65, dtype=torch.uint8)], dim=1)
+        lens = torch.where(with_tail, body + tail, body)
+        keep = torch.arange(body + tail)[None, :] < lens[:, None]
+        return rows[keep].numpy(), np.concatenate([[0], np.cumsum(lens.numpy())]).astype(np.int64)
+
+    ids, iso = np.arange(n, dtype=np.int32), np.ones(n, dtype=np.int32)
+    a1, o1 = sample(1)
+    a2, o2 = sample(2)
+    s1, s2 = _native.Sample(ctx, a1, o1, ids, iso), _native.Sample(ctx, a2, o2, ids, iso)
+    tab = _native.search_pair(ctx, s1, s2)
+    cols = tab.download()
+    assert len(tab) == 2 * n and (cols["qgene"] == cols["sgene"]).all()
+    assert tab.stats["n_seeds"] < 20 * n
+    s1.close(); s2.close()
 
 
 def _table_matrix(tab):
