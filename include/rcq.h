@@ -81,6 +81,15 @@ int rcq_graph_pickle(const char* path, int32_t n_samples, const char* const* sam
                      const int32_t* sgene, const int32_t* qgene, int64_t n_isolated,
                      const int32_t* iso_sample, const int32_t* iso_gene, int64_t counts[3]);
 
+/* ---- matrix.h5 (host only).  Replaces `mat.to_hdf(output_matrix, key="matrix")` (rna_clique.py:175-177; format:
+ * docs/formats.md:346-352, read back by export_matrix.py:113 pd.read_hdf): writes an HDF5 file holding ONE pandas
+ * fixed-format DataFrame under `key` — group attributes pandas_type="frame", pandas_version, encoding, errors,
+ * ndim, nblocks, *_variety; arrays axis0 (column labels), axis1 (row labels), block0_items, block0_values
+ * (float64, n_cols x n_rows) — without PyTables or libhdf5: superblock version 0, version-1 object headers,
+ * symbol-table groups, contiguous layout.  values is row-major n_rows x n_cols; labels are UTF-8 strings. */
+int rcq_matrix_h5_write(const char* path, const char* key, int64_t n_rows, int64_t n_cols,
+                        const char* const* row_labels, const char* const* col_labels, const double* values);
+
 /* ---- kernels (1)+(2): pack + seed index.  Replaces makeblastdb per sample
  * (find_all_pairs.py:120-159 make_one_db/make_all_dbs -> BlastDBCache.makedb).
  * ascii[ascii_len]: nucleotide letters (no newlines) holding at least the selected transcripts;

@@ -19,7 +19,7 @@ HSP_COLS = ["tx1", "tx2", "minus", "a0", "a1", "b0", "b1", "score2", "mismatch",
 # every symbol include/rcq.h declares (checked by tests/test_abi.py)
 SYMBOLS = [
     "rcq_last_error", "rcq_version", "rcq_ctx_create", "rcq_ctx_destroy", "rcq_ctx_sync", "rcq_ctx_stream",
-    "rcq_ctx_launches", "rcq_ctx_stage_times", "rcq_top_gene_mask", "rcq_fasta_scan", "rcq_fasta_parse", "rcq_parse_spades_ids", "rcq_fasta_format", "rcq_graph_pickle", "rcq_sample_create", "rcq_sample_free", "rcq_sample_info", "rcq_sample_download",
+    "rcq_ctx_launches", "rcq_ctx_stage_times", "rcq_top_gene_mask", "rcq_fasta_scan", "rcq_fasta_parse", "rcq_parse_spades_ids", "rcq_fasta_format", "rcq_graph_pickle", "rcq_matrix_h5_write", "rcq_sample_create", "rcq_sample_free", "rcq_sample_info", "rcq_sample_download",
     "rcq_ctx_set_dust", "rcq_sample_seed_mask",
     "rcq_search_pair", "rcq_table_rows", "rcq_table_download", "rcq_table_free", "rcq_debug_last_hsps", "rcq_debug_keep_hsps",
     "rcq_length_adjustment", "rcq_evalue", "rcq_bitscore", "rcq_phase2_host", "rcq_phase2_tables",
@@ -92,6 +92,7 @@ def lib():
         L.rcq_fasta_format.argtypes = [vp, vp, vp, i64, vp, vp, C.c_int32, vp]
         L.rcq_graph_pickle.argtypes = [C.c_char_p, C.c_int32, vp, C.c_int32, vp, vp, vp, vp, vp, i64, vp, vp, vp]
         L.rcq_fasta_format.restype = i64
+        L.rcq_matrix_h5_write.argtypes = [C.c_char_p, C.c_char_p, i64, i64, vp, vp, vp]
         L.rcq_top_gene_mask.argtypes = [vp, vp, i64, i64, vp]
         L.rcq_top_gene_mask.restype = i64
         L.rcq_debug_keep_hsps.argtypes = [vp, C.c_int]

@@ -119,8 +119,9 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
         tfree(ctx, cand); cand = nullptr;
         if (st.n_verified >= (1ll << 31) || n_seeds >= (1ll << 31))
             return rcq_fail(RCQ_ERR_CAPACITY, "rcq_search_pair: more than 2^31 seed candidates in one pair - low-complexity "
-                            "stretches (poly-A tails, microsatellites) shared by many transcripts; there is no DUST filter "
-                            "yet (DESIGN.md section 3), trim or mask them before the search");
+                            "stretches (poly-A tails, microsatellites) shared by many transcripts seed against each other; "
+                            "the DUST filter that keeps them out of seeding is off for these samples (rcq_ctx_set_dust) "
+                            "or does not cover this repeat");
         if (n_seeds <= cap && st.n_verified <= ccap) { seeded = true; break; }
         tfree(ctx, seeds); seeds = nullptr;
         cap = std::max(cap, n_seeds);

@@ -2,9 +2,10 @@
 outputs (od1/*_top.fasta, od2/<S1>--<S2>.<ext>, graph pickle, distance matrix), same return value
 (SampleSimilarity, {top-genes path: sample name}).  Directories are not created here, as upstream.
 
-matrix file: `.h5` -> DataFrame.to_hdf(key="matrix") exactly as upstream (needs PyTables);
-any other suffix is chosen from {.pkl, .csv, .npy}.  When PyTables is missing and `.h5` is asked
-for, the matrix is written next to it as `.pkl` and the ImportError is re-raised with that path."""
+matrix file: `.h5` -> the pandas fixed-format frame under the key "matrix" that upstream's
+DataFrame.to_hdf(key="matrix") writes, produced by the library's own HDF5 writer (rcq_matrix_h5_write: no
+PyTables needed; pd.read_hdf reads it where PyTables exists, h5fixed.read_frame anywhere); any other suffix is
+chosen from {.pkl, .csv, .npy}."""
 from __future__ import annotations
 
 import os
@@ -21,12 +22,8 @@ from .transcripts import default_parser
 def write_matrix(mat, path: Path) -> Path:
     path = Path(path)
     if path.suffix == ".h5":
-        try:
-            mat.to_hdf(path, key="matrix")
-        except ImportError as e:
-            alt = path.with_suffix(".pkl")
-            mat.to_pickle(alt)
-            raise ImportError(f"{e}; distance matrix saved as {alt} instead") from e
+        from .h5fixed import write_frame
+        write_frame(path, "matrix", mat)
     elif path.suffix == ".csv":
         mat.to_csv(path)
     elif path.suffix == ".npy":

@@ -43,7 +43,8 @@ def test_pack_revcomp_mask(ctx):
 
 
 def test_index_covers_every_28mer_window(ctx):
-    """Winnowing guarantee: every N-free 28-base window holds at least one indexed 16-mer."""
+    """Winnowing guarantee: every 28-base window free of seeding-mask bits (N or DUST) holds at least one
+    indexed 16-mer, and no indexed 16-mer touches a masked base."""
     _, raw = make_samples(taxa=1, count=30, seed=3)
     s = _gpu_samples(ctx, raw)[0]
     d = s.download()
@@ -52,12 +53,21 @@ def test_index_covers_every_28mer_window(ctx):
     sel = np.zeros(s.arena, dtype=bool)
     sel[pos] = True
     offsets = raw[0][1]
+    words, n_dust = s.seed_mask()
+    checked = 0
     for t in range(s.n_seq):
         n = int(offsets[t + 1] - offsets[t])
         o = int(d["off"][t])
         cs = np.concatenate([[0], np.cumsum(sel[o:o + n - 15])])
         win = cs[13:] - cs[:-13]           # windows of 13 consecutive 16-mers
-        assert win.min() >= 1
+        m = unpack_mask(words, o, n)
+        cm = np.concatenate([[0], np.cumsum(m)])
+        clean = (cm[28:] - cm[:-28]) == 0  # 28-base windows without a masked base
+        assert win[clean].min() >= 1
+        checked += int(clean.sum())
+        k16 = (cm[16:] - cm[:-16]) > 0     # 16-mers touching a masked base
+        assert not (sel[o:o + n - 15] & k16).any()
+    assert checked > 0.9 * (offsets[-1] - offsets[0] - 27 * s.n_seq) and n_dust > 0
 
 
 @pytest.mark.parametrize("kw", [
@@ -231,10 +241,14 @@ def test_shared_low_complexity_tails_are_masked_not_fatal(ctx):
     assert np.array_equal(_table_matrix(tab), res.rows(2)) and len(tab) == 2 * n
     was = ctx.set_dust(False)
     try:
-        a2 = _native.Sample(ctx, seqs, offs, ids, iso)
+        m = 300                                       # filter off (blastn -dust no): every tail against every tail
+        a2 = _native.Sample(ctx, seqs[:offs[m]], offs[:m + 1], ids[:m], iso[:m])
         t2 = _native.search_pair(ctx, a2, a2)
-        assert t2.stats["n_seeds"] >= n * n          # every tail against every tail
-        a2.close()
+        assert t2.stats["n_seeds"] >= m * m
+        a3 = _native.Sample(ctx, seqs, offs, ids, iso)
+        with pytest.raises(RuntimeError, match="low-complexity"):      # and at 3,000 transcripts the lists overflow
+            _native.search_pair(ctx, a3, a3)
+        a2.close(); a3.close()
     finally:
         ctx.set_dust(was)
     a.close(); b.close()
