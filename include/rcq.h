@@ -172,6 +172,12 @@ int32_t rcq_length_adjustment(int64_t m, int64_t n, int64_t nseq);
 double rcq_evalue(int32_t score, int64_t m, int64_t n, int64_t nseq);
 double rcq_bitscore(int32_t score);
 
+/* Measurement helper for bench.py (not on the product path): the INT32 instruction-issue ceiling of the GPU in
+ * lane-operations per second (one thread executing one 32-bit integer instruction), from a kernel of
+ * independent add / xor / shift chains at full occupancy; best of `reps` launches.  The integer roofline
+ * k_gapped is held against. */
+int rcq_int32_issue_peak(rcq_ctx* ctx, int32_t reps, double* lane_ops_per_second);
+
 /* ---- kernel (4): gene-match graph, ideal components, per-table reductions.
  * Replaces build_graph.py:40-68, filtered_distance.py:25-39,171-210,234-247 and
  * similarity_computer.py:21-42.  Node id = sample_index*stride + gene.

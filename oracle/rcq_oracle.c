@@ -749,7 +749,7 @@ typedef struct {
 orc_result* orc_search_pair(const orc_sample* s1, const orc_sample* s2, double evalue, int top_n,
                             int keep_all) {
     orc_result* res = calloc(1, sizeof *res);
-    int64_t c0 = g_dp_cells, sd0 = g_seeds;
+    int64_t c0 = g_dp_cells, sd0 = g_seeds, gs0 = g_greedy_steps;
     uvec_t U = find_ungapped(s1, s2);
     res->n_ungapped = U.n;
     res->G = find_gapped(s1, s2, &U);
@@ -764,7 +764,7 @@ orc_result* orc_search_pair(const orc_sample* s1, const orc_sample* s2, double e
     Bc.v = malloc(sizeof(row_t) * (Bc.n + 1)); memcpy(Bc.v, res->B.v, sizeof(row_t) * Bc.n);
     res->T = match_table(&Fc, &Bc, top_n, keep_all);
     free(Fc.v); free(Bc.v);
-    res->dp_cells = g_dp_cells - c0;
+    res->dp_cells = g_gapped_mode ? g_greedy_steps - gs0 : g_dp_cells - c0;
     res->n_seeds = g_seeds - sd0;
     return res;
 }
@@ -778,7 +778,7 @@ orc_result* orc_search_pair(const orc_sample* s1, const orc_sample* s2, double e
 orc_result* orc_search_pair_directions(const orc_sample* s1, const orc_sample* s2, double evalue, int top_n,
                                        int keep_all) {
     orc_result* res = calloc(1, sizeof *res);
-    int64_t c0 = g_dp_cells, sd0 = g_seeds;
+    int64_t c0 = g_dp_cells, sd0 = g_seeds, gs0 = g_greedy_steps;
     double log_cut = evalue > 0 ? log(evalue) : -INFINITY;
     uvec_t U = find_ungapped(s1, s2);
     res->n_ungapped = U.n;
@@ -798,7 +798,7 @@ orc_result* orc_search_pair_directions(const orc_sample* s1, const orc_sample* s
     Bc.v = malloc(sizeof(row_t) * (Bc.n + 1)); memcpy(Bc.v, res->B.v, sizeof(row_t) * Bc.n);
     res->T = match_table(&Fc, &Bc, top_n, keep_all);
     free(Fc.v); free(Bc.v);
-    res->dp_cells = g_dp_cells - c0;
+    res->dp_cells = g_gapped_mode ? g_greedy_steps - gs0 : g_dp_cells - c0;
     res->n_seeds = g_seeds - sd0;
     return res;
 }
@@ -806,7 +806,9 @@ void orc_result_free(orc_result* r) {
     if (!r) return;
     free(r->G.v); free(r->F.v); free(r->B.v); free(r->T.v); free(r);
 }
-/* counts: [0]=#gapped HSPs [1]=#fwd rows [2]=#bwd rows [3]=#table rows [4]=#seeds [5]=#ungapped [6]=dp cells */
+/* counts: [0]=#gapped HSPs [1]=#fwd rows [2]=#bwd rows [3]=#table rows [4]=#seeds [5]=#ungapped
+ * [6]=base comparisons of the gapped stage ("extension steps": the greedy waves' slide steps; cells of the
+ * cross-check DP when that mode is selected) */
 void orc_result_counts(const orc_result* r, int64_t* c) {
     c[0] = r->G.n; c[1] = r->F.n; c[2] = r->B.n; c[3] = r->T.n;
     c[4] = r->n_seeds; c[5] = r->n_ungapped; c[6] = r->dp_cells;

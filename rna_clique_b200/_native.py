@@ -20,7 +20,7 @@ HSP_COLS = ["tx1", "tx2", "minus", "a0", "a1", "b0", "b1", "score2", "mismatch",
 SYMBOLS = [
     "rcq_last_error", "rcq_version", "rcq_ctx_create", "rcq_ctx_destroy", "rcq_ctx_sync", "rcq_ctx_stream",
     "rcq_ctx_launches", "rcq_ctx_stage_times", "rcq_top_gene_mask", "rcq_fasta_scan", "rcq_fasta_parse", "rcq_parse_spades_ids", "rcq_fasta_format", "rcq_graph_pickle", "rcq_matrix_h5_write", "rcq_sample_create", "rcq_sample_free", "rcq_sample_info", "rcq_sample_download",
-    "rcq_ctx_set_dust", "rcq_sample_seed_mask",
+    "rcq_ctx_set_dust", "rcq_sample_seed_mask", "rcq_int32_issue_peak",
     "rcq_search_pair", "rcq_table_rows", "rcq_table_download", "rcq_table_free", "rcq_debug_last_hsps", "rcq_debug_keep_hsps",
     "rcq_length_adjustment", "rcq_evalue", "rcq_bitscore", "rcq_phase2_host", "rcq_phase2_tables",
     "rcq_table_flat_words", "rcq_table_flatten", "rcq_table_from_flat", "rcq_sample_meta", "rcq_sample_export", "rcq_sample_import",
@@ -76,6 +76,7 @@ def lib():
         L.rcq_sample_info.argtypes = [vp, vp]
         L.rcq_sample_download.argtypes = [vp, vp, vp, vp, vp, vp]
         L.rcq_ctx_set_dust.argtypes = [vp, C.c_int]
+        L.rcq_int32_issue_peak.argtypes = [vp, i32, C.POINTER(dbl)]
         L.rcq_sample_seed_mask.argtypes = [vp, vp, vp]
         L.rcq_search_pair.argtypes = [vp, vp, vp, dbl, i32, i32, C.POINTER(vp), C.POINTER(SearchStats)]
         L.rcq_table_rows.argtypes = [vp]
@@ -160,6 +161,12 @@ class Context:
         """DUST soft-masking of seeds for samples created on this context from now on (default on, as in
         blastn); returns the previous setting."""
         return bool(lib().rcq_ctx_set_dust(self.h, int(bool(on))))
+
+    def int32_issue_peak(self, reps: int = 5) -> float:
+        """Measured INT32 issue ceiling of the device, lane-operations per second (rcq_int32_issue_peak)."""
+        v = C.c_double()
+        check(lib().rcq_int32_issue_peak(self.h, int(reps), C.byref(v)))
+        return float(v.value)
 
     def close(self):
         if self.h:
@@ -320,10 +327,15 @@ def fasta_format(ascii_: np.ndarray, starts, lengths, headers, width: int = 60) 
     ascii_ = np.ascontiguousarray(ascii_, dtype=np.uint8)
     starts = np.ascontiguousarray(starts, dtype=np.int64)
     lengths = np.ascontiguousarray(lengths, dtype=np.int64)
-    hb = [h.encode() for h in headers]
-    hdr = np.frombuffer(b"".join(hb), dtype=np.uint8) if hb else np.zeros(0, np.uint8)
-    hdr_off = np.zeros(len(hb) + 1, dtype=np.int64)
-    np.cumsum([len(b) for b in hb], out=hdr_off[1:])
+    if isinstance(headers, tuple):          # (uint8 text, int64 offsets), Fasta.header_bytes
+        hdr = np.ascontiguousarray(headers[0], dtype=np.uint8)
+        hdr_off = np.ascontiguousarray(headers[1], dtype=np.int64)
+        hb = range(len(hdr_off) - 1)
+    else:
+        hb = [h.encode() for h in headers]
+        hdr = np.frombuffer(b"".join(hb), dtype=np.uint8) if hb else np.zeros(0, np.uint8)
+        hdr_off = np.zeros(len(hb) + 1, dtype=np.int64)
+        np.cumsum([len(b) for b in hb], out=hdr_off[1:])
     args = (ascii_.ctypes.data, starts.ctypes.data, lengths.ctypes.data, len(hb), hdr.ctypes.data if len(hdr) else None,
             hdr_off.ctypes.data, int(width))
     size = lib().rcq_fasta_format(*args, None)

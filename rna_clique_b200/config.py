@@ -121,8 +121,8 @@ class RNACliqueConfig:
             if self.graph is None:
                 self.graph = self.output_dir / "graph.pkl"
             if self.matrix is None:
-                ext = "h5" if default_extension() == "h5" else "pkl"    # HDF5 needs PyTables
-                self.matrix = self.output_dir / f"distance_matrix.{ext}"
+                # the upstream name (config.py:1482); written by the library's own HDF5 writer (h5fixed.py)
+                self.matrix = self.output_dir / "distance_matrix.h5"
         return self
 
     def make_output_dirs(self) -> None:

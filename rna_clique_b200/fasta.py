@@ -11,19 +11,45 @@ import numpy as np
 
 @dataclass
 class Fasta:
-    headers: list          # header lines without '>' (id = first whitespace-separated token)
+    _headers: list         # header lines without '>' (id = first whitespace-separated token); None = decode lazily from raw
     ascii: np.ndarray      # uint8, all sequence letters concatenated, newlines removed
     offsets: np.ndarray    # int64 [n+1]
     raw: np.ndarray = None        # the file bytes and the byte span of every header line, kept so the
-    hdr_start: np.ndarray = None  # default id pattern can be decoded natively (parse_fasta_ids)
-    hdr_end: np.ndarray = None
+    hdr_start: np.ndarray = None  # default id pattern can be decoded natively (parse_fasta_ids) and the
+    hdr_end: np.ndarray = None    # selected headers can be copied without becoming Python strings
+
+    @property
+    def headers(self):
+        if self._headers is None:
+            mv = memoryview(self.raw)
+            self._headers = [str(mv[a + 1:b], "utf-8").rstrip("\r") for a, b in zip(self.hdr_start.tolist(), self.hdr_end.tolist())]
+        return self._headers
 
     @property
     def ids(self):
         return [h.split(None, 1)[0] if h else "" for h in self.headers]
 
+    def header_bytes(self, keep):
+        """(uint8 header text of the records `keep` concatenated, int64 offsets [len(keep)+1]) without '>' or a
+        trailing CR, gathered from the file bytes with numpy (no Python string per record)."""
+        keep = np.asarray(keep, dtype=np.int64)
+        if self.raw is None:
+            hb = [self._headers[i].encode() for i in keep]
+            off = np.zeros(len(hb) + 1, dtype=np.int64)
+            np.cumsum([len(b) for b in hb], out=off[1:])
+            return (np.frombuffer(b"".join(hb), dtype=np.uint8) if hb else np.zeros(0, np.uint8)), off
+        a = self.hdr_start[keep] + 1
+        b = self.hdr_end[keep].copy()
+        has = b > a
+        b[has] -= (self.raw[b[has] - 1] == 13)
+        ln = np.maximum(b - a, 0)
+        off = np.zeros(len(keep) + 1, dtype=np.int64)
+        np.cumsum(ln, out=off[1:])
+        idx = np.arange(int(off[-1]), dtype=np.int64) + np.repeat(a - off[:-1], ln)
+        return self.raw[idx], off
+
     def __len__(self):
-        return len(self.headers)
+        return len(self.offsets) - 1
 
 
 def read_fasta(path: Path) -> Fasta:
@@ -35,9 +61,7 @@ def read_fasta(path: Path) -> Fasta:
     if raw.size == 0:
         return Fasta([], np.zeros(0, np.uint8), np.zeros(1, np.int64))
     ascii_, offsets, hs, he = _native.fasta_parse(raw)
-    mv = memoryview(raw)          # header lines are decoded from views: the file bytes are not copied
-    headers = [str(mv[a + 1:b], "utf-8").rstrip("\r") for a, b in zip(hs.tolist(), he.tolist())]
-    return Fasta(headers, ascii_, offsets, raw, hs, he)
+    return Fasta(None, ascii_, offsets, raw, hs, he)    # header strings are decoded only if somebody asks
 
 
 def read_fasta_numpy(path: Path) -> Fasta:
@@ -67,9 +91,10 @@ def read_fasta_numpy(path: Path) -> Fasta:
 
 def write_fasta(path: Path, headers, ascii_: np.ndarray, starts, lengths, width: int = 60) -> None:
     """Biopython-style output (SeqIO.write(..., "fasta"): '>' + header, 60 letters per line), as
-    select_top_genes_all.py:37-45 writes od1/<sample>_top.fasta.  Formatted natively in one buffer."""
+    select_top_genes_all.py:37-45 writes od1/<sample>_top.fasta.  Formatted natively in one buffer.
+    headers: list of str, or the (bytes, offsets) pair of Fasta.header_bytes."""
     from . import _native
-    _native.fasta_format(ascii_, starts, lengths, list(headers), width).tofile(str(path))
+    _native.fasta_format(ascii_, starts, lengths, headers if isinstance(headers, tuple) else list(headers), width).tofile(str(path))
 
 
 def write_fasta_python(path: Path, headers, ascii_: np.ndarray, starts, lengths, width: int = 60) -> None:

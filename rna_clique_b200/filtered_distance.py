@@ -64,12 +64,16 @@ class SampleSimilarity:
     sample_gene_columns = [["ssample", "sgene"], ["qsample", "qgene"]]
 
     def __init__(self, graph: Optional[nx.Graph], comparison_dfs: Iterable, sample_count: Optional[int] = None,
-                 ctx: Optional[_native.Context] = None):
+                 ctx: Optional[_native.Context] = None, _device: Optional[dict] = None):
+        """_device (set by rna_clique()): the device-resident tables the graph was built from
+        (filtering_step); while the graph is untouched the reduction runs on them (rcq_phase2_tables) and
+        `comparison_dfs` - lazy readers of the same tables on disk - is not consumed."""
         self.graph = graph
         self._sample_count = sample_count
         self._source = comparison_dfs
         self._stored = comparison_dfs if isinstance(comparison_dfs, Mapping) else None
         self._ctx_override = ctx
+        self._device = _device
 
     # ---- ingestion --------------------------------------------------------------------------
     @staticmethod
@@ -100,8 +104,36 @@ class SampleSimilarity:
         return out
 
     # ---- the device call ----------------------------------------------------------------------
+    def _use_device(self) -> bool:
+        return (self._device is not None and isinstance(self.graph, GeneMatchGraph) and self.graph.rcq_edges is not None
+                and all(t.h is not None for t in self._device["tables"]))
+
+    @cached_property
+    def _pair_names(self):
+        """(ssample, qsample) of every comparison table, in table order."""
+        if self._use_device():
+            d = self._device
+            if any(d["empty"]):
+                raise KeyError(0)   # the reference reads df["qsample"][0] of every table
+            return [(d["labels"][i], d["labels"][j]) for i, j in d["pairs"]]
+        return [(t["ssample"], t["qsample"]) for t in self._tables]
+
+    def _phase2_device(self):
+        d = self._device
+        names = sorted({s for pair in self._pair_names for s in pair})
+        idx = {s: i for i, s in enumerate(names)}
+        eng = d["engine"]
+        stride = 1 + max([0] + [int(max(sg.max(initial=0), qg.max(initial=0))) for _, _, sg, qg in self.graph.rcq_edges.groups])
+        res = _native.phase2_tables(self._ctx_override or eng.ctx, len(names), stride, d["tables"],
+                                    [idx[d["labels"][i]] for i, _ in d["pairs"]], [idx[d["labels"][j]] for _, j in d["pairs"]],
+                                    self._sample_count, True)
+        res.update(names=names, stride=stride, index=idx, n_real=len(d["tables"]))
+        return res
+
     @cached_property
     def _phase2(self):
+        if self._use_device():
+            return self._phase2_device()
         tabs = self._tables
         edges = None
         extra_samples = set()
@@ -124,7 +156,9 @@ class SampleSimilarity:
         row_off = np.concatenate([[0], np.cumsum([len(r[2]) for r in rows])]).astype(np.int64)
         sc = self._sample_count
         if sc is None and extra_samples:
-            sc = len(names)
+            # samples are counted over the graph's nodes only (filtered_distance.py:171-182): its edges and its
+            # isolated nodes; a sample that appears in the tables alone does not count
+            sc = len(extra_samples | {g[0] for g in edges.groups} | {g[1] for g in edges.groups})
         res = _native.phase2_host(self._ctx_override or _ctx(), len(names), stride, row_off, [r[0] for r in rows],
                                   [r[1] for r in rows], cat(2), cat(3), cat(4), cat(5), cat(6), sc, True,
                                   t_flags=[r[7] for r in rows])
@@ -179,10 +213,10 @@ class SampleSimilarity:
     def similarities(self) -> PairDict:
         p = self._phase2
         d = PairDict()
-        for t, ni, de in zip(self._tables, p["nident_sum"].tolist(), p["denom_sum"].tolist()):
+        for (ss, qs), ni, de in zip(self._pair_names, p["nident_sum"].tolist(), p["denom_sum"].tolist()):
             if de == 0:
                 raise NoIdealComponentsError()
-            d[(t["qsample"], t["ssample"])] = Fraction(int(ni), int(de))
+            d[(qs, ss)] = Fraction(int(ni), int(de))
         self._samples = sorted(d.key_elements())
         for s in self._samples:
             d[(s, s)] = 1

@@ -1,33 +1,156 @@
 """Phase 1 driver.  Mirrors the reference's filtering_step.py:61-164: top genes per sample ->
-all-pairs tables -> gene-matches graph -> graph pickle; returns lazy table readers."""
+all-pairs tables -> gene-matches graph -> graph pickle; returns lazy table readers.
+
+The reference runs three joblib stages one after the other (select_top_and_save per sample :128-143,
+makeblastdb per sample and blastn per pair inside find_all_pairs :144-156, build_graph :157).  Here they are
+one dependency-driven schedule on the multi-stream engine (engine.Engine._run_tasks):
+
+  host pool (up to `jobs` threads)    read + parse + select + write od1/<sample>_top.fasta   (native, GIL released)
+  engine workers (one per CUDA stream) upload sample k as soon as its records exist (pack, DUST, seed index),
+                                       search pair (i, j) as soon as both samples are resident, download the table
+  host pool again                      table -> DataFrame -> od2/<S1>--<S2>.<ext>, while later pairs search
+
+and the device tables stay resident: the graph is built from their gene columns, graph.pkl is written natively
+from the flat edge arrays, and SampleSimilarity reduces the device tables directly (rcq_phase2_tables) instead
+of reading od2/ back."""
 from __future__ import annotations
 
 import itertools
 import os
-import pickle
+import threading
+from concurrent.futures import ThreadPoolExecutor
 from pathlib import Path
-from typing import Callable, Iterable
+from typing import Callable, Iterable, Optional
 
-from .build_graph import build_graph, dump_graph
+import numpy as np
+
+from . import _native
+from .build_graph import EdgeArrays, GeneMatchGraph, dump_graph
 from .filtered_distance import SampleSimilarity
-from .find_all_pairs import find_all_pairs
-from .select_top_genes import select_top_and_save, select_top_and_save_all
+from .find_all_pairs import _label_and_save, make_output_path
+from .find_homologs import table_to_frame
+from .gene_matches_tables import default_extension
+from .select_top_genes import _select_and_write
 from .transcripts import default_parser
+
+_engine = None
+_engine_lock = threading.Lock()
+
+
+def shared_engine(jobs: Optional[int] = None, device: int = 0):
+    """The process-wide engine of the drop-in API: 2-6 CUDA streams (contexts) on one GPU, kept between calls so
+    that scratch slabs and memory pools are warm."""
+    global _engine
+    from .engine import Engine
+    with _engine_lock:
+        if _engine is None:
+            _engine = Engine(device, streams=max(2, min(6, int(jobs or 4))))
+        return _engine
+
+
+def close_shared_engine() -> None:
+    global _engine
+    with _engine_lock:
+        if _engine is not None:
+            _engine.close()
+            _engine = None
+
+
+def _frame_and_save(cols, db, t1, t2, out_path):
+    _label_and_save(table_to_frame(cols, *db), t1, t2, out_path)
 
 
 def filtering_step(dirs: Iterable[Path], out_dir_1: Path, out_dir_2: Path, cache_dir: Path, output_graph: Path,
                    top_genes: int, transcripts: str = "transcripts.fasta", top_matches: int = 1,
                    id_parser: Callable = default_parser, evalue: float = 1e-99, keep_all: bool = True,
                    jobs: int = max((os.cpu_count() or 2) - 1, 1)):
-    # the selected records go to the device as they are written (the role of make_all_dbs right after):
-    # od1/*_top.fasta is not read back
-    from .find_homologs import default_cache
-    path_to_sample = select_top_and_save_all(Path(out_dir_1), transcripts, dirs, top_genes, id_parser,
-                                             preload=default_cache(), jobs=jobs)
-    tables, table_paths, num_tables = find_all_pairs(path_to_sample, out_dir_2, cache_dir, path_to_sample.__getitem__,
-                                                     hf_args=[id_parser, top_matches, evalue, keep_all], jobs=jobs)
-    graph = build_graph(tables)
-    if output_graph is not None:
-        dump_graph(graph, output_graph)
-    p1, p2 = itertools.tee(table_paths)
-    return map(SampleSimilarity._read_table, p1), p2, graph, num_tables, path_to_sample
+    """Returns (tables, table_paths, graph, num_tables, path_to_sample) like the reference; `tables` reads the
+    od2/ files lazily, `graph` is a GeneMatchGraph (an nx.Graph filled on first use) that also carries the
+    device-resident tables for SampleSimilarity.  cache_dir is accepted and unused: the databases live in HBM."""
+    dirs = [Path(d) for d in dirs]
+    n = len(dirs)
+    eng = shared_engine(jobs)
+    S = len(eng.ctxs)
+    workers = max(1, min(int(jobs or 1), 16))
+    ext = default_extension()
+    pairs = list(itertools.combinations(range(n), 2))
+    out_paths = [Path(out_dir_1) / (d.stem + "_top.fasta") for d in dirs]
+    names = [d.stem for d in dirs]
+    table_paths = [make_output_path(out_dir_2, out_paths[i], out_paths[j], dict(zip(out_paths, names)).__getitem__, ext)
+                   for i, j in pairs]
+    samples = [None] * n
+    tables = [None] * len(pairs)
+    edges = [None] * len(pairs)
+    writes = [None] * len(pairs)
+    host = ThreadPoolExecutor(workers)
+    try:
+        # at most `window` parsed files are alive (a parsed 100,000-transcript file is ~0.4 GB of host memory)
+        window = workers + 2
+        lock = threading.Lock()
+        parsed = {}
+        state = {"next": 0}
+
+        def submit_parse():
+            with lock:
+                k = state["next"]
+                if k >= n:
+                    return
+                state["next"] = k + 1
+                parsed[k] = host.submit(_select_and_write, out_dir_1, transcripts, dirs[k], top_genes, id_parser)
+
+        for _ in range(min(window, n)):
+            submit_parse()
+        by_last = {}
+        for slot, (i, j) in enumerate(pairs):
+            by_last.setdefault(j, []).append(slot)
+        tasks = []
+        for k in range(n):
+            tasks.append(("u", k))
+            tasks.extend(("s", slot) for slot in by_last.get(k, []))
+
+        def ready(task, w):
+            kind, x = task
+            if kind == "u":
+                f = parsed.get(x)
+                return x % S == w and f is not None and f.done()
+            i, j = pairs[x]
+            return samples[i] is not None and samples[j] is not None
+
+        def run(ctx, task):
+            kind, x = task
+            if kind == "u":
+                out, _, rec = parsed.pop(x).result()
+                samples[x] = _native.Sample(ctx, rec[1], rec[2], rec[3], rec[4], name=str(out), lengths=rec[5])
+                del rec
+                submit_parse()
+                return
+            i, j = pairs[x]
+            s1, s2 = samples[i], samples[j]
+            t = _native.search_pair(ctx, s1, s2, evalue, top_matches, keep_all)
+            cols = t.download()
+            tables[x] = t
+            edges[x] = (cols["sgene"], cols["qgene"])
+            writes[x] = host.submit(_frame_and_save, cols, (s1.total, s1.n_seq, s2.total, s2.n_seq),
+                                    out_paths[i], out_paths[j], table_paths[x])
+
+        eng._run_tasks(tasks, ready, run, poll=0.0005)
+        e = EdgeArrays()
+        for slot, (i, j) in enumerate(pairs):
+            if len(edges[slot][0]):
+                e.add(str(out_paths[i]), str(out_paths[j]), *edges[slot])
+        graph = GeneMatchGraph(e)
+        # the device tables travel with the graph: SampleSimilarity reduces them in place (rna_clique.py hands them on)
+        graph.__dict__["_rcq_device"] = dict(engine=eng, tables=tables, pairs=pairs, labels=[str(p) for p in out_paths],
+                                             empty=[len(t) == 0 for t in tables])
+        if output_graph is not None:
+            dump_graph(graph, output_graph)
+        for f in writes:
+            f.result()
+    finally:
+        host.shutdown(wait=True)
+        for s in samples:
+            if s is not None:
+                s.close()
+    path_to_sample = dict(zip(out_paths, names))
+    p1, p2 = iter(table_paths), iter(table_paths)
+    return map(SampleSimilarity._read_table, p1), p2, graph, len(pairs), path_to_sample

@@ -44,7 +44,7 @@ def rna_clique(dirs: Iterable[Path], out_dir_1: Path, out_dir_2: Path, cache_dir
     tables = SampleSimilarity.mapping_from_dfs(tables)
     if store_dfs:
         tables = dict(tables)
-    sim = SampleSimilarity(graph, tables)
+    sim = SampleSimilarity(graph, tables, _device=getattr(graph, "__dict__", {}).get("_rcq_device"))
     if output_matrix is not None:
         write_matrix(sim.get_dissimilarity_df(), output_matrix)
     return sim, pts

@@ -76,7 +76,7 @@ def _select_and_write(out_dir: Path, transcripts: str, x: Path, *args):
     sel = TopGeneSelector.from_path(x / transcripts, *args)
     fa, keep, _, gene, iso = sel.get_top_gene_seqs()
     starts, lengths = fa.offsets[:-1][keep], np.diff(fa.offsets)[keep]
-    write_fasta(out, [fa.headers[i] for i in keep], fa.ascii, starts, lengths)
+    write_fasta(out, fa.header_bytes(keep), fa.ascii, starts, lengths)
     return out, x.stem, (sel.parser, fa.ascii, starts, np.asarray(gene, dtype=np.int32), np.asarray(iso, dtype=np.int32),
                          lengths.astype(np.int32))
 

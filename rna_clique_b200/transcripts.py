@@ -74,7 +74,9 @@ def parse_fasta_ids(fa, parser=default_parser):
     """parse_ids over the records of a Fasta.  The default rnaSPAdes pattern is decoded natively from the
     file bytes (rcq_parse_spades_ids, same re.search semantics: the last position that matches wins);
     any other parser runs in Python."""
-    if parser is default_parser and getattr(fa, "raw", None) is not None and len(fa):
+    pat = getattr(parser, "pattern", None)
+    is_default = parser is default_parser or (pat is not None and pat.pattern == default_gene_re.pattern and pat.flags == default_gene_re.flags)
+    if is_default and getattr(fa, "raw", None) is not None and len(fa):
         from . import _native
         cov, gene, iso, bad = _native.parse_spades_ids(fa.raw, fa.hdr_start, fa.hdr_end)
         if bad >= 0:

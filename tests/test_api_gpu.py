@@ -82,6 +82,7 @@ def test_rna_clique_end_to_end(tmp_path):
     od1.mkdir(); od2.mkdir()
     sim, pts = rna_clique(dirs, od1, od2, tmp_path / "db", tmp_path / "graph.pkl", tmp_path / "matrix.pkl", 100)
     assert sorted(pts.values()) == ["T0", "T1", "T2"] and all(p.exists() for p in pts)
+    assert sim._use_device()                           # reduced on the device-resident tables, od2/ not read back
     ext = default_extension()
     assert sorted(p.name for p in get_table_files(od2)) == [f"T0--T1.{ext}", f"T0--T2.{ext}", f"T1--T2.{ext}"]
     mat = pd.read_pickle(tmp_path / "matrix.pkl")
@@ -117,6 +118,33 @@ def test_rna_clique_end_to_end(tmp_path):
     # phase-2-only entry on the files just written
     again = SampleSimilarity.from_filenames(tmp_path / "graph.pkl", sorted(get_table_files(od2)))
     assert np.array_equal(again.get_dissimilarity_df().to_numpy(), m)
+    assert sorted(again.valid.itertuples(index=False, name=None)) == sorted(sim.valid.itertuples(index=False, name=None))
+    # touching the graph through networkx drops the device fast path; the tables are then read from od2/
+    sim2, _ = rna_clique(dirs, od1, od2, tmp_path / "db", tmp_path / "graph.pkl", None, 100, top_matches=2, keep_all=False)
+    g2 = sim2.graph
+    g2.add_node(("extra", 1)); g2.remove_node(("extra", 1))
+    assert not sim2._use_device()
+    want2 = [O.search_pair(osamples[i], osamples[j], top_n=2, keep_all=False).rows(2) for i in range(3) for j in range(i + 1, 3)]
+    ot2 = [dict(s=i, q=j, sgene=w[:, 12], qgene=w[:, 10], nident=w[:, 9], length=w[:, 0], gaps=w[:, 8])
+           for (i, j), w in zip([(0, 1), (0, 2), (1, 2)], want2)]
+    e2 = phase2_ref.phase2(3, ot2)
+    _, m2 = phase2_ref.distance_matrix([str(p) for p in paths], ot2, e2["sums"])
+    assert np.array_equal(sim2.get_dissimilarity_df().to_numpy(), m2)
+
+
+def test_rna_clique_writes_matrix_h5(tmp_path):
+    """The on-disk contract of the metric: rna_clique(..., output_matrix="distance_matrix.h5") (rna_clique.py:175-177)."""
+    from rna_clique_b200 import h5fixed
+    from rna_clique_b200.rna_clique import rna_clique
+    from rna_clique_b200.simulate import simulate, write_dataset
+    _, ts = simulate(4, 120, seed=3, mutation_rate=0.02)
+    dirs = write_dataset(tmp_path / "in", ts)
+    (tmp_path / "od1").mkdir(); (tmp_path / "od2").mkdir()
+    sim, pts = rna_clique(dirs, tmp_path / "od1", tmp_path / "od2", tmp_path / "db", tmp_path / "graph.pkl",
+                          tmp_path / "distance_matrix.h5", 90, jobs=3)
+    m = h5fixed.read_frame(tmp_path / "distance_matrix.h5", "matrix")
+    assert m.equals(sim.get_dissimilarity_df()) and m.shape == (4, 4) and list(m.index) == sorted(str(p) for p in pts)
+    assert len(list((tmp_path / "od2").iterdir())) == 6
 
 
 def test_run_analysis_from_yaml(tmp_path):
