@@ -25,7 +25,7 @@
 
 #define DUST_MAXT 62
 #define DUST_SEG 256          // end positions per thread of k_dust_flag
-#define DUST_FLAG_THREADS 128
+#define DUST_FLAG_THREADS 64
 #define DUST_EVAL_THREADS 128
 
 // 16 positions per thread: triplets starting at p .. p+15 need bases p .. p+17
@@ -47,36 +47,55 @@ __global__ void k_dust_triplets(const uint32_t* __restrict__ fwd, const uint32_t
     *(uint4*)(trip + w * 16) = make_uint4(out[0], out[1], out[2], out[3]);
 }
 
+// A block covers DUST_FLAG_THREADS x DUST_SEG consecutive positions.  Its triplet bytes (plus the 64 before them)
+// are staged in shared memory with coalesced loads, rows of 256 bytes padded to 260 so that the lanes of a warp,
+// which walk 256 bytes apart, read different banks; a thread's four counters of one word (triplet & 3) share a
+// 32-bit word whose bank is the thread's own.  (Reading the bytes straight from global memory cost 3.7 ms per
+// sample: 32 sectors per warp load, four loads per step.)
+#define DUST_ROW 260
 __global__ void __launch_bounds__(DUST_FLAG_THREADS) k_dust_flag(const uint8_t* __restrict__ trip, int64_t arena,
                                                                   uint32_t* __restrict__ flag) {
-    // counters [scale][triplet][thread]: lanes of a warp touch consecutive bytes for equal triplets
-    __shared__ uint8_t cnt[3 * 64 * DUST_FLAG_THREADS];
+    __shared__ uint32_t cnt[3 * 16 * DUST_FLAG_THREADS];                      // [scale][triplet >> 2][thread], byte = triplet & 3
+    __shared__ __align__(16) uint8_t tb[(DUST_FLAG_THREADS + 1) * DUST_ROW];   // positions block_start - 64 ..
     const int tid = threadIdx.x;
-    const int64_t seg = (int64_t)blockIdx.x * DUST_FLAG_THREADS + tid;
-    const int64_t start = seg * DUST_SEG;
-    for (int i = tid; i < 3 * 64 * DUST_FLAG_THREADS / 4; i += DUST_FLAG_THREADS) ((uint32_t*)cnt)[i] = 0u;
+    const int64_t block_start = (int64_t)blockIdx.x * DUST_FLAG_THREADS * DUST_SEG;
+    for (int i = tid; i < 3 * 16 * DUST_FLAG_THREADS; i += DUST_FLAG_THREADS) cnt[i] = 0u;
+    // stage: word w of the region holds positions block_start - 64 + 4w .. +3
+    const int n_words = (DUST_FLAG_THREADS * DUST_SEG + 64) / 4;
+    for (int w = tid; w < n_words; w += DUST_FLAG_THREADS) {
+        const int64_t p = block_start - 64 + 4ll * w;
+        uint32_t v = 0xFFFFFFFFu;
+        if (p >= 0 && p + 4 <= arena) v = __ldg((const uint32_t*)(trip + p));
+        const int rel = 4 * w;
+        *(uint32_t*)(tb + (rel >> 8) * DUST_ROW + (rel & 255)) = v;
+    }
     __syncthreads();
+    const int64_t start = block_start + (int64_t)tid * DUST_SEG;
     if (start >= arena) return;
-    const int64_t warm = start >= DUST_MAXT ? start - DUST_MAXT : 0;
     const int64_t end = min(start + DUST_SEG, arena);
     int32_t r16 = 0, r32 = 0, r62 = 0;
     uint32_t bits = 0;
-#define CNT(s, t) cnt[((s) * 64 + (t)) * DUST_FLAG_THREADS + tid]
-    for (int64_t e = warm; e < end; e++) {
-        const uint32_t t = trip[e];
-        if (t != 0xFFu) {
-            r16 += CNT(0, t)++; r32 += CNT(1, t)++; r62 += CNT(2, t)++;
-        }
-        if (e - 16 >= warm) { const uint32_t o = trip[e - 16]; if (o != 0xFFu) r16 -= --CNT(0, o); }
-        if (e - 32 >= warm) { const uint32_t o = trip[e - 32]; if (o != 0xFFu) r32 -= --CNT(1, o); }
-        if (e - DUST_MAXT >= warm) { const uint32_t o = trip[e - DUST_MAXT]; if (o != 0xFFu) r62 -= --CNT(2, o); }
-        if (e >= start) {
-            if (t != 0xFFu && (r16 > 8 || r32 > 32 || r62 > 64)) bits |= 1u << (e & 31);
-            if ((e & 31) == 31) { flag[e >> 5] = bits; bits = 0; }
+    uint8_t* cb = (uint8_t*)cnt;
+#define TB(rel) tb[((rel) >> 8) * DUST_ROW + ((rel) & 255)]
+#define CNT(s, t) cb[(((s) * 16 + ((t) >> 2)) * DUST_FLAG_THREADS + tid) * 4 + ((t) & 3)]
+    // rel = position - (block_start - 64); the walk starts DUST_MAXT positions early to fill the windows
+    const int rel0 = 64 + tid * DUST_SEG;
+    const int n = (int)(end - start);
+    for (int x = -DUST_MAXT; x < n; x++) {
+        const int rel = rel0 + x;
+        const uint32_t t = TB(rel);
+        if (t != 0xFFu) { r16 += CNT(0, t)++; r32 += CNT(1, t)++; r62 += CNT(2, t)++; }
+        if (x - 16 >= -DUST_MAXT) { const uint32_t o = TB(rel - 16); if (o != 0xFFu) r16 -= --CNT(0, o); }
+        if (x - 32 >= -DUST_MAXT) { const uint32_t o = TB(rel - 32); if (o != 0xFFu) r32 -= --CNT(1, o); }
+        if (x >= 0) {
+            const uint32_t o = TB(rel - DUST_MAXT);          // x - 62 >= -62
+            if (o != 0xFFu) r62 -= --CNT(2, o);
+            if (t != 0xFFu && (r16 > 8 || r32 > 32 || r62 > 64)) bits |= 1u << (x & 31);
+            if ((x & 31) == 31) { flag[(start + x) >> 5] = bits; bits = 0; }
         }
     }
 #undef CNT
-    if (end & 31) flag[(end - 1) >> 5] = bits;   // arena is a multiple of 64, DUST_SEG of 32: not reached
+#undef TB
 }
 
 // Warp per 1024 positions (grid-stride): the flagged end positions of the chunk are listed in shared memory,

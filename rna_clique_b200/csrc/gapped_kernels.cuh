@@ -410,7 +410,8 @@ __global__ void __launch_bounds__(128, 5) k_gapped(const Ungapped* __restrict__ 
                                                 const uint64_t* __restrict__ keys, int64_t n, KeyFmt F,
                                                 const uint32_t* __restrict__ heads, int64_t n_groups,
                                                 PairView P, Gapped* __restrict__ out, ScratchPool sp,
-                                                unsigned long long* __restrict__ ctr /* [0]=next group [1]=cells [2]=retries [3]=n gapped */) {
+                                                unsigned long long* __restrict__ ctr /* [0]=next group [1]=cells [2]=retries [3]=n gapped */,
+                                                const uint32_t* __restrict__ hlist /* deferred groups (k_gapped_half), or NULL = all groups */) {
     const int lane = threadIdx.x & 31;
     __shared__ __align__(16) int32_t ring_all[4][6 * RCQ_RING];
     // staged strands of the group's two transcripts (fast path): A forward, A reverse complement, B on the
@@ -421,10 +422,11 @@ __global__ void __launch_bounds__(128, 5) k_gapped(const Ungapped* __restrict__ 
     unsigned long long cells = 0, retries = 0, produced = 0;
     while (true) {
         unsigned long long g = 0;
-        if (lane == 0) g = atomicAdd(ctr, 1ull);
+        if (lane == 0) g = atomicAdd(hlist ? ctr + 5 : ctr, 1ull);
         g = __shfl_sync(FULL, g, 0);
-        if ((int64_t)g >= n_groups) break;
-        const int64_t h = heads[g];
+        // deferred mode: the list of group heads k_gapped_half could not finish, its length in ctr[4]
+        if ((int64_t)g >= (hlist ? (int64_t)ctr[4] : n_groups)) break;
+        const int64_t h = hlist ? hlist[g] : heads[g];
         int64_t e = h + 1;
         const uint64_t key = keys[h];
         while (e < n && keys[e] == key) e++;

@@ -9,6 +9,7 @@
 
 #include "seed_kernels.cuh"
 #include "gapped_kernels.cuh"
+#include "gapped_half.cuh"
 #include "select_kernels.cuh"
 
 struct GappedValid {
@@ -223,23 +224,31 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
         CU(cudaMemsetAsync(G, 0xFF, n_slots * sizeof(Gapped), ctx->stream));
         const int threads = 128;
         const bool masked = s1->n_masked || s2->n_masked;
-        int* occ = ctx->gapped_occ;   // resident blocks per SM of the two variants (per context: contexts run on their own threads)
+        int* occ = ctx->gapped_occ;   // resident blocks per SM: [0] k_gapped_half, [1] k_gapped<true> (per context: contexts run on their own threads)
         if (!occ[masked]) {
             int nb = 0;
             if (masked) CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_gapped<true>, threads, 0));
-            else CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_gapped<false>, threads, 0));
+            else CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_gapped_half, GH_THREADS, 0));
             occ[masked] = nb > 0 ? nb : 1;
             if (const char* e = getenv("RCQ_GAPPED_BPS")) occ[masked] = std::max(1, std::min(occ[masked], atoi(e)));
         }
-        const int blocks = RCQ_SMS * occ[masked];   // persistent warps, groups handed out by an atomic counter
+        const int blocks = RCQ_SMS * occ[masked];   // persistent (half-)warps, groups handed out by an atomic counter
         ScratchPool sp;
         RC(scratch_pool(ctx, 6ll * ((int64_t)s1->max_len + s2->max_len + 8), &sp));
         CU(cudaMemsetAsync(ctr, 0, 16 * sizeof(int64_t), ctx->stream));
         stage_tic(ctx, 4);
-        if (masked)
-            LAUNCH(ctx, k_gapped<true>, blocks, threads, 0, U, keys, n_hsp, F, heads, n_groups, P, G, sp, ctr);
-        else
-            LAUNCH(ctx, k_gapped<false>, blocks, threads, 0, U, keys, n_hsp, F, heads, n_groups, P, G, sp, ctr);
+        if (masked) {
+            // samples with N bases: the general path (mask words consulted in every comparison)
+            LAUNCH(ctx, k_gapped<true>, blocks, threads, 0, U, keys, n_hsp, F, heads, n_groups, P, G, sp, ctr, (const uint32_t*)nullptr);
+        } else {
+            // half-warp engines on register rows; groups whose band outgrows the 48-diagonal window (or whose
+            // transcripts exceed the staged length) are listed and finished by the wide kernel on global rows
+            uint32_t* deferred = nullptr;
+            RC(talloc(ctx, &deferred, n_groups));
+            LAUNCH(ctx, k_gapped_half, blocks, GH_THREADS, 0, U, keys, n_hsp, F, heads, n_groups, P, G, deferred, ctr);
+            LAUNCH(ctx, k_gapped<false>, RCQ_SMS, threads, 0, U, keys, n_hsp, F, heads, n_groups, P, G, sp, ctr, (const uint32_t*)deferred);
+            tfree(ctx, deferred);
+        }
         stage_toc(ctx, 4);
         tfree(ctx, U); tfree(ctx, keys); tfree(ctx, heads);
         // ---- compact (stable: group order, then processing order inside the group)
