@@ -54,6 +54,8 @@ def lib():
         L.orc_bitscore.restype = C.c_double
         L.orc_bitscore.argtypes = [C.c_int32]
         L.orc_set_gapped_mode.argtypes = [C.c_int]
+        L.orc_max_band.restype = C.c_int32
+        L.orc_max_band.argtypes = [C.c_int]
         L.orc_extend.argtypes = [C.c_char_p, C.c_int32, C.c_char_p, C.c_int32, C.c_int, C.c_void_p]
         _lib = L
     return _lib
@@ -121,6 +123,11 @@ def match_table_from_rows(fwd: np.ndarray, bwd: np.ndarray, top_n: int = 1, keep
     lib().orc_result_counts(r.h, c.ctypes.data)
     r.counts = dict(zip(["gapped", "fwd", "bwd", "rows", "seeds", "ungapped", "dp_cells"], c.tolist()))
     return r
+
+
+def max_band(reset: bool = True) -> int:
+    """Widest wave (in diagonals) any greedy extension has had since the last reset."""
+    return int(lib().orc_max_band(int(reset)))
 
 
 def set_dust(on: bool) -> None:

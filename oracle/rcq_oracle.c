@@ -327,6 +327,8 @@ int64_t orc_dp_cells(void) { return g_dp_cells; }
  * counts travel with every (d, k) point: a gap character opens a new gap unless the point it
  * comes from was entered by the same kind of gap and slid over no match. */
 static int64_t g_greedy_steps = 0;
+static int32_t g_max_band = 0;   /* widest wave (diagonals klo .. khi) of any extension so far: test hook */
+int32_t orc_max_band(int reset) { int32_t b = g_max_band; if (reset) g_max_band = 0; return b; }
 static ext_t greedy_extend(const uint8_t* q, int32_t qn, int qstep, const uint8_t* s, int32_t sn,
                            int sstep) {
     int32_t nd = qn + sn + 3;
@@ -351,6 +353,7 @@ static ext_t greedy_extend(const uint8_t* q, int32_t qn, int qstep, const uint8_
         int32_t tref = d >= 19 ? T[d - 19] : 0;
         int32_t nL = 1, nU = 0, wbest = NEG, ubmax = NEG;
         int32_t klo = L - 1 < -qn ? -qn : L - 1, khi = U + 1 > sn ? sn : U + 1;
+        if (khi - klo + 1 > g_max_band) g_max_band = khi - klo + 1;
         for (int32_t k = klo; k <= khi; k++) {
             int32_t bi = -1, mm = 0, gp = 0, go = 0; uint8_t op = 0;
             if (k >= L && k <= U && R[p][IX(k)] >= 0) {

@@ -71,18 +71,22 @@ __global__ void __launch_bounds__(GH_THREADS, 4) k_gapped_half(
     unsigned long long* __restrict__ ctr /* [0]=next group [1]=cells [2]=retries [3]=n gapped [4]=#deferred groups */) {
     __shared__ uint32_t stage_all[GH_THREADS / 16][4 * RCQ_STAGE_W];
     const int lane = threadIdx.x & 31, half = lane >> 4, j = lane & 15;
-    const unsigned hmask = 0xFFFFu << (16 * half);
+    const int hs = 16 * half;                       // shift of this half's bits in a ballot
     uint32_t* stage = stage_all[threadIdx.x >> 4];
     const uint32_t* stAf = stage;
     const uint32_t* stAr = stage + RCQ_STAGE_W;
     const uint32_t* stBs = stage + 2 * RCQ_STAGE_W;
     const uint32_t* stBo = stage + 3 * RCQ_STAGE_W;
 
+    // Every warp-wide primitive below runs with the FULL mask at a point all 32 lanes reach together (branches
+    // around them test ballot results, which are uniform): the two halves must never split into two sub-warps,
+    // or each would pay for the whole instruction stream.  A half that has nothing to do in a block takes part
+    // with its predicate off.
     int st = GH_FETCH;
     // group
     int64_t h = 0, e_ = 0;
     int32_t gsize = 0, ta = 0, tb = 0, minus = 0, la = 0, lb = 0, count = 0, it = 0;
-    Ungapped last; last.score = 0; last.diag = 0; last.a0 = 0; last.a1 = 0;
+    Ungapped last; last.score = 0; last.diag = 0; last.a0 = 0; last.a1 = 0; last.i0 = 0; last.ta = last.tb = last.minus = 0;
     bool have_last = false, group_open = false;
     // current HSP / extension
     int32_t i0 = 0, j0 = 0, phase = 0;
@@ -98,112 +102,82 @@ __global__ void __launch_bounds__(GH_THREADS, 4) k_gapped_half(
     uint32_t nstep = 0;                     // extension steps of the open group (this lane's share)
     unsigned long long cells = 0, produced = 0, n_deferred = 0;
 
-    // start an extension: wave 0 and the register rows.  Called per half (divergent).
-    auto begin_ext = [&](const uint32_t* Qw, int32_t qrel, int32_t qn, const uint32_t* Sw, int32_t srel, int32_t sn) {
-        X.Q = Qw + (qrel >> 4); X.qo = qrel & 15; X.qn = qn;
-        X.S = Sw + (srel >> 4); X.so = srel & 15; X.sn = sn;
-        // wave 0: slide along diagonal 0 (half-warp only: the other half is elsewhere)
-        int32_t lim = min(qn, sn), base = 0, first = lim;
-        {
-            SeqShared q, s;
-            q.b = X.Q; s.b = X.S;
-            bool done = lim <= 0;
-            while (!done) {
-                const int32_t o = base + 16 * j;
-                int32_t z = 0;
-                if (o < lim) z = min(run16(q, X.qo + o, s, X.so + o), lim - o);
-                const unsigned stop = (__ballot_sync(hmask, z < 16) >> (16 * half)) & 0xFFFFu;
-                if (stop) {
-                    const int src = __ffs(stop) - 1;
-                    first = base + 16 * src + __shfl_sync(hmask, z, src, 16);
-                    done = true;
-                } else {
-                    base += 256;
-                    if (base >= lim) { first = lim; done = true; }
-                }
-            }
-        }
-        if (j == 0) nstep += (uint32_t)(first + 1);
-        kb = GH_KB0;
-        R0 = R1 = R2 = NEG; M0 = M1 = M2 = 0; G0 = G1 = G2 = 0;
-        const bool mine = (0 - GH_KB0) / GH_CELLS == j;     // diagonal 0 = cell (0 - kb) % 3 of lane (0 - kb) / 3
-        if (mine) {
-            if ((0 - GH_KB0) % GH_CELLS == 0) R0 = first;
-            else if ((0 - GH_KB0) % GH_CELLS == 1) R1 = first;
-            else R2 = first;
-        }
-        bS = mine ? 2 * first : NEG; bD = 0; bK = 0; bM = 0; bG = 0;
-        gb = 2 * first; Tprev = gb;
-        T0 = (j == 0) ? gb : 0; T1 = 0;
-        Lk = 0; Uk = 0; d = 0;
-        overflow = false;
-        st = (qn + sn >= 1) ? GH_RUN : GH_FIN;
-    };
-
     while (true) {
-        if (st != GH_RUN) {
-            // ------------------------------------------------------------------ per half-warp (divergent)
-            while (st != GH_RUN && st != GH_DONE) {
-                if (st == GH_FIN) {
-                    if (overflow) {
-                        // the band outgrew the window: the whole group goes to the wide kernel
-                        if (j == 0) deferred[atomicAdd(ctr + 4, 1ull)] = (uint32_t)(h);     // group = head index of its HSP range
-                        n_deferred++;
-                        group_open = false;
-                        nstep = 0;
-                        st = GH_FETCH;
-                        continue;
+        // ------------------------------------------------------------------ set-up passes (both halves together)
+        while (__any_sync(FULL, st != GH_RUN && st != GH_DONE)) {
+            bool begin = false;                       // this half starts an extension at the end of the pass
+            const uint32_t* bQ = stage; const uint32_t* bS_ = stage;
+            int32_t bqrel = 0, bqn = 0, bsrel = 0, bsn = 0;
+            // ---- (1) an extension has ended
+            if (__any_sync(FULL, st == GH_FIN)) {
+                bool p = st == GH_FIN;
+                if (p && overflow) {
+                    // the band outgrew the window: the whole group goes to the wide kernel
+                    if (j == 0) deferred[atomicAdd(ctr + 4, 1ull)] = (uint32_t)h;
+                    n_deferred++;
+                    group_open = false; nstep = 0; overflow = false;
+                    st = GH_FETCH; p = false;
+                }
+                // best end point of the extension: score desc, then d asc, then k asc
+                uint64_t key = 0;
+                if (p && bS > NEG)
+                    key = ((uint64_t)(uint32_t)(bS + (1 << 20)) << 42) | ((uint64_t)((1 << 21) - 1 - bD) << 21) |
+                          (uint64_t)((1 << 21) - 1 - (bK + (1 << 20)));
+                uint64_t best = key;
+#pragma unroll
+                for (int o = 8; o; o >>= 1) { const uint64_t x = __shfl_xor_sync(FULL, best, o, 16); if (x > best) best = x; }
+                const unsigned who = (__ballot_sync(FULL, key == best) >> hs) & 0xFFFFu;
+                const int src = who ? __ffs(who) - 1 : 0;
+                const int32_t rS = __shfl_sync(FULL, bS, src, 16), rD = __shfl_sync(FULL, bD, src, 16),
+                              rK = __shfl_sync(FULL, bK, src, 16), rM = __shfl_sync(FULL, bM, src, 16),
+                              rG = __shfl_sync(FULL, bG, src, 16);
+                const int32_t rI = (rS - rK + 6 * rD) >> 1;          // score = 2 row + k - 6 d
+                bool dup = false;
+                Gapped gp;
+                gp.ta = ta; gp.tb = tb; gp.minus = minus;
+                gp.a0 = i0 + 1 - Lqi; gp.a1 = i0 + 1 + rI;
+                gp.b0 = j0 + 1 - Lsj; gp.b1 = j0 + 1 + rI + rK;
+                gp.score2 = Lscore2 + rS;
+                gp.mism = Lmism + rM;
+                gp.gaps = (Lgw >> 17) + (rG >> 17);
+                gp.gapopen = ((Lgw >> 3) & 0x3fff) + ((rG >> 3) & 0x3fff);
+                gp.nident = ((gp.a1 - gp.a0) + (gp.b1 - gp.b0) - gp.gaps) / 2 - gp.mism;
+                const bool fin_r = p && phase == 1;
+                if (fin_r) {
+                    for (int32_t c0 = j; c0 < count; c0 += 16) {
+                        const Gapped o2 = out[h + c0];
+                        dup = dup || (o2.a0 == gp.a0 && o2.a1 == gp.a1 && o2.b0 == gp.b0 && o2.b1 == gp.b1);
                     }
-                    // best end point of the extension: score desc, then d asc, then k asc
-                    uint64_t key = 0;
-                    if (bS > NEG)
-                        key = ((uint64_t)(uint32_t)(bS + (1 << 20)) << 42) | ((uint64_t)((1 << 21) - 1 - bD) << 21) |
-                              (uint64_t)((1 << 21) - 1 - (bK + (1 << 20)));
-                    uint64_t best = key;
-                    for (int o = 8; o; o >>= 1) { const uint64_t x = __shfl_xor_sync(hmask, best, o, 16); if (x > best) best = x; }
-                    const unsigned who = (__ballot_sync(hmask, key == best) >> (16 * half)) & 0xFFFFu;
-                    const int src = __ffs(who) - 1;
-                    const int32_t rS = __shfl_sync(hmask, bS, src, 16), rD = __shfl_sync(hmask, bD, src, 16),
-                                  rK = __shfl_sync(hmask, bK, src, 16), rM = __shfl_sync(hmask, bM, src, 16),
-                                  rG = __shfl_sync(hmask, bG, src, 16);
-                    const int32_t rI = (rS - rK + 6 * rD) >> 1;          // score = 2 row + k - 6 d
-                    if (phase == 0) {
-                        Lscore2 = rS; Lqi = rI; Lsj = rI + rK; Lmism = rM; Lgw = rG;
-                        phase = 1;
-                        begin_ext(stAf, i0 + 1, la - i0 - 1, stBs, j0 + 1, lb - j0 - 1);
-                    } else {
-                        Gapped gp;
-                        gp.ta = ta; gp.tb = tb; gp.minus = minus;
-                        gp.a0 = i0 + 1 - Lqi; gp.a1 = i0 + 1 + rI;
-                        gp.b0 = j0 + 1 - Lsj; gp.b1 = j0 + 1 + rI + rK;
-                        gp.score2 = Lscore2 + rS;
-                        gp.mism = Lmism + rM;
-                        gp.gaps = (Lgw >> 17) + (rG >> 17);
-                        gp.gapopen = ((Lgw >> 3) & 0x3fff) + ((rG >> 3) & 0x3fff);
-                        gp.nident = ((gp.a1 - gp.a0) + (gp.b1 - gp.b0) - gp.gaps) / 2 - gp.mism;
-                        bool dup = false;
-                        for (int32_t c0 = j; c0 < count; c0 += 16) {
-                            const Gapped o2 = out[h + c0];
-                            dup = dup || (o2.a0 == gp.a0 && o2.a1 == gp.a1 && o2.b0 == gp.b0 && o2.b1 == gp.b1);
-                        }
-                        if (!__any_sync(hmask, dup)) {
-                            if (j == 0) out[h + count] = gp;
-                            __syncwarp(hmask);
-                            count++;
-                        }
-                        st = GH_NEXT;
+                }
+                const bool any_dup = (__ballot_sync(FULL, dup) >> hs) & 0xFFFFu;
+                if (fin_r) {
+                    if (!any_dup) {
+                        if (j == 0) out[h + count] = gp;
+                        count++;
                     }
-                } else if (st == GH_FETCH) {
-                    if (group_open) {          // the finished group's work counts; a deferred one was dropped above
-                        cells += nstep;
-                        produced += (j == 0) ? (unsigned long long)count : 0ull;
-                        nstep = 0;
-                        group_open = false;
-                    }
-                    unsigned long long g = 0;
-                    if (j == 0) g = atomicAdd(ctr, 1ull);
-                    g = __shfl_sync(hmask, g, 0, 16);
-                    if ((int64_t)g >= n_groups) { st = GH_DONE; break; }
+                    st = GH_NEXT;
+                } else if (p) {           // the left part is done: keep it, start the right part
+                    Lscore2 = rS; Lqi = rI; Lsj = rI + rK; Lmism = rM; Lgw = rG;
+                    phase = 1;
+                    begin = true;
+                    bQ = stAf; bqrel = i0 + 1; bqn = la - i0 - 1; bS_ = stBs; bsrel = j0 + 1; bsn = lb - j0 - 1;
+                }
+                __syncwarp();             // out[] written by lane 0 of a half is read by its other lanes below
+            }
+            // ---- (2) take the next group and stage its four strands
+            if (__any_sync(FULL, st == GH_FETCH)) {
+                bool p = st == GH_FETCH;
+                if (p && group_open) {        // the finished group's work counts; a deferred one was dropped above
+                    cells += nstep;
+                    produced += (j == 0) ? (unsigned long long)count : 0ull;
+                    nstep = 0;
+                    group_open = false;
+                }
+                unsigned long long g = 0;
+                if (p && j == 0) g = atomicAdd(ctr, 1ull);
+                g = __shfl_sync(FULL, g, 0, 16);
+                if (p && (int64_t)g >= n_groups) { st = GH_DONE; p = false; }
+                if (p) {
                     h = heads[g];
                     e_ = h + 1;
                     const uint64_t key = keys[h];
@@ -212,61 +186,97 @@ __global__ void __launch_bounds__(GH_THREADS, 4) k_gapped_half(
                     ta = (int32_t)(key >> (F.tb_bits + 1));
                     tb = (int32_t)((key >> 1) & ((1u << F.tb_bits) - 1u));
                     minus = (int32_t)(key & 1);
-                    const int64_t oa = __ldg(P.offA + ta), ob = __ldg(P.offB + tb);
                     la = __ldg(P.lenA + ta); lb = __ldg(P.lenB + tb);
                     if (la > RCQ_STAGE_MAX || lb > RCQ_STAGE_MAX) {
                         if (j == 0) deferred[atomicAdd(ctr + 4, 1ull)] = (uint32_t)h;
                         n_deferred++;
-                        continue;
+                        p = false;            // stays in GH_FETCH: next pass takes another group
                     }
+                }
+                if (p) {
+                    const int64_t oa = __ldg(P.offA + ta), ob = __ldg(P.offB + tb);
                     const SeqArena Bs = minus ? P.Br : P.Bf, Bo = minus ? P.Bf : P.Br;
                     const int32_t wa = (la + 15) / 16 + 2, wb = (lb + 15) / 16 + 2;
                     const uint32_t* ga = P.Af.bits + (oa >> 4); const uint32_t* gr = P.Ar.bits + (oa >> 4);
                     const uint32_t* gs = Bs.bits + (ob >> 4); const uint32_t* go = Bo.bits + (ob >> 4);
-                    __syncwarp(hmask);
                     for (int32_t w = j; w < wa; w += 16) { stage[w] = __ldg(ga + w); stage[RCQ_STAGE_W + w] = __ldg(gr + w); }
                     for (int32_t w = j; w < wb; w += 16) { stage[2 * RCQ_STAGE_W + w] = __ldg(gs + w); stage[3 * RCQ_STAGE_W + w] = __ldg(go + w); }
-                    __syncwarp(hmask);
                     count = 0; it = 0; have_last = false; group_open = true;
                     st = GH_NEXT;
-                } else {   // GH_NEXT: the next ungapped HSP strictly after `last` in canonical order
-                    if (it >= gsize || count >= RCQ_MAX_GAPPED_PER_GROUP) { st = GH_FETCH; continue; }
-                    it++;
-                    Ungapped bestu; bool found = false;
-                    bestu.score = 0; bestu.diag = 0; bestu.a0 = 0; bestu.a1 = 0; bestu.i0 = 0;
+                }
+                __syncwarp();             // the staged words are read by the other lanes of the half
+            }
+            // ---- (3) the next ungapped HSP of the group, strictly after `last` in canonical order
+            if (__any_sync(FULL, st == GH_NEXT)) {
+                bool p = st == GH_NEXT;
+                if (p && (it >= gsize || count >= RCQ_MAX_GAPPED_PER_GROUP)) { st = GH_FETCH; p = false; }
+                if (p) it++;
+                Ungapped bestu; bool found = false;
+                bestu.score = 0; bestu.diag = 0; bestu.a0 = 0; bestu.a1 = 0; bestu.i0 = 0;
+                if (p) {
                     for (int64_t x = h + j; x < e_; x += 16) {
                         const Ungapped u = U[x];
                         if (u.score < 0) continue;
                         if (have_last && !ung_before(last, u)) continue;
                         if (!found || ung_before(u, bestu)) { bestu = u; found = true; }
                     }
-                    for (int o = 8; o; o >>= 1) {
-                        Ungapped v;
-                        v.score = __shfl_xor_sync(hmask, bestu.score, o, 16); v.diag = __shfl_xor_sync(hmask, bestu.diag, o, 16);
-                        v.a0 = __shfl_xor_sync(hmask, bestu.a0, o, 16); v.a1 = __shfl_xor_sync(hmask, bestu.a1, o, 16);
-                        v.i0 = __shfl_xor_sync(hmask, bestu.i0, o, 16);
-                        const bool f2 = __shfl_xor_sync(hmask, (int)found, o, 16);
-                        if (f2 && (!found || ung_before(v, bestu))) {
-                            bestu.score = v.score; bestu.diag = v.diag; bestu.a0 = v.a0; bestu.a1 = v.a1; bestu.i0 = v.i0; found = true;
-                        }
+                }
+#pragma unroll
+                for (int o = 8; o; o >>= 1) {
+                    Ungapped v;
+                    v.score = __shfl_xor_sync(FULL, bestu.score, o, 16); v.diag = __shfl_xor_sync(FULL, bestu.diag, o, 16);
+                    v.a0 = __shfl_xor_sync(FULL, bestu.a0, o, 16); v.a1 = __shfl_xor_sync(FULL, bestu.a1, o, 16);
+                    v.i0 = __shfl_xor_sync(FULL, bestu.i0, o, 16);
+                    const bool f2 = __shfl_xor_sync(FULL, (int)found, o, 16);
+                    if (f2 && (!found || ung_before(v, bestu))) {
+                        bestu.score = v.score; bestu.diag = v.diag; bestu.a0 = v.a0; bestu.a1 = v.a1; bestu.i0 = v.i0; found = true;
                     }
-                    if (!found) { st = GH_FETCH; continue; }
+                }
+                if (p && !found) { st = GH_FETCH; p = false; }
+                bool contained = false;
+                if (p) {
                     last = bestu; have_last = true;
                     const int32_t ub0 = bestu.a0 + bestu.diag, ub1 = bestu.a1 + bestu.diag;
-                    bool contained = false;
                     for (int32_t c0 = j; c0 < count; c0 += 16) {
-                        const Gapped gp = out[h + c0];
-                        contained = contained || (gp.a0 <= bestu.a0 && bestu.a1 <= gp.a1 && gp.b0 <= ub0 && ub1 <= gp.b1);
+                        const Gapped gq = out[h + c0];
+                        contained = contained || (gq.a0 <= bestu.a0 && bestu.a1 <= gq.a1 && gq.b0 <= ub0 && ub1 <= gq.b1);
                     }
-                    if (__any_sync(hmask, contained)) continue;
+                }
+                const bool any_contained = (__ballot_sync(FULL, contained) >> hs) & 0xFFFFu;
+                if (p && !any_contained) {
                     i0 = bestu.i0; j0 = i0 + bestu.diag;
                     phase = 0;
                     // left part: the anchor pair first, walking backwards = forwards on the opposite strands
-                    begin_ext(stAr, la - 1 - i0, i0 + 1, stBo, lb - 1 - j0, j0 + 1);
+                    begin = true;
+                    bQ = stAr; bqrel = la - 1 - i0; bqn = i0 + 1; bS_ = stBo; bsrel = lb - 1 - j0; bsn = j0 + 1;
+                }
+            }
+            // ---- (4) start the extensions asked for above: wave 0 and the register rows
+            if (__any_sync(FULL, begin)) {
+                if (begin) {
+                    X.Q = bQ + (bqrel >> 4); X.qo = bqrel & 15; X.qn = bqn;
+                    X.S = bS_ + (bsrel >> 4); X.so = bsrel & 15; X.sn = bsn;
+                }
+                const int32_t first = gh_coop_slide(X.Q, X.qo, X.S, X.so, begin ? min(X.qn, X.sn) : 0, j, half);
+                if (begin) {
+                    if (j == 0) nstep += (uint32_t)(first + 1);
+                    kb = GH_KB0;
+                    R0 = R1 = R2 = NEG; M0 = M1 = M2 = 0; G0 = G1 = G2 = 0;
+                    const bool mine = (0 - GH_KB0) / GH_CELLS == j;     // diagonal 0 = cell (0 - kb) % 3 of lane (0 - kb) / 3
+                    if (mine) {
+                        if ((0 - GH_KB0) % GH_CELLS == 0) R0 = first;
+                        else if ((0 - GH_KB0) % GH_CELLS == 1) R1 = first;
+                        else R2 = first;
+                    }
+                    bS = mine ? 2 * first : NEG; bD = 0; bK = 0; bM = 0; bG = 0;
+                    gb = 2 * first; Tprev = gb;
+                    T0 = (j == 0) ? gb : 0; T1 = 0;
+                    Lk = 0; Uk = 0; d = 0;
+                    overflow = false;
+                    st = (X.qn + X.sn >= 1) ? GH_RUN : GH_FIN;
                 }
             }
         }
-        __syncwarp();
         if (__all_sync(FULL, st == GH_DONE)) break;
 
         // ---------------------------------------------------------------------- one wave, both halves
@@ -276,10 +286,8 @@ __global__ void __launch_bounds__(GH_THREADS, 4) k_gapped_half(
         int32_t tref;
         {
             const int32_t slot = (d - RCQ_XDROP_OFFSET) & 31;
-            const int32_t mine = (slot & 16) ? T1 : T0;
             // lane (slot & 15) of each half holds the entry; the register is chosen on the receiving side
             const int32_t a0v = __shfl_sync(FULL, T0, slot & 15, 16), a1v = __shfl_sync(FULL, T1, slot & 15, 16);
-            (void)mine;
             tref = (slot & 16) ? a1v : a0v;
             if (d < RCQ_XDROP_OFFSET) tref = 0;
         }
@@ -295,7 +303,7 @@ __global__ void __launch_bounds__(GH_THREADS, 4) k_gapped_half(
                         overflow = true; st = GH_FIN; act = false;
                     } else {
                         const int32_t want = klo - (GH_WIN - width) / 2;     // ideal window start
-                        int32_t diff = want - kb;
+                        const int32_t diff = want - kb;
                         sh = diff >= 0 ? diff / GH_CELLS : -((-diff + GH_CELLS - 1) / GH_CELLS);
                         kb += GH_CELLS * sh;
                     }
@@ -333,7 +341,7 @@ __global__ void __launch_bounds__(GH_THREADS, 4) k_gapped_half(
             const int32_t right = c == 0 ? R1 : (c == 1 ? R2 : Rr);
             const int32_t rowmax = min(qn, sn - k);
             // candidates with their tie rank in the low bits: mismatch (rank 2), query gap (1), subject gap (0)
-            int32_t m4 = __vimax3_s32(mid * 4 + 6, right * 4 + 5, left * 4);
+            const int32_t m4 = __vimax3_s32(mid * 4 + 6, right * 4 + 5, left * 4);
             int32_t bi = m4 >> 2, t = m4 & 3;
             if (bi > rowmax) {
                 // an end of a sequence is in reach: candidates past it are invalid one by one
@@ -348,18 +356,17 @@ __global__ void __launch_bounds__(GH_THREADS, 4) k_gapped_half(
             const bool ok = act && bi >= 0 && 2 * bi + k >= xcut;
             const uint32_t sm = t == 2 ? (c == 0 ? M0 : (c == 1 ? M1 : M2)) : (t == 1 ? (c == 0 ? M1 : (c == 1 ? M2 : Mr)) : (c == 0 ? Ml : (c == 1 ? M0 : M1)));
             const uint32_t sg = t == 2 ? (c == 0 ? G0 : (c == 1 ? G1 : G2)) : (t == 1 ? (c == 0 ? G1 : (c == 1 ? G2 : Gr)) : (c == 0 ? Gl : (c == 1 ? G0 : G1)));
-            uint32_t mm = sm, gw;
-            if (t == 2) { mm++; gw = sg & ~7u; }
-            else {
-                const uint32_t op = t == 1 ? 1u : 2u;
-                gw = ((sg & ~7u) | op) + (1u << 17) + (((sg & 7u) != op) ? 8u : 0u);
-            }
+            const uint32_t op = 2u - (uint32_t)t;                 // 0 mismatch, 1 query gap, 2 subject gap
+            const uint32_t gapw = ((sg & ~7u) | op) + (1u << 17) + (((sg & 7u) != op) ? 8u : 0u);
+            nM[c] = sm + (t == 2 ? 1u : 0u);
+            nG[c] = t == 2 ? (sg & ~7u) : gapw;
             const int32_t lim = rowmax - bi;
-            int32_t z = 0;
-            if (ok && lim > 0) z = min(run16(Qs, X.qo + bi, Ss, X.so + bi + k), lim);
-            if (ok) nstep += (uint32_t)(z + 1);
+            // dead lanes compare the first words of the strands (in bounds) and drop the result
+            const int32_t r16 = run16(Qs, ok ? X.qo + bi : 0, Ss, ok ? X.so + bi + k : 0);
+            const int32_t z = (ok && lim > 0) ? min(r16, lim) : 0;
+            nstep += ok ? (uint32_t)(z + 1) : 0u;
             alive[c] = ok; bi_[c] = bi; lim_[c] = lim;
-            nR[c] = bi + z; nM[c] = mm; nG[c] = gw;
+            nR[c] = bi + z;
             cont[c] = ok && z == 16 && lim > 16;
         }
         // slides that survived their first 16 bases are finished by the half-warp together
@@ -367,32 +374,28 @@ __global__ void __launch_bounds__(GH_THREADS, 4) k_gapped_half(
         for (int c = 0; c < GH_CELLS; c++) {
             unsigned more = __ballot_sync(FULL, cont[c]);
             while (more) {
-                const unsigned mh = (more >> (16 * half)) & 0xFFFFu;
+                const unsigned mh = (more >> hs) & 0xFFFFu;
                 const int sl = mh ? __ffs(mh) - 1 : 0;
-                more &= ~((mh ? (1u << sl) : 0u) << (16 * half));
                 const int32_t e2 = __shfl_sync(FULL, nR[c], sl, 16), l2 = __shfl_sync(FULL, lim_[c], sl, 16);
                 const int32_t k2 = kb + GH_CELLS * sl + c;
                 const int32_t extra = gh_coop_slide(X.Q, X.qo + e2, X.S, X.so + e2 + k2, mh ? l2 - 16 : 0, j, half);
-                if (mh && j == sl) { nR[c] += extra; nstep += (uint32_t)extra; }
-                // the other half's bits are cleared by its own lanes: rebuild the common mask
-                more = __ballot_sync(FULL, (more >> lane) & 1u);
+                if (mh && j == sl) { nR[c] += extra; nstep += (uint32_t)extra; cont[c] = false; }
+                more = __ballot_sync(FULL, cont[c]);
             }
         }
         int32_t wbest = NEG, ubmax = NEG, nL = 1 << 28, nU = -(1 << 28);
 #pragma unroll
         for (int c = 0; c < GH_CELLS; c++) {
             const int32_t k = k0 + c;
-            if (alive[c]) {
-                const int32_t e = nR[c];
-                if (e > bi_[c]) nG[c] |= 4u;
-                const int32_t sc = 2 * e + k - d6;
-                wbest = max(wbest, sc);
-                nL = min(nL, k); nU = max(nU, k);
-                ubmax = max(ubmax, 2 * min(qn, sn - k) + k - d6);
-                if (sc > bS) { bS = sc; bD = d; bK = k; bM = (int32_t)nM[c]; bG = (int32_t)nG[c]; }
-            } else {
-                nR[c] = NEG;
-            }
+            const bool ok = alive[c];
+            const int32_t e = nR[c];
+            if (ok && e > bi_[c]) nG[c] |= 4u;
+            const int32_t sc = ok ? 2 * e + k - d6 : NEG;
+            wbest = max(wbest, sc);
+            nL = min(nL, ok ? k : (1 << 28)); nU = max(nU, ok ? k : -(1 << 28));
+            ubmax = max(ubmax, ok ? 2 * min(qn, sn - k) + k - d6 : NEG);
+            if (sc > bS) { bS = sc; bD = d; bK = k; bM = (int32_t)nM[c]; bG = (int32_t)nG[c]; }
+            if (!ok) nR[c] = NEG;
         }
         if (act) {
             R0 = nR[0]; R1 = nR[1]; R2 = nR[2];

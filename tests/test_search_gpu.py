@@ -149,10 +149,11 @@ def test_sample_export_import_round_trip(ctx):
 
 
 @pytest.mark.parametrize("length", [4000, 6500])
-def test_drifting_band_uses_the_wide_fallback(ctx, length):
+def test_drifting_band(ctx, length):
     """One base of every 29 deleted in sample 2: exact blocks of 28 (just enough to seed) and a band that
-    drifts one diagonal per block, far beyond the 124-diagonal shared-memory rows — the extension
-    re-runs on the pooled global rows (staged strands for 4000-base transcripts, arena reads for 6500)."""
+    drifts one diagonal per block, more than a hundred diagonals in all.  The half-warp kernel re-centres its
+    48-diagonal register window as the band moves (4000-base transcripts); 6500-base transcripts are longer than
+    the staged limit and go to the wide kernel on global rows."""
     from rna_clique_b200 import _native
     from oracle import oracle as O
     rng = np.random.default_rng(length)
@@ -170,12 +171,50 @@ def test_drifting_band_uses_the_wide_fallback(ctx, length):
     o = _oracle_samples(raw)
     tab = _native.search_pair(ctx, g[0], g[1])
     res = O.search_pair(o[0], o[1])
-    assert tab.stats["band_retries"] > 0
+    if length > 4096:
+        assert tab.stats["band_retries"] >= n          # every group deferred: transcripts beyond the staged length
+    else:
+        assert tab.stats["band_retries"] == 0 and tab.stats["dp_cells"] == res.counts["dp_cells"]
     assert np.array_equal(_native.debug_last_hsps(ctx), res.hsps())
     cols = tab.download()
     got = np.stack([cols[c] for c in _native.TABLE_COLS] + [cols["minus"].astype(np.int32), cols["reverse"].astype(np.int32)], axis=1)
     assert np.array_equal(got, res.rows(2)) and len(tab) == 2 * n
     assert (cols["gaps"] > 100).all()
+
+
+@pytest.mark.parametrize("unit,reps", [(11, 70), (7, 100), (17, 50)])
+def test_tandem_repeats_widen_the_band_beyond_the_register_window(ctx, unit, reps):
+    """Unique flanks around a tandem repeat with a few units missing in sample 2: inside the repeat every
+    diagonal a multiple of the unit away matches as well, the wave widens past 48 diagonals (the oracle reports
+    its widest wave) and the group is finished by the wide kernel; HSPs and table equal the oracle's."""
+    from rna_clique_b200 import _native
+    from oracle import oracle as O
+    rng = np.random.default_rng(4)
+    letters = np.frombuffer(b"ACGT", dtype=np.uint8)
+    s1, s2 = [], []
+    for _ in range(10):
+        u = rng.integers(0, 4, size=unit)
+        a = np.concatenate([rng.integers(0, 4, size=300), np.tile(u, reps), rng.integers(0, 4, size=300)])
+        b = a.copy()
+        hit = rng.random(len(b)) < 0.02
+        b[hit] = (b[hit] + rng.integers(1, 4, size=int(hit.sum()))) & 3
+        b = np.delete(b, np.arange(300 + unit * 10, 300 + unit * 13))
+        s1.append(a); s2.append(b)
+
+    def pack(ss):
+        offs = np.concatenate([[0], np.cumsum([len(x) for x in ss])]).astype(np.int64)
+        return letters[np.concatenate(ss)], offs, np.arange(len(ss), dtype=np.int32), np.ones(len(ss), dtype=np.int32)
+
+    raw = [pack(s1), pack(s2)]
+    g = _gpu_samples(ctx, raw)
+    o = _oracle_samples(raw)
+    O.max_band()
+    res = O.search_pair(o[0], o[1])
+    assert O.max_band() > 48
+    tab = _native.search_pair(ctx, g[0], g[1])
+    assert tab.stats["band_retries"] > 0
+    assert np.array_equal(_native.debug_last_hsps(ctx), res.hsps())
+    assert np.array_equal(_table_matrix(tab), res.rows(2)) and len(tab) >= 20
 
 
 def test_dust_mask_equals_the_oracle(ctx):
