@@ -321,8 +321,8 @@ int64_t orc_dp_cells(void) { return g_dp_cells; }
  *                ties: mismatch, then U, then L.  The entry is dropped when its score
  *                t - 6d < T(d - 19) - 108, T(x) = best score of waves <= x (0 for x < 0):
  *                19 = floor((108 + 1) / 6) + 1 is BLAST's xdrop_offset.  Then slide.
- *   stop       : when a wave has no valid diagonal, or when no valid diagonal of the wave could still
- *                beat the best end point even by matching to the end of q or s.
+ *   stop       : when a wave has no valid diagonal, or when no diagonal between its lowest and highest valid
+ *                one could still beat the best end point even by matching to the end of q or s.
  * Best end point: highest score; ties -> smaller d, then smaller k.  Mismatch / gap / gap-opening
  * counts travel with every (d, k) point: a gap character opens a new gap unless the point it
  * comes from was entered by the same kind of gap and slid over no match. */
@@ -351,7 +351,7 @@ static ext_t greedy_extend(const uint8_t* q, int32_t qn, int qstep, const uint8_
     for (int32_t d = 1; d <= qn + sn; d++) {
         const int p = (d - 1) & 1, c = d & 1;
         int32_t tref = d >= 19 ? T[d - 19] : 0;
-        int32_t nL = 1, nU = 0, wbest = NEG, ubmax = NEG;
+        int32_t nL = 1, nU = 0, wbest = NEG;
         int32_t klo = L - 1 < -qn ? -qn : L - 1, khi = U + 1 > sn ? sn : U + 1;
         if (khi - klo + 1 > g_max_band) g_max_band = khi - klo + 1;
         for (int32_t k = klo; k <= khi; k++) {
@@ -387,18 +387,21 @@ static ext_t greedy_extend(const uint8_t* q, int32_t qn, int qstep, const uint8_
             int32_t sc = 2 * e + k - 6 * d;
             if (sc > wbest) wbest = sc;
             if (sc > best.score2) { best.score2 = sc; best.qi = e; best.sj = e + k; best.mism = mm; best.gaps = gp; best.gapopen = go; }
-            /* the most this diagonal can still score: slide to the end of q or s with no further difference */
-            int32_t rowmax = qn < sn - k ? qn : sn - k;
-            if (2 * rowmax + k - 6 * d > ubmax) ubmax = 2 * rowmax + k - 6 * d;
         }
         if (d >= tcap) { tcap *= 2; T = realloc(T, sizeof(int32_t) * tcap); }
         T[d] = wbest > T[d - 1] ? wbest : T[d - 1];
         /* wave d-1's cells outside the new range must not be read as wave d+1's predecessors */
         L = nL; U = nU;
         if (L > U) break;
-        /* nothing alive can still beat the best end point (ties go to the smaller d): the result is final.
-         * Saves the waves that only run down the X-drop after a full-length alignment has ended. */
-        if (ubmax <= best.score2) break;
+        /* no diagonal of the band L .. U can still beat the best end point (ties go to the smaller d), even by
+         * sliding to the end of q or s without a further difference: 2 min(qn, sn - k) + k - 6 d peaks at
+         * k = sn - qn.  The result is final; this saves the waves that only run down the X-drop after a
+         * full-length alignment has ended. */
+        {
+            int32_t kp = sn - qn < L ? L : (sn - qn > U ? U : sn - qn);
+            int32_t rowmax = qn < sn - kp ? qn : sn - kp;
+            if (2 * rowmax + kp - 6 * d <= best.score2) break;
+        }
     }
 #undef IX
 #undef QB

@@ -26,9 +26,6 @@
 #pragma once
 #include "gapped_kernels.cuh"
 
-#define GH_CELLS 3                     // adjacent diagonals per lane
-#define GH_WIN (16 * GH_CELLS)         // diagonals per half-warp window
-#define GH_KB0 (-(GH_WIN / 2))         // window start of a new extension: diagonal 0 in the middle
 #define GH_THREADS 128
 
 enum { GH_FETCH = 0, GH_NEXT = 1, GH_RUN = 2, GH_FIN = 3, GH_DONE = 4 };
@@ -64,11 +61,19 @@ struct GhExt {            // one extension of a half-warp (uniform over its 16 l
     int32_t qn, sn;
 };
 
+// CELLS adjacent diagonals per lane: 3 (48-diagonal window) for the first pass over all groups, 4 (64) for the
+// groups the first pass gave up on; what outgrows that too goes to k_gapped.  Groups come from `heads` (in_list
+// == NULL) or from a list of group heads written by an earlier pass; groups given up are appended to out_list.
+template <int CELLS>
 __global__ void __launch_bounds__(GH_THREADS, 4) k_gapped_half(
     const Ungapped* __restrict__ U, const uint64_t* __restrict__ keys, int64_t n, KeyFmt F,
     const uint32_t* __restrict__ heads, int64_t n_groups, PairView P, Gapped* __restrict__ out,
-    uint32_t* __restrict__ deferred,
-    unsigned long long* __restrict__ ctr /* [0]=next group [1]=cells [2]=retries [3]=n gapped [4]=#deferred groups */) {
+    const uint32_t* __restrict__ in_list, const unsigned long long* __restrict__ in_count, unsigned long long* __restrict__ in_next,
+    uint32_t* __restrict__ out_list, unsigned long long* __restrict__ out_count,
+    unsigned long long* __restrict__ ctr /* [1]=cells [2]=groups given up by the first pass [3]=n gapped */) {
+    constexpr int GH_CELLS = CELLS;
+    constexpr int GH_WIN = 16 * CELLS;           // diagonals per half-warp window
+    constexpr int GH_KB0 = -(GH_WIN / 2);        // window start of a new extension: diagonal 0 in the middle
     __shared__ uint32_t stage_all[GH_THREADS / 16][4 * RCQ_STAGE_W];
     const int lane = threadIdx.x & 31, half = lane >> 4, j = lane & 15;
     const int hs = 16 * half;                       // shift of this half's bits in a ballot
@@ -94,8 +99,10 @@ __global__ void __launch_bounds__(GH_THREADS, 4) k_gapped_half(
     int32_t Lscore2 = 0, Lqi = 0, Lsj = 0, Lmism = 0, Lgw = 0;
     // wave state
     int32_t d = 0, Lk = 0, Uk = 0, gb = 0, Tprev = 0, kb = GH_KB0;
-    int32_t R0 = NEG, R1 = NEG, R2 = NEG;
-    uint32_t M0 = 0, M1 = 0, M2 = 0, G0 = 0, G1 = 0, G2 = 0;
+    int32_t R[CELLS];
+    uint32_t M[CELLS], G[CELLS];
+#pragma unroll
+    for (int c = 0; c < CELLS; c++) { R[c] = NEG; M[c] = 0; G[c] = 0; }
     int32_t bS = NEG, bD = 0, bK = 0, bM = 0, bG = 0;
     int32_t T0 = 0, T1 = 0;                 // T(x) for x & 31 == j and == j + 16
     bool overflow = false;
@@ -113,7 +120,7 @@ __global__ void __launch_bounds__(GH_THREADS, 4) k_gapped_half(
                 bool p = st == GH_FIN;
                 if (p && overflow) {
                     // the band outgrew the window: the whole group goes to the wide kernel
-                    if (j == 0) deferred[atomicAdd(ctr + 4, 1ull)] = (uint32_t)h;
+                    if (j == 0) out_list[atomicAdd(out_count, 1ull)] = (uint32_t)h;
                     n_deferred++;
                     group_open = false; nstep = 0; overflow = false;
                     st = GH_FETCH; p = false;
@@ -174,11 +181,11 @@ __global__ void __launch_bounds__(GH_THREADS, 4) k_gapped_half(
                     group_open = false;
                 }
                 unsigned long long g = 0;
-                if (p && j == 0) g = atomicAdd(ctr, 1ull);
+                if (p && j == 0) g = atomicAdd(in_next, 1ull);
                 g = __shfl_sync(FULL, g, 0, 16);
-                if (p && (int64_t)g >= n_groups) { st = GH_DONE; p = false; }
+                if (p && (int64_t)g >= (in_list ? (int64_t)*in_count : n_groups)) { st = GH_DONE; p = false; }
                 if (p) {
-                    h = heads[g];
+                    h = in_list ? in_list[g] : heads[g];
                     e_ = h + 1;
                     const uint64_t key = keys[h];
                     while (e_ < n && keys[e_] == key) e_++;
@@ -188,7 +195,7 @@ __global__ void __launch_bounds__(GH_THREADS, 4) k_gapped_half(
                     minus = (int32_t)(key & 1);
                     la = __ldg(P.lenA + ta); lb = __ldg(P.lenB + tb);
                     if (la > RCQ_STAGE_MAX || lb > RCQ_STAGE_MAX) {
-                        if (j == 0) deferred[atomicAdd(ctr + 4, 1ull)] = (uint32_t)h;
+                        if (j == 0) out_list[atomicAdd(out_count, 1ull)] = (uint32_t)h;
                         n_deferred++;
                         p = false;            // stays in GH_FETCH: next pass takes another group
                     }
@@ -261,13 +268,9 @@ __global__ void __launch_bounds__(GH_THREADS, 4) k_gapped_half(
                 if (begin) {
                     if (j == 0) nstep += (uint32_t)(first + 1);
                     kb = GH_KB0;
-                    R0 = R1 = R2 = NEG; M0 = M1 = M2 = 0; G0 = G1 = G2 = 0;
-                    const bool mine = (0 - GH_KB0) / GH_CELLS == j;     // diagonal 0 = cell (0 - kb) % 3 of lane (0 - kb) / 3
-                    if (mine) {
-                        if ((0 - GH_KB0) % GH_CELLS == 0) R0 = first;
-                        else if ((0 - GH_KB0) % GH_CELLS == 1) R1 = first;
-                        else R2 = first;
-                    }
+                    const bool mine = (0 - GH_KB0) / GH_CELLS == j;     // diagonal 0 = cell (0 - kb) % CELLS of lane (0 - kb) / CELLS
+#pragma unroll
+                    for (int c = 0; c < CELLS; c++) { R[c] = (mine && c == (0 - GH_KB0) % GH_CELLS) ? first : NEG; M[c] = 0; G[c] = 0; }
                     bS = mine ? 2 * first : NEG; bD = 0; bK = 0; bM = 0; bG = 0;
                     gb = 2 * first; Tprev = gb;
                     T0 = (j == 0) ? gb : 0; T1 = 0;
@@ -280,8 +283,8 @@ __global__ void __launch_bounds__(GH_THREADS, 4) k_gapped_half(
         if (__all_sync(FULL, st == GH_DONE)) break;
 
         // ---------------------------------------------------------------------- one wave, both halves
-        bool act = st == GH_RUN;
-        d += act ? 1 : 0;
+        const bool act0 = st == GH_RUN;
+        d += act0 ? 1 : 0;
         const int32_t qn = X.qn, sn = X.sn;
         int32_t tref;
         {
@@ -292,6 +295,7 @@ __global__ void __launch_bounds__(GH_THREADS, 4) k_gapped_half(
             if (d < RCQ_XDROP_OFFSET) tref = 0;
         }
         const int32_t klo = max(Lk - 1, -qn), khi = min(Uk + 1, sn);
+        bool act = act0;
         // keep the band inside the window: re-centre by whole lanes, or give the group up when it is wider than the window
         {
             const bool out_of_window = act && (klo < kb || khi > kb + GH_WIN - 1);
@@ -311,34 +315,39 @@ __global__ void __launch_bounds__(GH_THREADS, 4) k_gapped_half(
                 const int srcl = j + sh;
                 const bool in = srcl >= 0 && srcl < 16;
                 const int sl = in ? srcl : j;
-                const int32_t r0 = __shfl_sync(FULL, R0, sl, 16), r1 = __shfl_sync(FULL, R1, sl, 16), r2 = __shfl_sync(FULL, R2, sl, 16);
-                const uint32_t m0 = __shfl_sync(FULL, M0, sl, 16), m1 = __shfl_sync(FULL, M1, sl, 16), m2 = __shfl_sync(FULL, M2, sl, 16);
-                const uint32_t g0 = __shfl_sync(FULL, G0, sl, 16), g1 = __shfl_sync(FULL, G1, sl, 16), g2 = __shfl_sync(FULL, G2, sl, 16);
-                R0 = in ? r0 : NEG; R1 = in ? r1 : NEG; R2 = in ? r2 : NEG;
-                M0 = m0; M1 = m1; M2 = m2; G0 = g0; G1 = g1; G2 = g2;
+#pragma unroll
+                for (int c = 0; c < CELLS; c++) {
+                    const int32_t r = __shfl_sync(FULL, R[c], sl, 16);
+                    M[c] = __shfl_sync(FULL, M[c], sl, 16);
+                    G[c] = __shfl_sync(FULL, G[c], sl, 16);
+                    R[c] = in ? r : NEG;
+                }
             }
         }
         const int32_t d6 = 6 * d;
-        const int32_t xcut = tref - RCQ_XDROP_GAPPED2 + d6;       // alive iff 2 * row + k >= xcut
-        // the two neighbour cells this lane does not hold
-        int32_t Rl = __shfl_up_sync(FULL, R2, 1, 16), Rr = __shfl_down_sync(FULL, R0, 1, 16);
-        const uint32_t Ml = __shfl_up_sync(FULL, M2, 1, 16), Gl = __shfl_up_sync(FULL, G2, 1, 16);
-        const uint32_t Mr = __shfl_down_sync(FULL, M0, 1, 16), Gr = __shfl_down_sync(FULL, G0, 1, 16);
-        if (j == 0) Rl = NEG;
-        if (j == 15) Rr = NEG;
+        // alive iff 2 * row + k >= xcut (dead predecessors are far below any cut); a half that is not running gets a
+        // cut nothing passes
+        const int32_t xcut = act ? tref - RCQ_XDROP_GAPPED2 + d6 : 0x7fffffff;
+        // predecessor rows / counts of cells -1 .. CELLS: the two outer ones come from the neighbour lanes
+        int32_t Rx[CELLS + 2];
+        uint32_t Mx[CELLS + 2], Gx[CELLS + 2];
+        Rx[0] = __shfl_up_sync(FULL, R[CELLS - 1], 1, 16); Rx[CELLS + 1] = __shfl_down_sync(FULL, R[0], 1, 16);
+        Mx[0] = __shfl_up_sync(FULL, M[CELLS - 1], 1, 16); Mx[CELLS + 1] = __shfl_down_sync(FULL, M[0], 1, 16);
+        Gx[0] = __shfl_up_sync(FULL, G[CELLS - 1], 1, 16); Gx[CELLS + 1] = __shfl_down_sync(FULL, G[0], 1, 16);
+        if (j == 0) Rx[0] = NEG;
+        if (j == 15) Rx[CELLS + 1] = NEG;
+#pragma unroll
+        for (int c = 0; c < CELLS; c++) { Rx[c + 1] = R[c]; Mx[c + 1] = M[c]; Gx[c + 1] = G[c]; }
         const int32_t k0 = kb + GH_CELLS * j;
         SeqShared Qs, Ss;
         Qs.b = X.Q; Ss.b = X.S;
 
-        int32_t nR[GH_CELLS], bi_[GH_CELLS], lim_[GH_CELLS];
-        uint32_t nM[GH_CELLS], nG[GH_CELLS];
-        bool alive[GH_CELLS], cont[GH_CELLS];
+        int32_t lim_[CELLS], zsum = 0;
+        bool cont[CELLS], anycont = false;
 #pragma unroll
-        for (int c = 0; c < GH_CELLS; c++) {
+        for (int c = 0; c < CELLS; c++) {
             const int32_t k = k0 + c;
-            const int32_t left = c == 0 ? Rl : (c == 1 ? R0 : R1);
-            const int32_t mid = c == 0 ? R0 : (c == 1 ? R1 : R2);
-            const int32_t right = c == 0 ? R1 : (c == 1 ? R2 : Rr);
+            const int32_t left = Rx[c], mid = Rx[c + 1], right = Rx[c + 2];
             const int32_t rowmax = min(qn, sn - k);
             // candidates with their tie rank in the low bits: mismatch (rank 2), query gap (1), subject gap (0)
             const int32_t m4 = __vimax3_s32(mid * 4 + 6, right * 4 + 5, left * 4);
@@ -353,59 +362,57 @@ __global__ void __launch_bounds__(GH_THREADS, 4) k_gapped_half(
                 if (c1 > bi) { bi = c1; t = 1; }
                 if (c2 > bi) { bi = c2; t = 0; }
             }
-            const bool ok = act && bi >= 0 && 2 * bi + k >= xcut;
-            const uint32_t sm = t == 2 ? (c == 0 ? M0 : (c == 1 ? M1 : M2)) : (t == 1 ? (c == 0 ? M1 : (c == 1 ? M2 : Mr)) : (c == 0 ? Ml : (c == 1 ? M0 : M1)));
-            const uint32_t sg = t == 2 ? (c == 0 ? G0 : (c == 1 ? G1 : G2)) : (t == 1 ? (c == 0 ? G1 : (c == 1 ? G2 : Gr)) : (c == 0 ? Gl : (c == 1 ? G0 : G1)));
+            const bool ok = 2 * bi + k >= xcut;
+            const bool mis = t == 2, qgap = t == 1;
+            const uint32_t sm = mis ? Mx[c + 1] : (qgap ? Mx[c + 2] : Mx[c]);
+            const uint32_t sg = mis ? Gx[c + 1] : (qgap ? Gx[c + 2] : Gx[c]);
             const uint32_t op = 2u - (uint32_t)t;                 // 0 mismatch, 1 query gap, 2 subject gap
-            const uint32_t gapw = ((sg & ~7u) | op) + (1u << 17) + (((sg & 7u) != op) ? 8u : 0u);
-            nM[c] = sm + (t == 2 ? 1u : 0u);
-            nG[c] = t == 2 ? (sg & ~7u) : gapw;
+            const uint32_t base = sg & ~7u;
+            const uint32_t gapw = base + op + (1u << 17) + (((sg & 7u) != op) ? 8u : 0u);
             const int32_t lim = rowmax - bi;
-            // dead lanes compare the first words of the strands (in bounds) and drop the result
-            const int32_t r16 = run16(Qs, ok ? X.qo + bi : 0, Ss, ok ? X.so + bi + k : 0);
-            const int32_t z = (ok && lim > 0) ? min(r16, lim) : 0;
-            nstep += ok ? (uint32_t)(z + 1) : 0u;
-            alive[c] = ok; bi_[c] = bi; lim_[c] = lim;
-            nR[c] = bi + z;
-            cont[c] = ok && z == 16 && lim > 16;
+            // dead cells compare in-bounds words of the strands and drop the result
+            const int32_t bs = max(bi, 0);
+            const int32_t r16 = run16(Qs, X.qo + bs, Ss, max(X.so + bs + k, 0));
+            const int32_t z = ok ? min(r16, max(lim, 0)) : 0;
+            zsum += z;
+            lim_[c] = lim;
+            R[c] = ok ? bi + z : NEG;
+            M[c] = sm + (mis ? 1u : 0u);
+            G[c] = (mis ? base : gapw) | (z > 0 ? 4u : 0u);
+            cont[c] = z == 16 && lim > 16;
+            anycont = anycont || cont[c];
         }
         // slides that survived their first 16 bases are finished by the half-warp together
+        if (__any_sync(FULL, anycont)) {
 #pragma unroll
-        for (int c = 0; c < GH_CELLS; c++) {
-            unsigned more = __ballot_sync(FULL, cont[c]);
-            while (more) {
-                const unsigned mh = (more >> hs) & 0xFFFFu;
-                const int sl = mh ? __ffs(mh) - 1 : 0;
-                const int32_t e2 = __shfl_sync(FULL, nR[c], sl, 16), l2 = __shfl_sync(FULL, lim_[c], sl, 16);
-                const int32_t k2 = kb + GH_CELLS * sl + c;
-                const int32_t extra = gh_coop_slide(X.Q, X.qo + e2, X.S, X.so + e2 + k2, mh ? l2 - 16 : 0, j, half);
-                if (mh && j == sl) { nR[c] += extra; nstep += (uint32_t)extra; cont[c] = false; }
-                more = __ballot_sync(FULL, cont[c]);
+            for (int c = 0; c < CELLS; c++) {
+                unsigned more = __ballot_sync(FULL, cont[c]);
+                while (more) {
+                    const unsigned mh = (more >> hs) & 0xFFFFu;
+                    const int sl = mh ? __ffs(mh) - 1 : 0;
+                    const int32_t e2 = __shfl_sync(FULL, R[c], sl, 16), l2 = __shfl_sync(FULL, lim_[c], sl, 16);
+                    const int32_t k2 = kb + GH_CELLS * sl + c;
+                    const int32_t extra = gh_coop_slide(X.Q, X.qo + e2, X.S, X.so + e2 + k2, mh ? l2 - 16 : 0, j, half);
+                    if (mh && j == sl) { R[c] += extra; zsum += extra; cont[c] = false; }
+                    more = __ballot_sync(FULL, cont[c]);
+                }
             }
         }
-        int32_t wbest = NEG, ubmax = NEG, nL = 1 << 28, nU = -(1 << 28);
+        int32_t wbest = NEG, nL = 1 << 28, nU = -(1 << 28), nalive = 0;
 #pragma unroll
-        for (int c = 0; c < GH_CELLS; c++) {
+        for (int c = 0; c < CELLS; c++) {
             const int32_t k = k0 + c;
-            const bool ok = alive[c];
-            const int32_t e = nR[c];
-            if (ok && e > bi_[c]) nG[c] |= 4u;
-            const int32_t sc = ok ? 2 * e + k - d6 : NEG;
+            const bool ok = R[c] >= 0;
+            const int32_t sc = ok ? 2 * R[c] + k - d6 : NEG;
             wbest = max(wbest, sc);
             nL = min(nL, ok ? k : (1 << 28)); nU = max(nU, ok ? k : -(1 << 28));
-            ubmax = max(ubmax, ok ? 2 * min(qn, sn - k) + k - d6 : NEG);
-            if (sc > bS) { bS = sc; bD = d; bK = k; bM = (int32_t)nM[c]; bG = (int32_t)nG[c]; }
-            if (!ok) nR[c] = NEG;
+            nalive += ok ? 1 : 0;
+            if (sc > bS) { bS = sc; bD = d; bK = k; bM = (int32_t)M[c]; bG = (int32_t)G[c]; }
         }
-        if (act) {
-            R0 = nR[0]; R1 = nR[1]; R2 = nR[2];
-            M0 = nM[0]; M1 = nM[1]; M2 = nM[2];
-            G0 = nG[0]; G1 = nG[1]; G2 = nG[2];
-        }
+        nstep += (uint32_t)(zsum + nalive);       // one step per base slid over plus one per live cell
 #pragma unroll
         for (int o = 8; o; o >>= 1) {
             wbest = max(wbest, __shfl_xor_sync(FULL, wbest, o, 16));
-            ubmax = max(ubmax, __shfl_xor_sync(FULL, ubmax, o, 16));
             nL = min(nL, __shfl_xor_sync(FULL, nL, o, 16));
             nU = max(nU, __shfl_xor_sync(FULL, nU, o, 16));
         }
@@ -414,7 +421,11 @@ __global__ void __launch_bounds__(GH_THREADS, 4) k_gapped_half(
             if (j == (d & 15)) { if (d & 16) T1 = Tprev; else T0 = Tprev; }
             gb = max(gb, wbest);
             Lk = nL; Uk = nU;
-            if (Lk > Uk || ubmax <= gb || d >= qn + sn) st = GH_FIN;
+            // the most any diagonal of the band can still score: slide to the end of q or s with no further difference
+            // (2 min(qn, sn - k) + k peaks at k = sn - qn)
+            const int32_t kp = min(max(sn - qn, Lk), Uk);
+            const int32_t ub = 2 * min(qn, sn - kp) + kp - d6;
+            if (Lk > Uk || ub <= gb || d >= qn + sn) st = GH_FIN;
         }
     }
     // totals
@@ -426,5 +437,5 @@ __global__ void __launch_bounds__(GH_THREADS, 4) k_gapped_half(
         if (cells) atomicAdd(ctr + 1, cells);
         if (produced) atomicAdd(ctr + 3, produced);
     }
-    if (j == 0 && n_deferred) atomicAdd(ctr + 2, n_deferred);
+    if (j == 0 && n_deferred && !in_list) atomicAdd(ctr + 2, n_deferred);
 }

@@ -77,7 +77,7 @@ __device__ bool greedy_extend(const SeqArena Q, int64_t qpos, int32_t qn, const 
         if (d < RCQ_XDROP_OFFSET) tref = 0;
         const int32_t klo = max(L - 1, -qn), khi = min(U + 1, sn);
         if (RING && khi - klo + 1 > RCQ_RING) { ok = false; break; }
-        int32_t nL = 1 << 28, nU = -(1 << 28), wbest = NEG, ubmax = NEG;
+        int32_t nL = 1 << 28, nU = -(1 << 28), wbest = NEG;
         for (int32_t kb = klo; kb <= khi; kb += 32) {
             const int32_t k = kb + lane;
             int32_t bi = -1, src = 0, op = 0;
@@ -129,7 +129,6 @@ __device__ bool greedy_extend(const SeqArena Q, int64_t qpos, int32_t qn, const 
                     int32_t sc = 2 * e + k - 6 * d;
                     wbest = max(wbest, sc);
                     nL = min(nL, k); nU = max(nU, k);
-                    ubmax = max(ubmax, 2 * min(qn, sn - k) + k - 6 * d);
                     if (sc > bS) { bS = sc; bD = d; bK = k; bI = e; bM = mm; bG = gw; }
                 } else {
                     Rr[c + IX(k)] = -1;
@@ -139,14 +138,16 @@ __device__ bool greedy_extend(const SeqArena Q, int64_t qpos, int32_t qn, const 
         wbest = __reduce_max_sync(FULL, wbest);
         nL = __reduce_min_sync(FULL, nL);
         nU = __reduce_max_sync(FULL, nU);
-        ubmax = __reduce_max_sync(FULL, ubmax);
         Tprev = max(Tprev, wbest);
         if (lane == (d & 31)) Tl = Tprev;
         gb = max(gb, wbest);
         L = nL; U = nU;
         __syncwarp();
         if (L > U) break;
-        if (ubmax <= gb) break;      // nothing still alive can beat the best end point
+        {   // no diagonal of the band can still beat the best end point, even by matching to the end of q or s
+            const int32_t kp = min(max(sn - qn, L), U);
+            if (2 * min(qn, sn - kp) + kp - 6 * d <= gb) break;
+        }
     }
 #undef IX
     for (int o = 16; o; o >>= 1) nstep += __shfl_down_sync(FULL, nstep, o);
@@ -238,7 +239,7 @@ __device__ bool greedy_fast(const SEQ Q, int32_t qo, int32_t qn, const SEQ S, in
         if (RING && (klo - 2 < -RCQ_RING / 2 || khi + 2 >= RCQ_RING / 2)) { ok = false; break; }
         const int32_t xcut = tref - RCQ_XDROP_GAPPED2 + 6 * d;   // alive iff 2*row + k >= xcut
         const int32_t d6 = 6 * d;
-        int32_t nL = 1 << 28, nU = -(1 << 28), wbest = NEG, ubmax = NEG;
+        int32_t nL = 1 << 28, nU = -(1 << 28), wbest = NEG;
         for (int32_t kb = klo; kb <= khi; kb += 32) {
             const int32_t k = kb + lane;
             const bool active = k <= khi;
@@ -287,7 +288,6 @@ __device__ bool greedy_fast(const SEQ Q, int32_t qo, int32_t qn, const SEQ S, in
                     const int32_t sc = 2 * e + k - d6;
                     wbest = max(wbest, sc);
                     nL = min(nL, k); nU = max(nU, k);
-                    ubmax = max(ubmax, 2 * rowmax + k - d6);
                     if (sc > bS) { bS = sc; bD = d; bK = k; bI = e; bM = (int32_t)mm; bG = (int32_t)gw; }
                 } else {
                     Rr[c + ix] = NEG;
@@ -298,14 +298,16 @@ __device__ bool greedy_fast(const SEQ Q, int32_t qo, int32_t qn, const SEQ S, in
         wbest = __reduce_max_sync(FULL, wbest);
         nL = __reduce_min_sync(FULL, nL);
         nU = __reduce_max_sync(FULL, nU);
-        ubmax = __reduce_max_sync(FULL, ubmax);
         Tprev = max(Tprev, wbest);
         if (lane == (d & 31)) Tl = Tprev;
         gb = max(gb, wbest);
         L = nL; U = nU;
         __syncwarp();
         if (L > U) break;
-        if (ubmax <= gb) break;      // nothing still alive can beat the best end point
+        {   // no diagonal of the band can still beat the best end point, even by matching to the end of q or s
+            const int32_t kp = min(max(sn - qn, L), U);
+            if (2 * min(qn, sn - kp) + kp - d6 <= gb) break;
+        }
     }
 #undef IX
     nstep = __reduce_add_sync(FULL, nstep);
@@ -411,7 +413,8 @@ __global__ void __launch_bounds__(128, 5) k_gapped(const Ungapped* __restrict__ 
                                                 const uint32_t* __restrict__ heads, int64_t n_groups,
                                                 PairView P, Gapped* __restrict__ out, ScratchPool sp,
                                                 unsigned long long* __restrict__ ctr /* [0]=next group [1]=cells [2]=retries [3]=n gapped */,
-                                                const uint32_t* __restrict__ hlist /* deferred groups (k_gapped_half), or NULL = all groups */) {
+                                                const uint32_t* __restrict__ hlist /* group heads given up by k_gapped_half, or NULL = all groups */,
+                                                const unsigned long long* __restrict__ hcount, unsigned long long* __restrict__ hnext) {
     const int lane = threadIdx.x & 31;
     __shared__ __align__(16) int32_t ring_all[4][6 * RCQ_RING];
     // staged strands of the group's two transcripts (fast path): A forward, A reverse complement, B on the
@@ -422,10 +425,10 @@ __global__ void __launch_bounds__(128, 5) k_gapped(const Ungapped* __restrict__ 
     unsigned long long cells = 0, retries = 0, produced = 0;
     while (true) {
         unsigned long long g = 0;
-        if (lane == 0) g = atomicAdd(hlist ? ctr + 5 : ctr, 1ull);
+        if (lane == 0) g = atomicAdd(hlist ? hnext : ctr, 1ull);
         g = __shfl_sync(FULL, g, 0);
-        // deferred mode: the list of group heads k_gapped_half could not finish, its length in ctr[4]
-        if ((int64_t)g >= (hlist ? (int64_t)ctr[4] : n_groups)) break;
+        // deferred mode: the list of group heads k_gapped_half could not finish
+        if ((int64_t)g >= (hlist ? (int64_t)*hcount : n_groups)) break;
         const int64_t h = hlist ? hlist[g] : heads[g];
         int64_t e = h + 1;
         const uint64_t key = keys[h];

@@ -228,7 +228,7 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
         if (!occ[masked]) {
             int nb = 0;
             if (masked) CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_gapped<true>, threads, 0));
-            else CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_gapped_half, GH_THREADS, 0));
+            else CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_gapped_half<3>, GH_THREADS, 0));
             occ[masked] = nb > 0 ? nb : 1;
             if (const char* e = getenv("RCQ_GAPPED_BPS")) occ[masked] = std::max(1, std::min(occ[masked], atoi(e)));
         }
@@ -239,15 +239,23 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
         stage_tic(ctx, 4);
         if (masked) {
             // samples with N bases: the general path (mask words consulted in every comparison)
-            LAUNCH(ctx, k_gapped<true>, blocks, threads, 0, U, keys, n_hsp, F, heads, n_groups, P, G, sp, ctr, (const uint32_t*)nullptr);
+            LAUNCH(ctx, k_gapped<true>, blocks, threads, 0, U, keys, n_hsp, F, heads, n_groups, P, G, sp, ctr,
+                   (const uint32_t*)nullptr, (const unsigned long long*)nullptr, (unsigned long long*)nullptr);
         } else {
-            // half-warp engines on register rows; groups whose band outgrows the 48-diagonal window (or whose
-            // transcripts exceed the staged length) are listed and finished by the wide kernel on global rows
-            uint32_t* deferred = nullptr;
-            RC(talloc(ctx, &deferred, n_groups));
-            LAUNCH(ctx, k_gapped_half, blocks, GH_THREADS, 0, U, keys, n_hsp, F, heads, n_groups, P, G, deferred, ctr);
-            LAUNCH(ctx, k_gapped<false>, RCQ_SMS, threads, 0, U, keys, n_hsp, F, heads, n_groups, P, G, sp, ctr, (const uint32_t*)deferred);
-            tfree(ctx, deferred);
+            // half-warp engines on register rows: 48-diagonal windows for every group, 64-diagonal windows for the
+            // groups whose band outgrew 48 (a few per cent), and the wide kernel on global rows for what is left
+            // (bands beyond 64, transcripts beyond the staged length).  ctr: [4] / [6] lengths of the two lists,
+            // [5] / [7] their read positions.
+            uint32_t *list1 = nullptr, *list2 = nullptr;
+            RC(talloc(ctx, &list1, n_groups));
+            RC(talloc(ctx, &list2, n_groups));
+            LAUNCH(ctx, k_gapped_half<3>, blocks, GH_THREADS, 0, U, keys, n_hsp, F, heads, n_groups, P, G,
+                   (const uint32_t*)nullptr, (const unsigned long long*)nullptr, ctr, list1, ctr + 4, ctr);
+            LAUNCH(ctx, k_gapped_half<4>, blocks, GH_THREADS, 0, U, keys, n_hsp, F, heads, n_groups, P, G,
+                   (const uint32_t*)list1, (const unsigned long long*)(ctr + 4), ctr + 5, list2, ctr + 6, ctr);
+            LAUNCH(ctx, k_gapped<false>, RCQ_SMS * 2, threads, 0, U, keys, n_hsp, F, heads, n_groups, P, G, sp, ctr,
+                   (const uint32_t*)list2, (const unsigned long long*)(ctr + 6), ctr + 7);
+            tfree(ctx, list1); tfree(ctx, list2);
         }
         stage_toc(ctx, 4);
         tfree(ctx, U); tfree(ctx, keys); tfree(ctx, heads);
