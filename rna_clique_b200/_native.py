@@ -5,12 +5,13 @@ entry point that needs the GPU raises."""
 from __future__ import annotations
 
 import ctypes as C
+import os
 from pathlib import Path
 
 import numpy as np
 
 HERE = Path(__file__).resolve().parent
-LIB_PATH = HERE / "librnaclique_b200.so"
+LIB_PATH = Path(os.environ.get("RCQ_LIB") or HERE / "librnaclique_b200.so")   # RCQ_LIB: an experimental build of the same library
 
 TABLE_COLS = ["length", "mismatch", "gapopen", "qstart", "qend", "sstart", "send", "score", "gaps",
               "nident", "qgene", "qiso", "sgene", "siso", "qlen"]

@@ -55,11 +55,13 @@ __global__ void k_dust_triplets(const uint32_t* __restrict__ fwd, const uint32_t
 #define DUST_ROW 260
 __global__ void __launch_bounds__(DUST_FLAG_THREADS) k_dust_flag(const uint8_t* __restrict__ trip, int64_t arena,
                                                                   uint32_t* __restrict__ flag) {
-    __shared__ uint32_t cnt[3 * 16 * DUST_FLAG_THREADS];                      // [scale][triplet >> 2][thread], byte = triplet & 3
+    // one counter array per window length, [triplet >> 2][thread], byte = triplet & 3: separate arrays let the
+    // three read-modify-write chains of a step run side by side
+    __shared__ uint32_t cnt16[16 * DUST_FLAG_THREADS], cnt32[16 * DUST_FLAG_THREADS], cnt62[16 * DUST_FLAG_THREADS];
     __shared__ __align__(16) uint8_t tb[(DUST_FLAG_THREADS + 1) * DUST_ROW];   // positions block_start - 64 ..
     const int tid = threadIdx.x;
     const int64_t block_start = (int64_t)blockIdx.x * DUST_FLAG_THREADS * DUST_SEG;
-    for (int i = tid; i < 3 * 16 * DUST_FLAG_THREADS; i += DUST_FLAG_THREADS) cnt[i] = 0u;
+    for (int i = tid; i < 16 * DUST_FLAG_THREADS; i += DUST_FLAG_THREADS) { cnt16[i] = 0u; cnt32[i] = 0u; cnt62[i] = 0u; }
     // stage: word w of the region holds positions block_start - 64 + 4w .. +3
     const int n_words = (DUST_FLAG_THREADS * DUST_SEG + 64) / 4;
     for (int w = tid; w < n_words; w += DUST_FLAG_THREADS) {
@@ -75,9 +77,9 @@ __global__ void __launch_bounds__(DUST_FLAG_THREADS) k_dust_flag(const uint8_t* 
     const int64_t end = min(start + DUST_SEG, arena);
     int32_t r16 = 0, r32 = 0, r62 = 0;
     uint32_t bits = 0;
-    uint8_t* cb = (uint8_t*)cnt;
+    uint8_t* const cb0 = (uint8_t*)cnt16; uint8_t* const cb1 = (uint8_t*)cnt32; uint8_t* const cb2 = (uint8_t*)cnt62;
 #define TB(rel) tb[((rel) >> 8) * DUST_ROW + ((rel) & 255)]
-#define CNT(s, t) cb[(((s) * 16 + ((t) >> 2)) * DUST_FLAG_THREADS + tid) * 4 + ((t) & 3)]
+#define CNT(s, t) ((s) == 0 ? cb0 : (s) == 1 ? cb1 : cb2)[((((t) >> 2)) * DUST_FLAG_THREADS + tid) * 4 + ((t) & 3)]
     // rel = position - (block_start - 64); the walk starts DUST_MAXT positions early to fill the windows
     const int rel0 = 64 + tid * DUST_SEG;
     const int n = (int)(end - start);

@@ -27,6 +27,9 @@
 #include "gapped_kernels.cuh"
 
 #define GH_THREADS 128
+#ifndef GH_MIN_BLOCKS
+#define GH_MIN_BLOCKS 4               // resident blocks per SM the register budget is set for
+#endif
 
 enum { GH_FETCH = 0, GH_NEXT = 1, GH_RUN = 2, GH_FIN = 3, GH_DONE = 4 };
 
@@ -65,7 +68,7 @@ struct GhExt {            // one extension of a half-warp (uniform over its 16 l
 // groups the first pass gave up on; what outgrows that too goes to k_gapped.  Groups come from `heads` (in_list
 // == NULL) or from a list of group heads written by an earlier pass; groups given up are appended to out_list.
 template <int CELLS>
-__global__ void __launch_bounds__(GH_THREADS, 4) k_gapped_half(
+__global__ void __launch_bounds__(GH_THREADS, GH_MIN_BLOCKS) k_gapped_half(
     const Ungapped* __restrict__ U, const uint64_t* __restrict__ keys, int64_t n, KeyFmt F,
     const uint32_t* __restrict__ heads, int64_t n_groups, PairView P, Gapped* __restrict__ out,
     const uint32_t* __restrict__ in_list, const unsigned long long* __restrict__ in_count, unsigned long long* __restrict__ in_next,

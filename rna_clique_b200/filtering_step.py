@@ -67,6 +67,9 @@ def filtering_step(dirs: Iterable[Path], out_dir_1: Path, out_dir_2: Path, cache
     """Returns (tables, table_paths, graph, num_tables, path_to_sample) like the reference; `tables` reads the
     od2/ files lazily, `graph` is a GeneMatchGraph (an nx.Graph filled on first use) that also carries the
     device-resident tables for SampleSimilarity.  cache_dir is accepted and unused: the databases live in HBM."""
+    import time
+    trace = os.environ.get("RCQ_TRACE_API")
+    t_0 = time.perf_counter()
     dirs = [Path(d) for d in dirs]
     n = len(dirs)
     eng = shared_engine(jobs)
@@ -134,6 +137,7 @@ def filtering_step(dirs: Iterable[Path], out_dir_1: Path, out_dir_2: Path, cache
                                     out_paths[i], out_paths[j], table_paths[x])
 
         eng._run_tasks(tasks, ready, run, poll=0.0005)
+        t_1 = time.perf_counter()
         e = EdgeArrays()
         for slot, (i, j) in enumerate(pairs):
             if len(edges[slot][0]):
@@ -144,8 +148,12 @@ def filtering_step(dirs: Iterable[Path], out_dir_1: Path, out_dir_2: Path, cache
                                              empty=[len(t) == 0 for t in tables])
         if output_graph is not None:
             dump_graph(graph, output_graph)
+        t_2 = time.perf_counter()
         for f in writes:
             f.result()
+        if trace:
+            print(f"[filtering_step] parse+upload+search {t_1 - t_0:.3f} s, graph {t_2 - t_1:.3f} s, "
+                  f"waiting for table files {time.perf_counter() - t_2:.3f} s", file=__import__("sys").stderr)
     finally:
         host.shutdown(wait=True)
         for s in samples:

@@ -38,6 +38,8 @@ def rna_clique(dirs: Iterable[Path], out_dir_1: Path, out_dir_2: Path, cache_dir
                top_matches: int = 1, id_parser: Callable = default_parser, evalue: float = 1e-99,
                keep_all: bool = True, store_dfs: bool = False,
                jobs: int = max((os.cpu_count() or 2) - 1, 1)):
+    import time
+    t0 = time.perf_counter()
     tables, table_paths, graph, num_tables, pts = _fs.filtering_step(
         dirs, out_dir_1, out_dir_2, cache_dir, output_graph, top_genes, transcripts, top_matches, id_parser,
         evalue, keep_all, jobs)
@@ -45,6 +47,10 @@ def rna_clique(dirs: Iterable[Path], out_dir_1: Path, out_dir_2: Path, cache_dir
     if store_dfs:
         tables = dict(tables)
     sim = SampleSimilarity(graph, tables, _device=getattr(graph, "__dict__", {}).get("_rcq_device"))
+    t1 = time.perf_counter()
     if output_matrix is not None:
         write_matrix(sim.get_dissimilarity_df(), output_matrix)
+    if os.environ.get("RCQ_TRACE_API"):
+        import sys
+        print(f"[rna_clique] filtering_step {t1 - t0:.3f} s, phase 2 + matrix {time.perf_counter() - t1:.3f} s", file=sys.stderr)
     return sim, pts

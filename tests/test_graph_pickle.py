@@ -90,3 +90,36 @@ def test_dump_graph_keeps_the_graph_lazy_and_falls_back(tmp_path):
     sp.write_pickle(tmp_path / "s.pkl")
     sg = pickle.load(open(tmp_path / "s.pkl", "rb"))
     assert list(sg.nodes) == [("a", 2_000_000_000), ("b", 1_999_999_999), ("a", 5), ("b", 5)] and sg.number_of_edges() == 2
+
+
+def test_sorted_tables_parallel_parts_and_repeated_sample_pairs(tmp_path):
+    """The writer's three duplicate-row paths and its parallel adjacency section: tables sorted by gene pair with tie
+    rows next to each other (one comparison per row), an unsorted table (a hash set of its own), two groups
+    joining the same samples (one global set), on enough nodes for several parts."""
+    rng = np.random.default_rng(9)
+    names = [f"od1/S{k}_top.fasta" for k in range(4)]
+    n_genes = 3000
+    e = EdgeArrays()
+    for i in range(4):
+        for j in range(i + 1, 4):
+            q = np.sort(rng.choice(n_genes, size=n_genes * 4 // 5, replace=False)).astype(np.int32)
+            s = q.copy()
+            wrong = rng.random(len(q)) < 0.03
+            s[wrong] = rng.integers(0, n_genes, size=int(wrong.sum()))
+            rep = np.repeat(np.arange(len(q)), 1 + (rng.random(len(q)) < 0.5))     # tie rows directly after their twin
+            e.add(names[i], names[j], s[rep], q[rep])
+    got_info = e.write_pickle(tmp_path / "sorted.pkl")
+    _same(pickle.load(open(tmp_path / "sorted.pkl", "rb")), _reference_graph(e))
+    assert got_info["nodes"] > 4096
+    # one table out of order
+    s0, q0, sg, qg = e.groups[2]
+    perm = rng.permutation(len(sg))
+    e.groups[2] = (s0, q0, sg[perm], qg[perm])
+    e.write_pickle(tmp_path / "mixed.pkl")
+    _same(pickle.load(open(tmp_path / "mixed.pkl", "rb")), _reference_graph(e))
+    # the same sample pair twice, in both orientations, with edges in common
+    s0, q0, sg, qg = e.groups[0]
+    e.add(q0, s0, qg[:500], sg[:500])
+    e.add(s0, q0, sg[200:900], qg[200:900])
+    e.write_pickle(tmp_path / "repeat.pkl")
+    _same(pickle.load(open(tmp_path / "repeat.pkl", "rb")), _reference_graph(e))
