@@ -56,8 +56,10 @@ int64_t rcq_top_gene_mask(const double* coverage, const int32_t* gene, int64_t n
 
 /* ---- FASTA ingest (host only).  Replaces the two Bio.SeqIO.parse passes of select_top_genes.py:110-127
  * and, for the default rnaSPAdes pattern (transcripts.py:8), the per-record regex of transcripts.py:69-126.
- * rcq_fasta_scan counts records and letters; rcq_fasta_parse writes the letters (newlines, CR and spaces
- * removed) into ascii_out[n_letters], offsets[n_records+1] and the byte span of every header line;
+ * rcq_fasta_scan counts the records and bounds the letters from above (file size minus header lines; line ends
+ * inside the sequence lines are still counted) by hopping between '>' characters; rcq_fasta_parse writes the
+ * letters (newlines, CR and spaces removed) into ascii_out[], offsets[n_records+1] (offsets[n_records] = the true
+ * letter count) and the byte span of every header line;
  * rcq_parse_spades_ids decodes (coverage, gene, isoform) of every record id (first whitespace-separated
  * token of the header) and returns -1, or the index of the first id the pattern does not match. */
 int rcq_fasta_scan(const uint8_t* raw, int64_t n, int64_t* n_records, int64_t* n_letters);
@@ -80,6 +82,13 @@ int rcq_graph_pickle(const char* path, int32_t n_samples, const char* const* sam
                      int32_t n_groups, const int32_t* g_s, const int32_t* g_q, const int64_t* g_off,
                      const int32_t* sgene, const int32_t* qgene, int64_t n_isolated,
                      const int32_t* iso_sample, const int32_t* iso_gene, int64_t counts[3]);
+
+/* The same writer fed group by group (no concatenated copy of the columns): group g has g_len[g] rows in
+ * sgene[g][] / qgene[g][]. */
+int rcq_graph_pickle_groups(const char* path, int32_t n_samples, const char* const* sample_names,
+                            int32_t n_groups, const int32_t* g_s, const int32_t* g_q, const int64_t* g_len,
+                            const int32_t* const* sgene, const int32_t* const* qgene, int64_t n_isolated,
+                            const int32_t* iso_sample, const int32_t* iso_gene, int64_t counts[3]);
 
 /* ---- matrix.h5 (host only).  Replaces `mat.to_hdf(output_matrix, key="matrix")` (rna_clique.py:175-177; format:
  * docs/formats.md:346-352, read back by export_matrix.py:113 pd.read_hdf): writes an HDF5 file holding ONE pandas

@@ -20,7 +20,7 @@ HSP_COLS = ["tx1", "tx2", "minus", "a0", "a1", "b0", "b1", "score2", "mismatch",
 # every symbol include/rcq.h declares (checked by tests/test_abi.py)
 SYMBOLS = [
     "rcq_last_error", "rcq_version", "rcq_ctx_create", "rcq_ctx_destroy", "rcq_ctx_sync", "rcq_ctx_stream",
-    "rcq_ctx_launches", "rcq_ctx_stage_times", "rcq_top_gene_mask", "rcq_fasta_scan", "rcq_fasta_parse", "rcq_parse_spades_ids", "rcq_fasta_format", "rcq_graph_pickle", "rcq_matrix_h5_write", "rcq_sample_create", "rcq_sample_free", "rcq_sample_info", "rcq_sample_download",
+    "rcq_ctx_launches", "rcq_ctx_stage_times", "rcq_top_gene_mask", "rcq_fasta_scan", "rcq_fasta_parse", "rcq_parse_spades_ids", "rcq_fasta_format", "rcq_graph_pickle", "rcq_graph_pickle_groups", "rcq_matrix_h5_write", "rcq_sample_create", "rcq_sample_free", "rcq_sample_info", "rcq_sample_download",
     "rcq_ctx_set_dust", "rcq_sample_seed_mask", "rcq_int32_issue_peak",
     "rcq_search_pair", "rcq_table_rows", "rcq_table_download", "rcq_table_free", "rcq_debug_last_hsps", "rcq_debug_keep_hsps",
     "rcq_length_adjustment", "rcq_evalue", "rcq_bitscore", "rcq_phase2_host", "rcq_phase2_tables",
@@ -94,6 +94,7 @@ def lib():
         L.rcq_fasta_format.argtypes = [vp, vp, vp, i64, vp, vp, C.c_int32, vp]
         L.rcq_graph_pickle.argtypes = [C.c_char_p, C.c_int32, vp, C.c_int32, vp, vp, vp, vp, vp, i64, vp, vp, vp]
         L.rcq_fasta_format.restype = i64
+        L.rcq_graph_pickle_groups.argtypes = [C.c_char_p, C.c_int32, vp, C.c_int32, vp, vp, vp, vp, vp, i64, vp, vp, vp]
         L.rcq_matrix_h5_write.argtypes = [C.c_char_p, C.c_char_p, i64, i64, vp, vp, vp]
         L.rcq_top_gene_mask.argtypes = [vp, vp, i64, i64, vp]
         L.rcq_top_gene_mask.restype = i64
@@ -315,11 +316,12 @@ def fasta_parse(raw: np.ndarray):
     raw = np.ascontiguousarray(raw, dtype=np.uint8)
     cnt = np.zeros(2, dtype=np.int64)
     check(lib().rcq_fasta_scan(raw.ctypes.data, len(raw), cnt.ctypes.data, cnt.ctypes.data + 8))
-    n, letters = int(cnt[0]), int(cnt[1])
+    n, letters = int(cnt[0]), int(cnt[1])      # letters: an upper bound (line ends are still counted)
     ascii_ = np.empty(letters, dtype=np.uint8)
     offsets = np.zeros(n + 1, dtype=np.int64)
     hs, he = np.zeros(n, dtype=np.int64), np.zeros(n, dtype=np.int64)
     check(lib().rcq_fasta_parse(raw.ctypes.data, len(raw), ascii_.ctypes.data, offsets.ctypes.data, hs.ctypes.data, he.ctypes.data))
+    ascii_ = ascii_[:int(offsets[n])]
     return ascii_, offsets, hs, he
 
 
@@ -354,15 +356,16 @@ def graph_pickle(path, sample_names, groups, isolated=()) -> dict:
     arr = (C.c_char_p * max(len(names), 1))(*names)
     g_s = np.ascontiguousarray([g[0] for g in groups], dtype=np.int32)
     g_q = np.ascontiguousarray([g[1] for g in groups], dtype=np.int32)
-    g_off = np.zeros(len(groups) + 1, dtype=np.int64)
-    np.cumsum([len(g[2]) for g in groups], out=g_off[1:])
-    cat = lambda k: np.ascontiguousarray(np.concatenate([np.asarray(g[k], dtype=np.int32) for g in groups]) if groups else np.zeros(0, np.int32), dtype=np.int32)
-    sg, qg = cat(2), cat(3)
+    cols = [(np.ascontiguousarray(g[2], dtype=np.int32), np.ascontiguousarray(g[3], dtype=np.int32)) for g in groups]
+    g_len = np.ascontiguousarray([len(c[0]) for c in cols], dtype=np.int64)
+    sp = (C.c_void_p * max(len(cols), 1))(*[c[0].ctypes.data for c in cols])
+    qp = (C.c_void_p * max(len(cols), 1))(*[c[1].ctypes.data for c in cols])
     iso_s = np.ascontiguousarray([i[0] for i in isolated], dtype=np.int32)
     iso_g = np.ascontiguousarray([i[1] for i in isolated], dtype=np.int32)
     counts = np.zeros(3, dtype=np.int64)
-    check(lib().rcq_graph_pickle(str(path).encode(), len(names), C.cast(arr, C.c_void_p), len(groups), _ptr(g_s), _ptr(g_q),
-                                 g_off.ctypes.data, _ptr(sg), _ptr(qg), len(iso_s), _ptr(iso_s), _ptr(iso_g), counts.ctypes.data))
+    check(lib().rcq_graph_pickle_groups(str(path).encode(), len(names), C.cast(arr, C.c_void_p), len(groups), _ptr(g_s), _ptr(g_q),
+                                        _ptr(g_len), C.cast(sp, C.c_void_p), C.cast(qp, C.c_void_p), len(iso_s), _ptr(iso_s),
+                                        _ptr(iso_g), counts.ctypes.data))
     return dict(nodes=int(counts[0]), edges=int(counts[1]), bytes=int(counts[2]))
 
 

@@ -7,23 +7,26 @@
 
 static inline bool is_skip(uint8_t c) { return c == '\n' || c == '\r' || c == ' '; }
 
-// Pass 1: number of records (lines starting with '>') and of sequence letters (every byte outside
-// header lines that is not LF, CR or space).
+// Pass 1: number of records (lines starting with '>') and an upper bound of the sequence letters.  '>' is rare
+// outside header lines, so the records are counted by hopping from '>' to '>' with memchr; the letter count
+// returned is the file size minus the header lines - every LF, CR or space inside the sequence lines makes the
+// true count (offsets[n_records] after rcq_fasta_parse) smaller.
 extern "C" int rcq_fasta_scan(const uint8_t* raw, int64_t n, int64_t* n_records, int64_t* n_letters) {
     if (n < 0 || (n > 0 && !raw) || !n_records || !n_letters) return rcq_fail(RCQ_ERR_ARG, "rcq_fasta_scan: bad argument");
-    int64_t rec = 0, let = 0, p = 0;
+    int64_t rec = 0, hdr_bytes = 0, p = 0;
     while (p < n) {
-        const uint8_t* nl = (const uint8_t*)memchr(raw + p, '\n', (size_t)(n - p));
-        const int64_t e = nl ? (int64_t)(nl - raw) : n;
-        if (raw[p] == '>') rec++;
-        else {
-            int64_t k = e - p;
-            for (int64_t i = p; i < e; i++) k -= (raw[i] == '\r' || raw[i] == ' ');
-            let += k;
-        }
-        p = e + 1;
+        const uint8_t* gt = (const uint8_t*)memchr(raw + p, '>', (size_t)(n - p));
+        if (!gt) break;
+        const int64_t at = (int64_t)(gt - raw);
+        if (at == 0 || raw[at - 1] == '\n') {
+            const uint8_t* nl = (const uint8_t*)memchr(gt, '\n', (size_t)(n - at));
+            const int64_t e = nl ? (int64_t)(nl - raw) : n;
+            rec++;
+            hdr_bytes += e - at + 1;
+            p = e + 1;
+        } else p = at + 1;
     }
-    *n_records = rec; *n_letters = let;
+    *n_records = rec; *n_letters = n - hdr_bytes > 0 ? n - hdr_bytes : 0;
     return 0;
 }
 

@@ -78,13 +78,14 @@ void run_threads(int n_threads, F f) {                  // f(t) on n_threads thr
 // parts.  (The first version - one global hash set, one byte at a time - took 4.6 s of a 6.7 s rna_clique().)
 static int graph_pickle_impl(const char* path, int32_t n_samples, const char* const* sample_names,
                              int32_t n_groups, const int32_t* g_s, const int32_t* g_q, const int64_t* g_off,
-                             const int32_t* sgene, const int32_t* qgene, int64_t n_isolated,
+                             const int32_t* const* sgene_of, const int32_t* const* qgene_of, int64_t n_isolated,
                              const int32_t* iso_sample, const int32_t* iso_gene, int64_t counts[3]) {
+    // sgene_of[g] / qgene_of[g]: the columns of group g, biased by -g_off[g] so that they are indexed by the global row
     if (!path || n_samples < 0 || n_groups < 0 || n_isolated < 0 || (n_samples && !sample_names) ||
         (n_groups && (!g_s || !g_q || !g_off)) || (n_isolated && (!iso_sample || !iso_gene)))
         return rcq_fail(RCQ_ERR_ARG, "rcq_graph_pickle: bad argument");
     const int64_t n_rows = n_groups ? g_off[n_groups] : 0;
-    if (n_rows && (!sgene || !qgene)) return rcq_fail(RCQ_ERR_ARG, "rcq_graph_pickle: bad argument");
+    if (n_rows && (!sgene_of || !qgene_of)) return rcq_fail(RCQ_ERR_ARG, "rcq_graph_pickle: bad argument");
     const int n_threads = (int)std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
     static const bool trace = getenv("RCQ_TRACE") != nullptr;
     auto T0 = std::chrono::steady_clock::now();
@@ -100,6 +101,7 @@ static int graph_pickle_impl(const char* path, int32_t n_samples, const char* co
         if (g_s[g] < 0 || g_s[g] >= n_samples || g_q[g] < 0 || g_q[g] >= n_samples)
             return rcq_fail(RCQ_ERR_ARG, "rcq_graph_pickle: sample index out of range");
         int32_t ms = max_gene[g_s[g]], mq = max_gene[g_q[g]];
+        const int32_t* sgene = sgene_of[g]; const int32_t* qgene = qgene_of[g];
         for (int64_t r = g_off[g]; r < g_off[g + 1]; r++) {
             if (sgene[r] < 0 || qgene[r] < 0) return rcq_fail(RCQ_ERR_ARG, "rcq_graph_pickle: negative gene id");
             if (sgene[r] > ms) ms = sgene[r];
@@ -153,6 +155,7 @@ static int graph_pickle_impl(const char* path, int32_t n_samples, const char* co
         parallel_for(n_groups, n_threads, [&](int, int64_t g0, int64_t g1) {
             for (int64_t g = g0; g < g1; g++) {
                 const int64_t bs = base[g_s[g]], bq = base[g_q[g]];
+                const int32_t* sgene = sgene_of[g]; const int32_t* qgene = qgene_of[g];
                 for (int64_t r = g_off[g]; r < g_off[g + 1]; r++) {
                     note(bs + sgene[r], (uint32_t)(2 * r));
                     note(bq + qgene[r], (uint32_t)(2 * r + 1));
@@ -180,12 +183,14 @@ static int graph_pickle_impl(const char* path, int32_t n_samples, const char* co
         parallel_for(n_groups, n_threads, [&](int, int64_t g0, int64_t g1) {
             for (int64_t g = g0; g < g1; g++) {
                 const int64_t bs = base[g_s[g]], bq = base[g_q[g]];
+                const int32_t* sgene = sgene_of[g]; const int32_t* qgene = qgene_of[g];
                 for (int64_t r = g_off[g]; r < g_off[g + 1]; r++) { ru[r] = slot_id[bs + sgene[r]]; rv[r] = slot_id[bq + qgene[r]]; }
             }
         });
     } else {
         for (int32_t g = 0; g < n_groups; g++) {
             const int32_t sidx = g_s[g], q = g_q[g];
+            const int32_t* sgene = sgene_of[g]; const int32_t* qgene = qgene_of[g];
             for (int64_t r = g_off[g]; r < g_off[g + 1]; r++) { ru[r] = node_of(sidx, sgene[r]); rv[r] = node_of(q, qgene[r]); }
         }
         for (int64_t i = 0; i < n_isolated; i++) node_of(iso_sample[i], iso_gene[i]);
@@ -226,6 +231,7 @@ static int graph_pickle_impl(const char* path, int32_t n_samples, const char* co
         parallel_for(n_groups, n_threads, [&](int, int64_t g0, int64_t g1) {
             for (int64_t g = g0; g < g1; g++) {
                 const int64_t r0 = g_off[g], r1 = g_off[g + 1];
+                const int32_t* sgene = sgene_of[g]; const int32_t* qgene = qgene_of[g];
                 bool sorted = true;        // rows ordered by (qgene, sgene), as rcq_search_pair and the reference write them
                 for (int64_t r = r0 + 1; r < r1 && sorted; r++)
                     sorted = qgene[r] > qgene[r - 1] || (qgene[r] == qgene[r - 1] && sgene[r] >= sgene[r - 1]);
@@ -377,9 +383,30 @@ extern "C" int rcq_graph_pickle(const char* path, int32_t n_samples, const char*
                                 const int32_t* sgene, const int32_t* qgene, int64_t n_isolated,
                                 const int32_t* iso_sample, const int32_t* iso_gene, int64_t counts[3]) {
     try {   // no C++ exception may cross the C ABI
-        return graph_pickle_impl(path, n_samples, sample_names, n_groups, g_s, g_q, g_off, sgene, qgene, n_isolated,
-                                 iso_sample, iso_gene, counts);
+        std::vector<const int32_t*> sp((size_t)std::max(n_groups, 0), sgene), qp((size_t)std::max(n_groups, 0), qgene);   // one flat column: no bias
+        return graph_pickle_impl(path, n_samples, sample_names, n_groups, g_s, g_q, g_off, (n_groups && sgene) ? sp.data() : nullptr,
+                                 (n_groups && qgene) ? qp.data() : nullptr, n_isolated, iso_sample, iso_gene, counts);
     } catch (const std::bad_alloc&) {
         return rcq_fail(RCQ_ERR_CAPACITY, "rcq_graph_pickle: out of host memory");
+    }
+}
+
+extern "C" int rcq_graph_pickle_groups(const char* path, int32_t n_samples, const char* const* sample_names,
+                                       int32_t n_groups, const int32_t* g_s, const int32_t* g_q, const int64_t* g_len,
+                                       const int32_t* const* sgene, const int32_t* const* qgene, int64_t n_isolated,
+                                       const int32_t* iso_sample, const int32_t* iso_gene, int64_t counts[3]) {
+    try {
+        if (n_groups < 0 || (n_groups && (!g_len || !sgene || !qgene))) return rcq_fail(RCQ_ERR_ARG, "rcq_graph_pickle_groups: bad argument");
+        std::vector<int64_t> off((size_t)n_groups + 1, 0);
+        std::vector<const int32_t*> sp((size_t)n_groups), qp((size_t)n_groups);
+        for (int32_t g = 0; g < n_groups; g++) {
+            if (g_len[g] < 0 || (g_len[g] && (!sgene[g] || !qgene[g]))) return rcq_fail(RCQ_ERR_ARG, "rcq_graph_pickle_groups: bad group");
+            off[g + 1] = off[g] + g_len[g];
+            sp[g] = sgene[g] - off[g]; qp[g] = qgene[g] - off[g];
+        }
+        return graph_pickle_impl(path, n_samples, sample_names, n_groups, g_s, g_q, off.data(), sp.data(), qp.data(), n_isolated,
+                                 iso_sample, iso_gene, counts);
+    } catch (const std::bad_alloc&) {
+        return rcq_fail(RCQ_ERR_CAPACITY, "rcq_graph_pickle_groups: out of host memory");
     }
 }

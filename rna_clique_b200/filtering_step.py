@@ -30,7 +30,7 @@ from .filtered_distance import SampleSimilarity
 from .find_all_pairs import _label_and_save, make_output_path
 from .find_homologs import table_to_frame
 from .gene_matches_tables import default_extension
-from .select_top_genes import _select_and_write
+from .select_top_genes import _parse_and_select
 from .transcripts import default_parser
 
 _engine = None
@@ -93,13 +93,22 @@ def filtering_step(dirs: Iterable[Path], out_dir_1: Path, out_dir_2: Path, cache
         parsed = {}
         state = {"next": 0}
 
+        od1_writes = [None] * n
+
+        def parse_task(k):
+            # the device needs the selected records only: od1/<sample>_top.fasta is formatted and written as a task
+            # of its own, behind the parses already queued
+            out, stem, rec, write = _parse_and_select(out_dir_1, transcripts, dirs[k], top_genes, id_parser)
+            od1_writes[k] = host.submit(write)
+            return out, stem, rec
+
         def submit_parse():
             with lock:
                 k = state["next"]
                 if k >= n:
                     return
                 state["next"] = k + 1
-                parsed[k] = host.submit(_select_and_write, out_dir_1, transcripts, dirs[k], top_genes, id_parser)
+                parsed[k] = host.submit(parse_task, k)
 
         for _ in range(min(window, n)):
             submit_parse()
@@ -149,8 +158,9 @@ def filtering_step(dirs: Iterable[Path], out_dir_1: Path, out_dir_2: Path, cache
         if output_graph is not None:
             dump_graph(graph, output_graph)
         t_2 = time.perf_counter()
-        for f in writes:
-            f.result()
+        for f in writes + od1_writes:
+            if f is not None:
+                f.result()
         if trace:
             print(f"[filtering_step] parse+upload+search {t_1 - t_0:.3f} s, graph {t_2 - t_1:.3f} s, "
                   f"waiting for table files {time.perf_counter() - t_2:.3f} s", file=__import__("sys").stderr)

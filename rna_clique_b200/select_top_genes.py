@@ -68,17 +68,30 @@ class TopGeneSelector:
         return cls(lambda: read_fasta(Path(path)), *args, **kwargs)
 
 
-def _select_and_write(out_dir: Path, transcripts: str, x: Path, *args):
-    """Host half of select_top_and_save (thread-safe: no device work): returns (out path, x.stem, records),
-    records = (parser, letters, starts, gene, iso, lengths) of what was written."""
+def _parse_and_select(out_dir: Path, transcripts: str, x: Path, *args):
+    """Read, parse and select (thread-safe: no device work): returns (out path, x.stem, records, write), records =
+    (parser, letters, starts, gene, iso, lengths) of the selected transcripts and write() = the callable that
+    formats and writes out_dir/<x.stem>_top.fasta.  The device only needs `records`, so a pipeline can upload the
+    sample while (or before) the file is written."""
     x = Path(x)
     out = Path(out_dir) / (x.stem + "_top.fasta")
     sel = TopGeneSelector.from_path(x / transcripts, *args)
     fa, keep, _, gene, iso = sel.get_top_gene_seqs()
     starts, lengths = fa.offsets[:-1][keep], np.diff(fa.offsets)[keep]
-    write_fasta(out, fa.header_bytes(keep), fa.ascii, starts, lengths)
+
+    def write():
+        write_fasta(out, fa.header_bytes(keep), fa.ascii, starts, lengths)
+
     return out, x.stem, (sel.parser, fa.ascii, starts, np.asarray(gene, dtype=np.int32), np.asarray(iso, dtype=np.int32),
-                         lengths.astype(np.int32))
+                         lengths.astype(np.int32)), write
+
+
+def _select_and_write(out_dir: Path, transcripts: str, x: Path, *args):
+    """Host half of select_top_and_save (thread-safe: no device work): returns (out path, x.stem, records),
+    records = (parser, letters, starts, gene, iso, lengths) of what was written."""
+    out, stem, rec, write = _parse_and_select(out_dir, transcripts, x, *args)
+    write()
+    return out, stem, rec
 
 
 def select_top_and_save(out_dir: Path, transcripts: str, x: Path, *args, preload=None) -> tuple[Path, str]:
