@@ -222,6 +222,17 @@ int rcq_sample_meta(const rcq_sample* s, int64_t meta[8]);
 int rcq_sample_export(rcq_ctx* ctx, const rcq_sample* s, uint8_t* dev_flat);
 int rcq_sample_import(rcq_ctx* ctx, const int64_t meta[8], const uint8_t* dev_flat, rcq_sample** out);
 
+/* ---- multi-GPU exchange of what phase 2 reads (s_node, q_node, nident, length, gaps): 20 bytes per row.
+ * rcq_phase2_pack writes the five columns of this rank's tables as one column-major block [5][n_local] into
+ * dev_out (device memory, 5 * sum(rows) int32); the host layer all-gathers the blocks (NCCL).
+ * rcq_phase2_packed runs phase 2 on the gathered buffer: table t (row_off as in rcq_phase2_host, global pair
+ * order) has column c, row x at dev_packed[src_base[t] + c * src_stride[t] + x]. */
+int rcq_phase2_pack(rcq_ctx* ctx, int32_t n_tables, const rcq_table* const* tables, int32_t* dev_out);
+int rcq_phase2_packed(rcq_ctx* ctx, int32_t n_samples, int64_t stride, int32_t n_tables, const int64_t* row_off,
+                      const int32_t* t_s, const int32_t* t_q, const int64_t* src_base, const int64_t* src_stride,
+                      const int32_t* dev_packed, int32_t sample_count, int64_t* nident_sum, int64_t* denom_sum,
+                      uint8_t* valid, int64_t counts[6]);
+
 /* ---- multi-GPU exchange: serialise a table to / from a flat int32 buffer that the
  * host layer all-gathers with NCCL (torch.distributed) — device pointers in, device pointers out. */
 int64_t rcq_table_flat_words(const rcq_table* t);

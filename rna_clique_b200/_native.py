@@ -23,7 +23,7 @@ SYMBOLS = [
     "rcq_ctx_launches", "rcq_ctx_stage_times", "rcq_top_gene_mask", "rcq_fasta_scan", "rcq_fasta_parse", "rcq_parse_spades_ids", "rcq_fasta_format", "rcq_graph_pickle", "rcq_graph_pickle_groups", "rcq_matrix_h5_write", "rcq_sample_create", "rcq_sample_free", "rcq_sample_info", "rcq_sample_download",
     "rcq_ctx_set_dust", "rcq_sample_seed_mask", "rcq_int32_issue_peak",
     "rcq_search_pair", "rcq_table_rows", "rcq_table_download", "rcq_table_free", "rcq_debug_last_hsps", "rcq_debug_keep_hsps",
-    "rcq_length_adjustment", "rcq_evalue", "rcq_bitscore", "rcq_phase2_host", "rcq_phase2_tables",
+    "rcq_length_adjustment", "rcq_evalue", "rcq_bitscore", "rcq_phase2_host", "rcq_phase2_tables", "rcq_phase2_pack", "rcq_phase2_packed",
     "rcq_table_flat_words", "rcq_table_flatten", "rcq_table_from_flat", "rcq_sample_meta", "rcq_sample_export", "rcq_sample_import",
 ]
 
@@ -108,6 +108,8 @@ def lib():
         L.rcq_bitscore.restype = dbl
         L.rcq_phase2_host.argtypes = [vp, i32, i64, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, vp, vp, vp, vp]
         L.rcq_phase2_tables.argtypes = [vp, i32, i64, i32, vp, vp, vp, i32, vp, vp, vp, vp]
+        L.rcq_phase2_pack.argtypes = [vp, i32, vp, vp]
+        L.rcq_phase2_packed.argtypes = [vp, i32, i64, i32, vp, vp, vp, vp, vp, vp, i32, vp, vp, vp, vp]
         L.rcq_sample_meta.argtypes = [vp, vp]
         L.rcq_sample_export.argtypes = [vp, vp, vp]
         L.rcq_sample_import.argtypes = [vp, vp, vp, C.POINTER(vp)]
@@ -442,6 +444,36 @@ def phase2_tables(ctx: Context, n_samples: int, stride: int, tables, t_s, t_q, s
     counts = np.zeros(6, dtype=np.int64)
     code = lib().rcq_phase2_tables(ctx.h, n_samples, stride, n_tables, hs, t_s.ctypes.data, t_q.ctypes.data,
                                    int(sample_count or 0), ni.ctypes.data, de.ctypes.data, _ptr(valid), counts.ctypes.data)
+    res = dict(nident_sum=ni[:n_tables], denom_sum=de[:n_tables], valid=valid,
+               counts=dict(zip(["components", "ideal", "sample_count", "nodes", "edges", "ge_samples"], counts.tolist())))
+    if code == -4:
+        res["no_ideal"] = True
+        return res
+    check(code)
+    res["no_ideal"] = False
+    return res
+
+
+def phase2_pack(ctx: Context, tables, dev_ptr: int) -> None:
+    """rcq_phase2_pack: the five phase-2 columns of `tables` as one column-major int32 block at dev_ptr."""
+    hs = (C.c_void_p * max(len(tables), 1))(*[t.h for t in tables])
+    check(lib().rcq_phase2_pack(ctx.h, len(tables), hs, dev_ptr))
+
+
+def phase2_packed(ctx: Context, n_samples: int, stride: int, row_off, t_s, t_q, src_base, src_stride, dev_ptr: int,
+                  sample_count=None, want_valid: bool = False):
+    """rcq_phase2_packed: phase 2 on the all-gathered five-column blocks."""
+    row_off = np.ascontiguousarray(row_off, dtype=np.int64)
+    n_tables = len(row_off) - 1
+    t_s = np.ascontiguousarray(t_s, dtype=np.int32); t_q = np.ascontiguousarray(t_q, dtype=np.int32)
+    src_base = np.ascontiguousarray(src_base, dtype=np.int64); src_stride = np.ascontiguousarray(src_stride, dtype=np.int64)
+    ni = np.zeros(max(n_tables, 1), dtype=np.int64)
+    de = np.zeros(max(n_tables, 1), dtype=np.int64)
+    valid = np.zeros(n_samples * stride, dtype=np.uint8) if want_valid else None
+    counts = np.zeros(6, dtype=np.int64)
+    code = lib().rcq_phase2_packed(ctx.h, n_samples, stride, n_tables, row_off.ctypes.data, t_s.ctypes.data, t_q.ctypes.data,
+                                   src_base.ctypes.data, src_stride.ctypes.data, dev_ptr, int(sample_count or 0),
+                                   ni.ctypes.data, de.ctypes.data, _ptr(valid), counts.ctypes.data)
     res = dict(nident_sum=ni[:n_tables], denom_sum=de[:n_tables], valid=valid,
                counts=dict(zip(["components", "ideal", "sample_count", "nodes", "edges", "ge_samples"], counts.tolist())))
     if code == -4:

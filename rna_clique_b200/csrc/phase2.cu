@@ -291,6 +291,72 @@ extern "C" int rcq_phase2_tables(rcq_ctx* ctx, int32_t n_samples, int64_t stride
     return rc;
 }
 
+// ---- multi-GPU exchange of what phase 2 reads: five columns, 20 bytes per row -------------
+// rcq_phase2_pack: the five columns of this rank's tables as one column-major block [5][n_local] (k_p2_gather);
+// the host layer all-gathers the blocks over NCCL.  rcq_phase2_packed: phase 2 on the gathered buffer; table t
+// has its rows at dev_packed[src_base[t] + c * src_stride[t] + x] for column c, row x (src_stride = rows of the
+// block that holds it).
+__global__ void k_p2_unpack(const int64_t* __restrict__ row_off, const int64_t* __restrict__ src_base,
+                            const int64_t* __restrict__ src_stride, const int32_t* __restrict__ in, int32_t n_tables,
+                            int64_t n, int32_t* __restrict__ out) {
+    const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n) return;
+    const int32_t t = table_of(row_off, n_tables, r);
+    const int64_t at = __ldg(src_base + t) + (r - __ldg(row_off + t)), st = __ldg(src_stride + t);
+#pragma unroll
+    for (int c = 0; c < 5; c++) out[c * n + r] = __ldg(in + at + c * st);
+}
+
+extern "C" int rcq_phase2_pack(rcq_ctx* ctx, int32_t n_tables, const rcq_table* const* tables, int32_t* dev_out) {
+    if (!ctx || n_tables < 0 || (n_tables && (!tables || !dev_out))) return rcq_fail(RCQ_ERR_ARG, "rcq_phase2_pack: bad argument");
+    CU(cudaSetDevice(ctx->device));
+    std::vector<int64_t> host((size_t)2 * n_tables + 1, 0);
+    for (int t = 0; t < n_tables; t++) host[t + 1] = host[t] + tables[t]->n;
+    for (int t = 0; t < n_tables; t++) host[n_tables + 1 + t] = (int64_t)(uintptr_t)tables[t]->cols;
+    const int64_t n = host[n_tables];
+    if (n) {
+        int64_t* d_host = nullptr;
+        RC(dalloc(ctx, &d_host, (int64_t)host.size()));
+        CU(cudaMemcpyAsync(d_host, host.data(), host.size() * 8, cudaMemcpyHostToDevice, ctx->stream));
+        LAUNCH(ctx, k_p2_gather, grid_for(n, 256), 256, 0, d_host, (const int32_t* const*)(d_host + n_tables + 1), n_tables, n, dev_out);
+        dfree(ctx, d_host);
+    }
+    CU(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+extern "C" int rcq_phase2_packed(rcq_ctx* ctx, int32_t n_samples, int64_t stride, int32_t n_tables, const int64_t* row_off,
+                                 const int32_t* t_s, const int32_t* t_q, const int64_t* src_base, const int64_t* src_stride,
+                                 const int32_t* dev_packed, int32_t sample_count, int64_t* nident_sum, int64_t* denom_sum,
+                                 uint8_t* valid, int64_t counts[6]) {
+    if (!ctx || n_samples < 0 || stride < 1 || n_tables < 0 ||
+        (n_tables && (!row_off || !t_s || !t_q || !src_base || !src_stride || !nident_sum || !denom_sum)))
+        return rcq_fail(RCQ_ERR_ARG, "rcq_phase2_packed: bad argument");
+    CU(cudaSetDevice(ctx->device));
+    const int64_t n = n_tables ? row_off[n_tables] : 0;
+    if (n && !dev_packed) return rcq_fail(RCQ_ERR_ARG, "rcq_phase2_packed: bad argument");
+    // one host block [row offsets | src_base | src_stride | t_s | t_q]
+    const size_t words64 = (size_t)3 * n_tables + 1;
+    std::vector<int64_t> host(words64 + (size_t)n_tables + 1, 0);
+    for (int t = 0; t <= n_tables && n_tables; t++) host[t] = row_off[t];
+    for (int t = 0; t < n_tables; t++) { host[n_tables + 1 + t] = src_base[t]; host[2 * (size_t)n_tables + 1 + t] = src_stride[t]; }
+    int32_t* h32 = (int32_t*)(host.data() + words64);
+    for (int t = 0; t < n_tables; t++) { h32[t] = t_s[t]; h32[n_tables + t] = t_q[t]; }
+    P2View V;
+    memset(&V, 0, sizeof V);
+    V.n_samples = n_samples; V.n_tables = n_tables; V.stride = stride; V.n_rows = n;
+    int64_t* d_host = nullptr; int32_t* d_cols = nullptr;
+    RC(dalloc(ctx, &d_host, (int64_t)host.size()));
+    RC(dalloc(ctx, &d_cols, 5 * n));
+    CU(cudaMemcpyAsync(d_host, host.data(), host.size() * 8, cudaMemcpyHostToDevice, ctx->stream));
+    if (n) LAUNCH(ctx, k_p2_unpack, grid_for(n, 256), 256, 0, d_host, d_host + n_tables + 1, d_host + 2 * n_tables + 1, dev_packed, n_tables, n, d_cols);
+    V.row_off = d_host; V.t_s = (const int32_t*)(d_host + words64); V.t_q = V.t_s + n_tables;
+    V.sgene = d_cols; V.qgene = d_cols + n; V.nident = d_cols + 2 * n; V.length = d_cols + 3 * n; V.gaps = d_cols + 4 * n;
+    int rc = phase2_run(ctx, V, sample_count, nident_sum, denom_sum, valid, counts);
+    dfree(ctx, d_host); dfree(ctx, d_cols);
+    return rc;
+}
+
 // ---- flat (de)serialisation for the NCCL all-gather of hit tables ----------------
 extern "C" int64_t rcq_table_flat_words(const rcq_table* t) { return t ? (int64_t)RCQ_NCOLS * t->n : 0; }
 extern "C" int rcq_table_flatten(rcq_ctx* ctx, const rcq_table* t, int32_t* dev_out) {

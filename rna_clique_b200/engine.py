@@ -315,14 +315,23 @@ class Engine:
             for key, v in t.stats.items():
                 stats[key] = stats.get(key, 0) + v
         t_search = time.perf_counter()
-        if world > 1:
-            from .exchange import allgather_tables
-            tables = allgather_tables(self.ctx, dist, pairs, owner, mine, my_tables)
-        else:
-            tables = my_tables
         stride = 1 + max([0] + [int(np.max(s["gene"], initial=0)) for s in inputs])
-        t_exchange = time.perf_counter()
-        res = self.phase2(n, pairs, tables, stride)
+        if world > 1 and not keep_tables:
+            # the one exchange of results: the five columns phase 2 reads (20 bytes per row), all-gathered as one
+            # block per rank and reduced in place on every rank (exchange.phase2_exchanged)
+            from .exchange import phase2_exchanged
+            tables = my_tables
+            t_exchange = time.perf_counter()
+            res = phase2_exchanged(self.ctx, dist, n, stride, pairs, owner, mine, my_tables)
+            res.pop("_keep", None)
+        else:
+            if world > 1:       # whole tables on every rank (subset re-runs keep them)
+                from .exchange import allgather_tables
+                tables = allgather_tables(self.ctx, dist, pairs, owner, mine, my_tables)
+            else:
+                tables = my_tables
+            t_exchange = time.perf_counter()
+            res = self.phase2(n, pairs, tables, stride)
         t_phase2 = time.perf_counter()
         out = dict(host_ms=dict(upload=(t_upload - t_start) * 1e3, search=(t_search - t_upload) * 1e3,
                                 exchange=(t_exchange - t_search) * 1e3, phase2=(t_phase2 - t_exchange) * 1e3),
