@@ -209,28 +209,48 @@ def phase2_exchanged(ctx, dist, n_samples: int, stride: int, pairs, owner, mine,
     one block, the blocks are all-gathered (one collective for the row counts, one for the payload), and
     rcq_phase2_packed reduces the gathered buffer in place on every rank.  The library's stream waits for the
     collective through an event: no device-wide synchronisation."""
+    import os
+    import time
     world, rank = dist.get_world_size(), dist.get_rank()
     device = torch.device("cuda", ctx.device) if torch.cuda.is_available() and _is_nccl(dist) else torch.device("cpu")
     on_gpu = device.type == "cuda"
-    rows = torch.zeros(len(pairs), dtype=torch.int64, device=device)
+    trace = os.environ.get("RCQ_TRACE_EXCHANGE") and rank == 0
+    marks = [("start", time.perf_counter())]
+
+    def mark(name):
+        if trace:
+            if on_gpu:
+                torch.cuda.synchronize(device)
+            marks.append((name, time.perf_counter()))
+    info = torch.zeros((2, len(pairs)), dtype=torch.int64, device=device)   # rows of every table, rank + 1 of its holder
     mine_sorted = sorted(range(len(mine)), key=lambda x: mine[x])          # local tables in global pair order
     local = [my_tables[x] for x in mine_sorted]
     if mine:
-        rows[torch.as_tensor([mine[x] for x in mine_sorted], device=device)] = torch.as_tensor([len(t) for t in local], dtype=torch.int64, device=device)
-    dist.all_reduce(rows)                                                  # disjoint ids: the sum is a gather
-    rows = rows.cpu().numpy()
-    owner = np.asarray(owner)
+        ids = torch.as_tensor([mine[x] for x in mine_sorted], device=device)
+        info[0, ids] = torch.as_tensor([len(t) for t in local], dtype=torch.int64, device=device)
+        info[1, ids] = rank + 1
+    dist.all_reduce(info)                                                  # disjoint ids: the sum is a gather
+    info = info.cpu().numpy()
+    rows, holder = info[0], info[1] - 1
+    mark("row counts")
+    if (holder < 0).any() or (holder >= world).any():
+        raise RuntimeError("phase2_exchanged: a pair was searched by no rank or by several")
+    if owner is not None and not np.array_equal(np.asarray(owner), holder):
+        raise RuntimeError("phase2_exchanged: tables are not where the schedule put them")
+    owner = holder
     n_by_rank = [int(rows[owner == r].sum()) for r in range(world)]
     pad = max(max(n_by_rank), 1)
     cuda_dev = torch.device("cuda", ctx.device)
     buf = torch.zeros(5 * pad, dtype=torch.int32, device=cuda_dev)
     _native.phase2_pack(ctx, local, buf.data_ptr())                        # synchronous on the library's stream
+    mark("pack")
     gathered = torch.empty((world, 5 * pad), dtype=torch.int32, device=device)
     send = buf if buf.device == device else buf.to(device)
     if _is_nccl(dist):
         dist.all_gather_into_tensor(gathered, send)
     else:
         dist.all_gather(list(gathered.unbind(0)), send)
+    mark("all-gather")
     if gathered.is_cuda:
         ev = torch.cuda.Event()
         ev.record(torch.cuda.current_stream(gathered.device))
@@ -249,5 +269,10 @@ def phase2_exchanged(ctx, dist, n_samples: int, stride: int, pairs, owner, mine,
         at[r] += int(rows[k])
     res = _native.phase2_packed(ctx, n_samples, stride, row_off, [p[0] for p in pairs], [p[1] for p in pairs], src_base, src_stride,
                                 dev.data_ptr(), sample_count, want_valid)
+    mark("phase 2")
+    if trace:
+        import sys
+        print("[phase2_exchanged] " + ", ".join(f"{b[0]} {1e3 * (b[1] - a[1]):.2f} ms" for a, b in zip(marks, marks[1:])) +
+              f"; {int(rows.sum())} rows, pad {pad}", file=sys.stderr)
     res["_keep"] = (dev, gathered, buf)
     return res

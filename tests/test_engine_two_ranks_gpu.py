@@ -70,4 +70,6 @@ def test_two_ranks_on_one_gpu_equal_the_single_process_run():
         for lab, m, ni, de, counts, n_local in res[rank]:
             assert lab == ref["labels"] and np.array_equal(m, ref["matrix"])
             assert ni == ref["nident_sum"].tolist() and de == ref["denom_sum"].tolist() and counts == ref["counts"]
-            assert n_local == 5                      # 10 pairs, two ranks
+    # pairs are drawn at run time: every pair is searched exactly once, by whichever rank was free
+    for step in range(2):
+        assert sum(res[rank][step][5] for rank in range(world)) == 10
