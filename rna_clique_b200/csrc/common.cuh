@@ -62,7 +62,7 @@ struct rcq_ctx {
     int64_t gs_per_slot = 0;
     int32_t gs_slots = 0;
     int dust_on = 1;              // symmetric DUST soft-masking of seeds in samples built on this context (blastn default)
-    int gapped_occ[2] = {0, 0};   // resident blocks per SM of k_gapped<false/true> (occupancy query, cached)
+    int gapped_occ[3] = {0, 0, 0};   // resident blocks per SM of the gapped kernels (occupancy query, cached)
     // per-stage device time (CUDA events on this stream), accumulated across calls:
     // 0 pack+index, 1 seed join, 2 ungapped, 3 sort/group, 4 gapped DP, 5 selection+table, 6 phase 2
     double stage_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};

@@ -413,7 +413,7 @@ __global__ void __launch_bounds__(128, 5) k_gapped(const Ungapped* __restrict__ 
                                                 const uint32_t* __restrict__ heads, int64_t n_groups,
                                                 PairView P, Gapped* __restrict__ out, ScratchPool sp,
                                                 unsigned long long* __restrict__ ctr /* [0]=next group [1]=cells [2]=retries [3]=n gapped */,
-                                                const uint32_t* __restrict__ hlist /* group heads given up by k_gapped_half, or NULL = all groups */,
+                                                const uint32_t* __restrict__ hlist /* group heads given up by k_gapped_reg, or NULL = all groups */,
                                                 const unsigned long long* __restrict__ hcount, unsigned long long* __restrict__ hnext) {
     const int lane = threadIdx.x & 31;
     __shared__ __align__(16) int32_t ring_all[4][6 * RCQ_RING];
@@ -427,7 +427,7 @@ __global__ void __launch_bounds__(128, 5) k_gapped(const Ungapped* __restrict__ 
         unsigned long long g = 0;
         if (lane == 0) g = atomicAdd(hlist ? hnext : ctr, 1ull);
         g = __shfl_sync(FULL, g, 0);
-        // deferred mode: the list of group heads k_gapped_half could not finish
+        // deferred mode: the list of group heads k_gapped_reg could not finish
         if ((int64_t)g >= (hlist ? (int64_t)*hcount : n_groups)) break;
         const int64_t h = hlist ? hlist[g] : heads[g];
         int64_t e = h + 1;

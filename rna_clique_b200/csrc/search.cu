@@ -9,7 +9,7 @@
 
 #include "seed_kernels.cuh"
 #include "gapped_kernels.cuh"
-#include "gapped_half.cuh"
+#include "gapped_reg.cuh"
 #include "select_kernels.cuh"
 
 struct GappedValid {
@@ -64,6 +64,31 @@ static int scratch_pool(rcq_ctx* ctx, int64_t per_slot, ScratchPool* sp) {
 
 static int read_counters(rcq_ctx* ctx, int n) {
     return publish_counters(ctx, ctx->d_ctr, n);
+}
+
+// The register-row passes of the gapped stage: LANES x C1 diagonals for every group, LANES x C2 for the groups the
+// first pass gave up.  ctr: [0] / [5] read positions, [4] / [6] lengths of the two lists (rcq_search_pair below).
+template <int LANES, int C1, int C2, int THREADS, int MINB>
+static int launch_gapped_reg(rcq_ctx* ctx, int* occ_slot, const Ungapped* U, const uint64_t* keys, int64_t n_hsp, KeyFmt F,
+                             const uint32_t* heads, int64_t n_groups, PairView P, Gapped* G, unsigned long long* ctr,
+                             uint32_t* list1, uint32_t* list2) {
+    auto k1 = k_gapped_reg<LANES, C1, THREADS, MINB>;
+    auto k2 = k_gapped_reg<LANES, C2, THREADS, MINB>;
+    const size_t smem = gr_smem_bytes<LANES, THREADS>();
+    if (!*occ_slot) {
+        CU(cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CU(cudaFuncSetAttribute(k2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int nb = 0;
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k1, THREADS, smem));
+        *occ_slot = nb > 0 ? nb : 1;
+        if (const char* e = getenv("RCQ_GAPPED_BPS")) *occ_slot = std::max(1, std::min(*occ_slot, atoi(e)));
+    }
+    const int blocks = RCQ_SMS * *occ_slot;   // persistent engines, groups handed out by an atomic counter
+    LAUNCH(ctx, k1, blocks, THREADS, smem, U, keys, n_hsp, F, heads, n_groups, P, G,
+           (const uint32_t*)nullptr, (const unsigned long long*)nullptr, ctr, list1, ctr + 4, ctr);
+    LAUNCH(ctx, k2, blocks, THREADS, smem, U, keys, n_hsp, F, heads, n_groups, P, G,
+           (const uint32_t*)list1, (const unsigned long long*)(ctr + 4), ctr + 5, list2, ctr + 6, ctr);
+    return RCQ_OK;
 }
 
 extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sample* s2, double evalue,
@@ -224,35 +249,33 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
         CU(cudaMemsetAsync(G, 0xFF, n_slots * sizeof(Gapped), ctx->stream));
         const int threads = 128;
         const bool masked = s1->n_masked || s2->n_masked;
-        int* occ = ctx->gapped_occ;   // resident blocks per SM: [0] k_gapped_half, [1] k_gapped<true> (per context: contexts run on their own threads)
-        if (!occ[masked]) {
+        int* occ = ctx->gapped_occ;   // resident blocks per SM: [0] k_gapped_reg<8>, [1] k_gapped<true>, [2] k_gapped_reg<16> (per context: contexts run on their own threads)
+        if (masked && !occ[1]) {
             int nb = 0;
-            if (masked) CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_gapped<true>, threads, 0));
-            else CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_gapped_half<3>, GH_THREADS, 0));
-            occ[masked] = nb > 0 ? nb : 1;
-            if (const char* e = getenv("RCQ_GAPPED_BPS")) occ[masked] = std::max(1, std::min(occ[masked], atoi(e)));
+            CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_gapped<true>, threads, 0));
+            occ[1] = nb > 0 ? nb : 1;
         }
-        const int blocks = RCQ_SMS * occ[masked];   // persistent (half-)warps, groups handed out by an atomic counter
         ScratchPool sp;
         RC(scratch_pool(ctx, 6ll * ((int64_t)s1->max_len + s2->max_len + 8), &sp));
         CU(cudaMemsetAsync(ctr, 0, 16 * sizeof(int64_t), ctx->stream));
         stage_tic(ctx, 4);
         if (masked) {
             // samples with N bases: the general path (mask words consulted in every comparison)
-            LAUNCH(ctx, k_gapped<true>, blocks, threads, 0, U, keys, n_hsp, F, heads, n_groups, P, G, sp, ctr,
+            LAUNCH(ctx, k_gapped<true>, RCQ_SMS * occ[1], threads, 0, U, keys, n_hsp, F, heads, n_groups, P, G, sp, ctr,
                    (const uint32_t*)nullptr, (const unsigned long long*)nullptr, (unsigned long long*)nullptr);
         } else {
-            // half-warp engines on register rows: 48-diagonal windows for every group, 64-diagonal windows for the
+            // engines of 8 lanes on register rows: 48-diagonal windows for every group, 64-diagonal windows for the
             // groups whose band outgrew 48 (a few per cent), and the wide kernel on global rows for what is left
             // (bands beyond 64, transcripts beyond the staged length).  ctr: [4] / [6] lengths of the two lists,
-            // [5] / [7] their read positions.
+            // [5] / [7] their read positions.  RCQ_GAPPED_VARIANT=16 selects half-warp engines (measurement only).
             uint32_t *list1 = nullptr, *list2 = nullptr;
             RC(talloc(ctx, &list1, n_groups));
             RC(talloc(ctx, &list2, n_groups));
-            LAUNCH(ctx, k_gapped_half<3>, blocks, GH_THREADS, 0, U, keys, n_hsp, F, heads, n_groups, P, G,
-                   (const uint32_t*)nullptr, (const unsigned long long*)nullptr, ctr, list1, ctr + 4, ctr);
-            LAUNCH(ctx, k_gapped_half<4>, blocks, GH_THREADS, 0, U, keys, n_hsp, F, heads, n_groups, P, G,
-                   (const uint32_t*)list1, (const unsigned long long*)(ctr + 4), ctr + 5, list2, ctr + 6, ctr);
+            const char* variant = getenv("RCQ_GAPPED_VARIANT");
+            if (variant && atoi(variant) == 16)
+                RC((launch_gapped_reg<16, 3, 4, 128, 4>(ctx, &occ[2], U, keys, n_hsp, F, heads, n_groups, P, G, ctr, list1, list2)));
+            else
+                RC((launch_gapped_reg<8, 6, 8, 128, 4>(ctx, &occ[0], U, keys, n_hsp, F, heads, n_groups, P, G, ctr, list1, list2)));
             LAUNCH(ctx, k_gapped<false>, RCQ_SMS * 2, threads, 0, U, keys, n_hsp, F, heads, n_groups, P, G, sp, ctr,
                    (const uint32_t*)list2, (const unsigned long long*)(ctr + 6), ctr + 7);
             tfree(ctx, list1); tfree(ctx, list2);

@@ -17,6 +17,7 @@ def main():
     ap.add_argument("--config", type=int, default=1)
     ap.add_argument("--pairs", type=int, default=6)
     ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--variants", default="", help="comma-separated RCQ_GAPPED_VARIANT values to time in turn (8, 16)")
     a = ap.parse_args()
     taxa, count, top = CONFIGS[a.config]
     import itertools
@@ -34,20 +35,23 @@ def main():
         offs = t.offsets.numpy()
         keep = select_top_genes(t.coverage, t.gene, top)
         ss[k] = _native.Sample(ctx, t.ascii, offs[:-1][keep], t.gene[keep], t.iso[keep], lengths=np.diff(offs).astype(np.int32)[keep])
-    _native.search_pair(ctx, ss[pairs[0][0]], ss[pairs[0][1]]).close()
-    ctx.stage_times(reset=True)
-    cells = retries = 0
-    for _ in range(a.reps):
-        for i, j in pairs:
-            t = _native.search_pair(ctx, ss[i], ss[j])
-            cells += t.stats["dp_cells"]; retries += t.stats["band_retries"]
-            t.close()
-    st = ctx.stage_times(reset=True)
-    n = a.reps * len(pairs)
-    g = st["gapped_dp"]["ms"] / n
-    print(f"lib {_native.LIB_PATH.name}: gapped {g:.3f} ms per pair, {cells / n / (g * 1e-3) / 1e9:.1f} GCUPS, {retries / n:.0f} groups given up per pair; "
-          + ", ".join(f"{k} {v['ms'] / n:.3f}" for k, v in st.items() if k not in ("gapped_dp", "pack_index", "phase2")))
-
+    import os
+    for v in (a.variants.split(",") if a.variants else [None]):
+        if v is not None:
+            os.environ["RCQ_GAPPED_VARIANT"] = v
+        _native.search_pair(ctx, ss[pairs[0][0]], ss[pairs[0][1]]).close()
+        ctx.stage_times(reset=True)
+        cells = retries = 0
+        for _ in range(a.reps):
+            for i, j in pairs:
+                t = _native.search_pair(ctx, ss[i], ss[j])
+                cells += t.stats["dp_cells"]; retries += t.stats["band_retries"]
+                t.close()
+        st = ctx.stage_times(reset=True)
+        n = a.reps * len(pairs)
+        g = st["gapped_dp"]["ms"] / n
+        print(f"lib {_native.LIB_PATH.name} variant {v}: gapped {g:.3f} ms per pair, {cells / n / (g * 1e-3) / 1e9:.1f} GCUPS, {retries / n:.0f} groups given up per pair; "
+              + ", ".join(f"{k} {v2['ms'] / n:.3f}" for k, v2 in st.items() if k not in ("gapped_dp", "pack_index", "phase2")))
 
 if __name__ == "__main__":
     main()
