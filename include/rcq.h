@@ -128,6 +128,25 @@ int rcq_sample_download(const rcq_sample* s, uint32_t* fwd, uint32_t* rc, uint32
 int rcq_ctx_set_dust(rcq_ctx* ctx, int on);
 int rcq_sample_seed_mask(const rcq_sample* s, uint32_t* smask, int64_t* n_dust);
 
+/* The same DUST seeding mask without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Runs the kernels rcq_sample_create runs for the mask (csrc/dust_kernels.cuh) with
+ * their scratch — one triplet byte per base, one flag bit per base, counters — in a file-scope
+ * `static __device__` array of the library (18.1 MB, held by every GPU that loads the library until the process
+ * exits) instead of the context's memory pool; the call itself performs no cudaMalloc / cudaFree and needs no
+ * rcq_ctx.  Inputs and output are the caller's DEVICE buffers on `device`, laid out as rcq_sample_download /
+ * rcq_sample_seed_mask return them: dev_fwd = 2-bit words (arena_bases / 16 uint32), dev_mask = not-ACGT and
+ * padding bits (arena_bases / 32 uint32), dev_smask = output (arena_bases / 32 uint32) = dev_mask | DUST.
+ * arena_bases: a positive multiple of 64, at most RCQ_DUST_STATIC_MAX_BASES — larger inputs are rejected with
+ * RCQ_ERR_CAPACITY and a message naming the limit.  stream: a cudaStream_t (NULL = the default stream); the work
+ * is queued on it and the call returns without waiting unless n_dust (host, may be NULL: bases masked by DUST
+ * alone) is asked for.  All calls on a GPU share the one scratch array, which keeps the previous call's
+ * contents (what has to start at zero is cleared by the call): calls that OVERLAP on the same GPU — two host
+ * threads, or two streams without an ordering between them — race; serialise them. */
+#define RCQ_DUST_STATIC_MAX_BASES (1ll << 24)
+int rcq_dust_mask_static(int device, const uint32_t* dev_fwd, const uint32_t* dev_mask, int64_t arena_bases,
+                         uint32_t* dev_smask, void* stream, int64_t* n_dust);
+
 /* ---- kernel (3) + table assembly.  One UNORDERED sample pair: both blastn directions
  * (find_homologs.py:82-133 gene_matches, :124 TabularBlastnSearch), the per-query-gene
  * best-bitscore reduction (:135-164) and HomologFinder.get_match_table (:215-302).

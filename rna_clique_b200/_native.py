@@ -21,7 +21,7 @@ HSP_COLS = ["tx1", "tx2", "minus", "a0", "a1", "b0", "b1", "score2", "mismatch",
 SYMBOLS = [
     "rcq_last_error", "rcq_version", "rcq_ctx_create", "rcq_ctx_destroy", "rcq_ctx_sync", "rcq_ctx_stream",
     "rcq_ctx_launches", "rcq_ctx_stage_times", "rcq_top_gene_mask", "rcq_fasta_scan", "rcq_fasta_parse", "rcq_parse_spades_ids", "rcq_fasta_format", "rcq_graph_pickle", "rcq_graph_pickle_groups", "rcq_matrix_h5_write", "rcq_sample_create", "rcq_sample_free", "rcq_sample_info", "rcq_sample_download",
-    "rcq_ctx_set_dust", "rcq_sample_seed_mask", "rcq_int32_issue_peak",
+    "rcq_ctx_set_dust", "rcq_sample_seed_mask", "rcq_dust_mask_static", "rcq_int32_issue_peak",
     "rcq_search_pair", "rcq_table_rows", "rcq_table_download", "rcq_table_free", "rcq_debug_last_hsps", "rcq_debug_keep_hsps",
     "rcq_length_adjustment", "rcq_evalue", "rcq_bitscore", "rcq_phase2_host", "rcq_phase2_tables", "rcq_phase2_pack", "rcq_phase2_packed",
     "rcq_table_flat_words", "rcq_table_flatten", "rcq_table_from_flat", "rcq_sample_meta", "rcq_sample_export", "rcq_sample_import",
@@ -79,6 +79,7 @@ def lib():
         L.rcq_ctx_set_dust.argtypes = [vp, C.c_int]
         L.rcq_int32_issue_peak.argtypes = [vp, i32, C.POINTER(dbl)]
         L.rcq_sample_seed_mask.argtypes = [vp, vp, vp]
+        L.rcq_dust_mask_static.argtypes = [C.c_int, vp, vp, C.c_int64, vp, vp, vp]
         L.rcq_search_pair.argtypes = [vp, vp, vp, dbl, i32, i32, C.POINTER(vp), C.POINTER(SearchStats)]
         L.rcq_table_rows.argtypes = [vp]
         L.rcq_table_rows.restype = i64

@@ -4,6 +4,7 @@
 //   pack   : 1 B/nt read + 0.25 B/nt written (+0.25 rc +2x1/32 masks)
 //   index  : 0.25 B/nt read, 8 B per selected minimizer written, then an 8-B-key radix sort.
 #include <cub/cub.cuh>
+#include <mutex>
 #include "sample.cuh"
 #include "dust_kernels.cuh"
 
@@ -470,5 +471,92 @@ int rcq_sample_build(rcq_ctx* ctx, rcq_sample* s, const uint8_t* d_ascii, int64_
     // depends on (seeds are re-sorted by transcript and diagonal)
     if (s->n_index) RC(sort_index(ctx, s->index, s->fctx, s->n_index));
     LAUNCH(ctx, k_build_dir, grid_for(s->n_index + 1, 256), 256, 0, s->index, s->n_index, s->dir);
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// rcq_dust_mask_static — the DUST seeding-mask kernels of the sample build (k_dust_triplets, k_dust_flag,
+// k_dust_eval, k_dust_or, launched exactly as above) for callers that must not allocate: their scratch (triplet
+// bytes, flag words, counters) lives in the file-scope device array below instead of the context's pool.  No
+// counterpart in the reference (include/rcq.h).  The array is held by
+// every GPU that loads the library until the process exits; every call on a GPU shares it, so calls that overlap
+// on one GPU race.
+#define RCQ_DUST_STATIC_CTR_BYTES 256
+#define RCQ_DUST_STATIC_FLAG_BYTES (RCQ_DUST_STATIC_MAX_BASES / 8)
+#define RCQ_DUST_STATIC_BYTES (RCQ_DUST_STATIC_CTR_BYTES + RCQ_DUST_STATIC_FLAG_BYTES + RCQ_DUST_STATIC_MAX_BASES)
+static __device__ __align__(256) uint8_t g_dust_static[RCQ_DUST_STATIC_BYTES];
+
+#define RCQ_DUST_STATIC_MAX_DEVICES 64
+static uint8_t* g_dust_static_ptr[RCQ_DUST_STATIC_MAX_DEVICES];   // device address of g_dust_static on each GPU
+static std::mutex g_dust_static_mu;
+
+namespace {
+struct DeviceGuard {        // makes `device` current for the call and puts the caller's device back
+    int prev = -1;
+    bool changed = false;
+    cudaError_t enter(int device) {
+        cudaError_t e = cudaGetDevice(&prev);
+        if (e != cudaSuccess) return e;
+        if (prev != device) { e = cudaSetDevice(device); changed = e == cudaSuccess; }
+        return e;
+    }
+    ~DeviceGuard() { if (changed) cudaSetDevice(prev); }
+};
+}  // namespace
+
+// In host code `g_dust_static` is only a stand-in for the symbol: the address a kernel can use comes from
+// cudaGetSymbolAddress, asked once per device with that device current.
+static int dust_static_base(int device, uint8_t** base) {
+    std::lock_guard<std::mutex> lock(g_dust_static_mu);
+    if (!g_dust_static_ptr[device]) {
+        void* p = nullptr;
+        CU(cudaGetSymbolAddress(&p, g_dust_static));
+        if (!p) return rcq_fail(RCQ_ERR_CUDA, "rcq_dust_mask_static: cudaGetSymbolAddress returned a null address");
+        g_dust_static_ptr[device] = (uint8_t*)p;
+    }
+    *base = g_dust_static_ptr[device];
+    return 0;
+}
+
+extern "C" int rcq_dust_mask_static(int device, const uint32_t* dev_fwd, const uint32_t* dev_mask, int64_t arena_bases,
+                                    uint32_t* dev_smask, void* stream, int64_t* n_dust) {
+    if (device < 0 || device >= RCQ_DUST_STATIC_MAX_DEVICES || !dev_fwd || !dev_mask || !dev_smask)
+        return rcq_fail(RCQ_ERR_ARG, "rcq_dust_mask_static: bad argument");
+    if (arena_bases <= 0 || arena_bases % 64)
+        return rcq_fail(RCQ_ERR_ARG, "rcq_dust_mask_static: arena_bases must be a positive multiple of 64");
+    if (arena_bases > RCQ_DUST_STATIC_MAX_BASES) {
+        char a[32], b[32];
+        snprintf(a, sizeof a, "%lld", (long long)arena_bases);
+        snprintf(b, sizeof b, "%lld", (long long)RCQ_DUST_STATIC_MAX_BASES);
+        return rcq_fail(RCQ_ERR_CAPACITY, "rcq_dust_mask_static: %s bases exceed the static scratch (at most %s bases per call)", a, b);
+    }
+    DeviceGuard guard;
+    CU(guard.enter(device));
+    uint8_t* base = nullptr;
+    RC(dust_static_base(device, &base));
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned long long* ctr = (unsigned long long*)base;
+    uint32_t* flag = (uint32_t*)(base + RCQ_DUST_STATIC_CTR_BYTES);
+    uint8_t* trip = base + RCQ_DUST_STATIC_CTR_BYTES + RCQ_DUST_STATIC_FLAG_BYTES;
+    const int64_t words = arena_bases / 16, mwords = arena_bases / 32;
+    // the array keeps the last call's contents: counters and the output (k_dust_eval ORs into it) start at zero;
+    // triplets and flags are written in full for [0, arena_bases) before they are read
+    CU(cudaMemsetAsync(ctr, 0, RCQ_DUST_STATIC_CTR_BYTES, st));
+    CU(cudaMemsetAsync(flag, 0, (size_t)mwords * 4, st));
+    CU(cudaMemsetAsync(dev_smask, 0, (size_t)mwords * 4, st));
+    k_dust_triplets<<<grid_for(words, 256), 256, 0, st>>>(dev_fwd, dev_mask, arena_bases, trip);
+    CU(cudaGetLastError());
+    k_dust_flag<<<grid_for((arena_bases + DUST_SEG - 1) / DUST_SEG, DUST_FLAG_THREADS), DUST_FLAG_THREADS, 0, st>>>(trip, arena_bases, flag);
+    CU(cudaGetLastError());
+    k_dust_eval<<<RCQ_SMS * 8, DUST_EVAL_THREADS, 0, st>>>(trip, flag, arena_bases, dev_smask, ctr);
+    CU(cudaGetLastError());
+    k_dust_or<<<grid_for(mwords, 256), 256, 0, st>>>(dev_mask, dev_smask, mwords, ctr);
+    CU(cudaGetLastError());
+    if (n_dust) {
+        unsigned long long v = 0;
+        CU(cudaMemcpyAsync(&v, ctr + 4, sizeof v, cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        *n_dust = (int64_t)v;
+    }
     return 0;
 }
