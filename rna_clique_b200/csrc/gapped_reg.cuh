@@ -374,8 +374,8 @@ __global__ void __launch_bounds__(THREADS, MINB) k_gapped_reg(
         SeqShared Qs, Ss;
         Qs.b = X.Q; Ss.b = X.S;
 
-        int32_t zsum = 0, nalive = 0;
-        int32_t wbest = NEG, nL = 1 << 28, nU = -(1 << 28);
+        int32_t zsum = 0;
+        uint32_t alive = 0;                       // bit c: cell c of this lane is inside the X-drop band
         // the first cell of the lane whose slide ran past its 16 bases: finished below by the whole engine
         bool has_cont = false;
         int32_t ce = 0, cl = 0, ck = 0, cidx = 0;
@@ -402,7 +402,8 @@ __global__ void __launch_bounds__(THREADS, MINB) k_gapped_reg(
             const uint32_t sg = mis ? Gx[c + 1] : (qgap ? Gx[c + 2] : Gx[c]);
             const uint32_t op = 2u - (uint32_t)t;                 // 0 mismatch, 1 query gap, 2 subject gap
             const uint32_t base = sg & ~7u;
-            const uint32_t gapw = base + op + (1u << 17) + (((sg & 7u) != op) ? 8u : 0u);
+            // a gap base: one more gap, and one more opening unless the same kind of gap ended right here
+            const uint32_t gapw = (base | op) + (1u << 17) + ((((sg ^ op) & 7u) + 7u) & 8u);
             const int32_t lim = rowmax - bi;
             // dead cells compare in-bounds words of the strands and drop the result
             const int32_t bs = max(bi, 0);
@@ -424,8 +425,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_gapped_reg(
             zsum += z;
             R[c] = ok ? bi + z : NEG;
             G[c] = (mis ? base : gapw) | (z > 0 ? 4u : 0u);
-            nalive += ok ? 1 : 0;
-            nL = min(nL, ok ? k : (1 << 28)); nU = max(nU, ok ? k : -(1 << 28));
+            alive |= ok ? (1u << c) : 0u;
         }
         // slides that survived their first 16 bases are finished by the engine together
         if (__any_sync(FULL, has_cont)) {
@@ -446,20 +446,32 @@ __global__ void __launch_bounds__(THREADS, MINB) k_gapped_reg(
                 }
             }
         }
+        // best cell of the lane in this wave: score first, then the lowest diagonal (dead cells: NEG far below)
+        int32_t lkey = NEG;
 #pragma unroll
         for (int c = 0; c < CELLS; c++) {
-            const int32_t k = k0 + c;
-            const int32_t sc = R[c] >= 0 ? 2 * R[c] + k - d6 : NEG;
-            wbest = max(wbest, sc);
-            if (sc > bS) { bS = sc; bD = d; bK = k; bG = (int32_t)G[c]; }
+            const int32_t sc = R[c] >= 0 ? 2 * R[c] + (k0 + c) - d6 : (NEG >> 4);
+            lkey = max(lkey, sc * 16 + (15 - c));
         }
-        nstep += (uint32_t)(zsum + nalive);       // one step per base slid over plus one per live cell
+        int32_t wbest = lkey >> 4;
+        if (alive && wbest > bS) {                // strictly better than every earlier wave: (d, k) ties keep the first
+            const int cb = 15 - (lkey & 15);
+            bS = wbest; bD = d; bK = k0 + cb;
+            uint32_t g = G[0];
+#pragma unroll
+            for (int c = 1; c < CELLS; c++) g = (c == cb) ? G[c] : g;
+            bG = (int32_t)g;
+        }
+        nstep += (uint32_t)(zsum + __popc(alive));       // one step per base slid over plus one per live cell
+        // live range of the band, both ends in one packed 16-bit maximum (|k| <= RCQ_STAGE_MAX): high = Uk, low = -Lk
+        uint32_t rng = alive ? (((uint32_t)(uint16_t)(int16_t)(k0 + 31 - __clz(alive)) << 16) | (uint32_t)(uint16_t)(int16_t)(-(k0 + __ffs(alive) - 1)))
+                             : 0x8AD08AD0u;       // (-30000, -30000): no live cell
 #pragma unroll
         for (int o = LANES / 2; o; o >>= 1) {
             wbest = max(wbest, __shfl_xor_sync(FULL, wbest, o, LANES));
-            nL = min(nL, __shfl_xor_sync(FULL, nL, o, LANES));
-            nU = max(nU, __shfl_xor_sync(FULL, nU, o, LANES));
+            rng = __vmaxs2(rng, __shfl_xor_sync(FULL, rng, o, LANES));
         }
+        const int32_t nU = (int32_t)(int16_t)(rng >> 16), nL = -(int32_t)(int16_t)(rng & 0xFFFFu);
         if (act) {
             Tprev = max(Tprev, wbest);
             if (j == 0) tring[d & 31] = Tprev;
