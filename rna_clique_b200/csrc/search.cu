@@ -135,6 +135,18 @@ extern "C" int rcq_search_pair(rcq_ctx* ctx, const rcq_sample* s1, const rcq_sam
         LAUNCH(ctx, k_seed_probe, grid_for(s1->n_index, PROBE_TA), PROBE_THREADS, 0, s1->index, s1->fctx, s1->n_index, s2->index,
                s2->fctx, s2->dir, cand, ccap, ctr);
         stage_toc(ctx, 7);
+        {   // candidates into position order of sample 1 (counting sort on the top bits; the count stays on the device)
+            uint2* cand2 = nullptr; uint32_t* hist = nullptr;
+            RC(talloc(ctx, &cand2, ccap));
+            RC(talloc(ctx, &hist, (int64_t)CAND_BUCKETS * CAND_PAD));
+            const int shift = std::max(0, bits_for(s1->arena) - CAND_BUCKET_BITS);
+            CU(cudaMemsetAsync(hist, 0, (size_t)CAND_BUCKETS * CAND_PAD * sizeof(uint32_t), ctx->stream));
+            LAUNCH(ctx, k_cand_hist, RCQ_SMS * 4, 256, 0, cand, ccap, ctr, shift, hist);
+            LAUNCH(ctx, k_cand_scan, 1, 1024, 0, hist);
+            LAUNCH(ctx, k_cand_scatter, RCQ_SMS * 8, 256, 0, cand, ccap, ctr, shift, hist, cand2);
+            tfree(ctx, cand); tfree(ctx, hist);
+            cand = cand2;
+        }
         LAUNCH(ctx, k_seed_verify, RCQ_SMS * 16, 256, 0, cand, ccap, P, seeds, cap, ctr);
         stage_toc(ctx, 1);
         RC(read_counters(ctx, 3));

@@ -162,6 +162,62 @@ __global__ void __launch_bounds__(PROBE_THREADS) k_seed_probe(
     }
 }
 
+// ---- between probe and verify: candidates leave the probe in index-key order, i.e. at random positions of both
+// samples, and the verify gathers about ten 32-byte sectors per candidate.  Three small kernels put them into
+// CAND_BUCKETS buckets by their position in sample A (counting sort on the top bits of pA; order inside a bucket is
+// whatever the atomics give, no result depends on it), so that neighbouring threads of the verify read neighbouring
+// bases, masks and index bits of A - and of B wherever the two samples list their genes in the same order.  The
+// candidate count stays on the device (counters[1]).
+#define CAND_BUCKET_BITS 12
+#define CAND_BUCKETS (1 << CAND_BUCKET_BITS)
+#define CAND_PAD 32            // one counter per 128-byte line: atomics of different buckets never share a line
+__global__ void __launch_bounds__(256) k_cand_hist(const uint2* __restrict__ cand, int64_t cand_cap,
+                                                   const unsigned long long* __restrict__ counters, int shift,
+                                                   uint32_t* __restrict__ hist) {
+    __shared__ uint32_t h[CAND_BUCKETS];
+    for (int i = threadIdx.x; i < CAND_BUCKETS; i += blockDim.x) h[i] = 0;
+    __syncthreads();
+    const int64_t n_cand = min((int64_t)counters[1], cand_cap);
+    for (int64_t x = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; x < n_cand; x += (int64_t)gridDim.x * blockDim.x)
+        atomicAdd(&h[(__ldg(&cand[x].x) >> 1) >> shift], 1u);
+    __syncthreads();
+    for (int i = threadIdx.x; i < CAND_BUCKETS; i += blockDim.x)
+        if (h[i]) atomicAdd(hist + (size_t)i * CAND_PAD, h[i]);
+}
+// counts -> exclusive start offsets, one block of 1024 threads
+__global__ void __launch_bounds__(1024) k_cand_scan(uint32_t* __restrict__ hist) {
+    __shared__ uint32_t wsum[32];
+    constexpr int PER = CAND_BUCKETS / 1024;
+    uint32_t v[PER], tot = 0;
+#pragma unroll
+    for (int r = 0; r < PER; r++) { v[r] = hist[(size_t)(threadIdx.x * PER + r) * CAND_PAD]; tot += v[r]; }
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    uint32_t incl = tot;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
+    if (lane == 31) wsum[w] = incl;
+    __syncthreads();
+    if (w == 0) {
+        uint32_t x = wsum[lane], i2 = x;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, i2, o); if (lane >= o) i2 += y; }
+        wsum[lane] = i2 - x;
+    }
+    __syncthreads();
+    uint32_t run = wsum[w] + incl - tot;
+#pragma unroll
+    for (int r = 0; r < PER; r++) { hist[(size_t)(threadIdx.x * PER + r) * CAND_PAD] = run; run += v[r]; }
+}
+__global__ void __launch_bounds__(256) k_cand_scatter(const uint2* __restrict__ cand, int64_t cand_cap,
+                                                      const unsigned long long* __restrict__ counters, int shift,
+                                                      uint32_t* __restrict__ offs, uint2* __restrict__ out) {
+    const int64_t n_cand = min((int64_t)counters[1], cand_cap);
+    for (int64_t x = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; x < n_cand; x += (int64_t)gridDim.x * blockDim.x) {
+        const uint2 c = __ldg(cand + x);
+        out[atomicAdd(offs + (size_t)((c.x >> 1) >> shift) * CAND_PAD, 1u)] = c;
+    }
+}
+
 // ---- phase 2: verify.  Thread per candidate (grid-stride).  A candidate survives when the two
 // 16-mers are equal on the implied strand, the exact run through them is >= 28 long, and it is
 // the leftmost position of that run indexed in BOTH samples.  Every window of 13 consecutive
