@@ -65,6 +65,15 @@ int64_t rcq_top_gene_mask(const double* coverage, const int32_t* gene, int64_t n
 int rcq_fasta_scan(const uint8_t* raw, int64_t n, int64_t* n_records, int64_t* n_letters);
 int rcq_fasta_parse(const uint8_t* raw, int64_t n, uint8_t* ascii_out, int64_t* offsets,
                     int64_t* hdr_start, int64_t* hdr_end);
+/* Lean ingest for a caller that keeps only some records (the top-gene selection of select_top_genes.py:108-127
+ * needs the ids of all records but the letters of the selected ones): rcq_fasta_headers = header spans of every
+ * record without touching the sequence bytes (n_records from rcq_fasta_scan); rcq_fasta_extract = the letters
+ * (LF, CR, spaces removed) of the records keep[0 .. n_keep) concatenated into out[cap], out_off[n_keep + 1] their
+ * offsets; returns the number of letters, or -1 with the error set. */
+int rcq_fasta_headers(const uint8_t* raw, int64_t n, int64_t n_records, int64_t* hdr_start, int64_t* hdr_end);
+int64_t rcq_fasta_extract(const uint8_t* raw, int64_t n, const int64_t* hdr_start, const int64_t* hdr_end,
+                          int64_t n_records, const int64_t* keep, int64_t n_keep, uint8_t* out, int64_t cap,
+                          int64_t* out_off);
 /* FASTA text of selected records ('>' header LF, `width` letters per line, as Bio.SeqIO.write does for
  * od1/<sample>_top.fasta, select_top_genes_all.py:37-45); out == NULL returns the size only. */
 int64_t rcq_fasta_format(const uint8_t* ascii, const int64_t* starts, const int64_t* lengths, int64_t n,
@@ -197,6 +206,14 @@ int rcq_debug_keep_hsps(rcq_ctx* ctx, int on);
 /* Karlin-Altschul helpers shared by the host layer (blastn 1/-2 linear-gap parameters):
  * length adjustment and evalue of a raw score for query length m against a db (n bases, nseq). */
 int32_t rcq_length_adjustment(int64_t m, int64_t n, int64_t nseq);
+/* pident / evalue / bitscore of every row of a table as blastn's tabular output prints them (the reference parses
+ * them from that text, find_homologs.py:124-125): host code, one pass over the integer columns of
+ * rcq_table_download; forward rows (reverse == 0) use the statistics of the database (bases_fwd, seqs_fwd) =
+ * sample 1, backward rows those of sample 2.  ln_k, ln_2: log(0.46), log(2) as the caller computes them. */
+int rcq_table_stats(int64_t n, const int32_t* score, const int32_t* qlen, const uint8_t* reverse,
+                    const int32_t* nident, const int32_t* length, int64_t bases_fwd, int64_t seqs_fwd,
+                    int64_t bases_bwd, int64_t seqs_bwd, double ln_k, double ln_2, double* pident,
+                    double* evalue, double* bitscore);
 double rcq_evalue(int32_t score, int64_t m, int64_t n, int64_t nseq);
 double rcq_bitscore(int32_t score);
 

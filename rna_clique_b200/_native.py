@@ -20,10 +20,10 @@ HSP_COLS = ["tx1", "tx2", "minus", "a0", "a1", "b0", "b1", "score2", "mismatch",
 # every symbol include/rcq.h declares (checked by tests/test_abi.py)
 SYMBOLS = [
     "rcq_last_error", "rcq_version", "rcq_ctx_create", "rcq_ctx_destroy", "rcq_ctx_sync", "rcq_ctx_stream",
-    "rcq_ctx_launches", "rcq_ctx_stage_times", "rcq_top_gene_mask", "rcq_fasta_scan", "rcq_fasta_parse", "rcq_parse_spades_ids", "rcq_fasta_format", "rcq_graph_pickle", "rcq_graph_pickle_groups", "rcq_matrix_h5_write", "rcq_sample_create", "rcq_sample_free", "rcq_sample_info", "rcq_sample_download",
+    "rcq_ctx_launches", "rcq_ctx_stage_times", "rcq_top_gene_mask", "rcq_fasta_scan", "rcq_fasta_parse", "rcq_fasta_headers", "rcq_fasta_extract", "rcq_parse_spades_ids", "rcq_fasta_format", "rcq_graph_pickle", "rcq_graph_pickle_groups", "rcq_matrix_h5_write", "rcq_sample_create", "rcq_sample_free", "rcq_sample_info", "rcq_sample_download",
     "rcq_ctx_set_dust", "rcq_sample_seed_mask", "rcq_dust_mask_static", "rcq_int32_issue_peak",
     "rcq_search_pair", "rcq_table_rows", "rcq_table_download", "rcq_table_free", "rcq_debug_last_hsps", "rcq_debug_keep_hsps",
-    "rcq_length_adjustment", "rcq_evalue", "rcq_bitscore", "rcq_phase2_host", "rcq_phase2_tables", "rcq_phase2_pack", "rcq_phase2_packed",
+    "rcq_length_adjustment", "rcq_table_stats", "rcq_evalue", "rcq_bitscore", "rcq_phase2_host", "rcq_phase2_tables", "rcq_phase2_pack", "rcq_phase2_packed",
     "rcq_table_flat_words", "rcq_table_flatten", "rcq_table_from_flat", "rcq_sample_meta", "rcq_sample_export", "rcq_sample_import",
 ]
 
@@ -90,6 +90,9 @@ def lib():
         L.rcq_debug_last_hsps.restype = i64
         L.rcq_fasta_scan.argtypes = [vp, i64, vp, vp]
         L.rcq_fasta_parse.argtypes = [vp, i64, vp, vp, vp, vp]
+        L.rcq_fasta_headers.argtypes = [vp, i64, i64, vp, vp]
+        L.rcq_fasta_extract.argtypes = [vp, i64, vp, vp, i64, vp, i64, vp, i64, vp]
+        L.rcq_fasta_extract.restype = i64
         L.rcq_parse_spades_ids.argtypes = [vp, vp, vp, i64, vp, vp, vp]
         L.rcq_parse_spades_ids.restype = i64
         L.rcq_fasta_format.argtypes = [vp, vp, vp, i64, vp, vp, C.c_int32, vp]
@@ -103,6 +106,7 @@ def lib():
         L.rcq_debug_keep_hsps.restype = C.c_int
         L.rcq_length_adjustment.argtypes = [i64, i64, i64]
         L.rcq_length_adjustment.restype = i32
+        L.rcq_table_stats.argtypes = [i64, vp, vp, vp, vp, vp, i64, i64, i64, i64, dbl, dbl, vp, vp, vp]
         L.rcq_evalue.argtypes = [i32, i64, i64, i64]
         L.rcq_evalue.restype = dbl
         L.rcq_bitscore.argtypes = [i32]
@@ -326,6 +330,32 @@ def fasta_parse(raw: np.ndarray):
     check(lib().rcq_fasta_parse(raw.ctypes.data, len(raw), ascii_.ctypes.data, offsets.ctypes.data, hs.ctypes.data, he.ctypes.data))
     ascii_ = ascii_[:int(offsets[n])]
     return ascii_, offsets, hs, he
+
+
+def fasta_headers(raw: np.ndarray):
+    """(hdr_start int64[n], hdr_end int64[n]) of FASTA bytes: the header line of every record, sequence bytes untouched."""
+    cnt = np.zeros(2, dtype=np.int64)
+    check(lib().rcq_fasta_scan(raw.ctypes.data, len(raw), cnt.ctypes.data, cnt.ctypes.data + 8))
+    n = int(cnt[0])
+    hs, he = np.zeros(n, dtype=np.int64), np.zeros(n, dtype=np.int64)
+    check(lib().rcq_fasta_headers(raw.ctypes.data, len(raw), n, hs.ctypes.data, he.ctypes.data))
+    return hs, he
+
+
+def fasta_extract(raw: np.ndarray, hs: np.ndarray, he: np.ndarray, keep: np.ndarray, alloc=None):
+    """Letters of the records `keep` (ascending record numbers): (uint8 buffer holding them, offsets int64[len(keep)+1]).
+    alloc(nbytes) -> uint8 array of at least that size (e.g. pinned memory); numpy.empty by default."""
+    keep = np.ascontiguousarray(keep, dtype=np.int64)
+    nxt = np.append(hs[1:], len(raw))
+    bound = int((nxt[keep] - he[keep]).sum()) if len(keep) else 0
+    out = (alloc or (lambda b: np.empty(b, dtype=np.uint8)))(max(bound, 1))
+    off = np.zeros(len(keep) + 1, dtype=np.int64)
+    L = lib()
+    tot = L.rcq_fasta_extract(raw.ctypes.data, len(raw), hs.ctypes.data, he.ctypes.data, len(hs), keep.ctypes.data, len(keep),
+                              out.ctypes.data, len(out), off.ctypes.data)
+    if tot < 0:
+        raise RuntimeError(L.rcq_last_error().decode())
+    return out[:max(int(tot), 1)], off
 
 
 def fasta_format(ascii_: np.ndarray, starts, lengths, headers, width: int = 60) -> np.ndarray:

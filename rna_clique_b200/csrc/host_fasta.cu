@@ -53,6 +53,61 @@ extern "C" int rcq_fasta_parse(const uint8_t* raw, int64_t n, uint8_t* ascii_out
     return 0;
 }
 
+// Lean ingest for callers that keep only some records (top-gene selection): the header spans of every record
+// without touching the sequence bytes (records are found by hopping from '>' to '>' like rcq_fasta_scan; n_records
+// is that call's count) ...
+extern "C" int rcq_fasta_headers(const uint8_t* raw, int64_t n, int64_t n_records, int64_t* hdr_start, int64_t* hdr_end) {
+    if (n < 0 || n_records < 0 || (n > 0 && !raw) || (n_records && (!hdr_start || !hdr_end)))
+        return rcq_fail(RCQ_ERR_ARG, "rcq_fasta_headers: bad argument");
+    int64_t rec = 0, p = 0;
+    while (p < n) {
+        const uint8_t* gt = (const uint8_t*)memchr(raw + p, '>', (size_t)(n - p));
+        if (!gt) break;
+        const int64_t at = (int64_t)(gt - raw);
+        if (at == 0 || raw[at - 1] == '\n') {
+            const uint8_t* nl = (const uint8_t*)memchr(gt, '\n', (size_t)(n - at));
+            const int64_t e = nl ? (int64_t)(nl - raw) : n;
+            if (rec >= n_records) return rcq_fail(RCQ_ERR_ARG, "rcq_fasta_headers: more records than announced");
+            hdr_start[rec] = at; hdr_end[rec] = e; rec++;
+            p = e + 1;
+        } else p = at + 1;
+    }
+    if (rec != n_records) return rcq_fail(RCQ_ERR_ARG, "rcq_fasta_headers: fewer records than announced");
+    return 0;
+}
+// ... and the letters (LF, CR and spaces removed) of the records keep[0 .. n_keep) only, concatenated into out
+// (capacity cap bytes; the sequence bytes of a record are a safe bound of its letters), out_off[k] = letters
+// before keep[k], out_off[n_keep] = total.  Returns the total, or -1 (error set) when cap is too small.
+extern "C" int64_t rcq_fasta_extract(const uint8_t* raw, int64_t n, const int64_t* hdr_start, const int64_t* hdr_end,
+                                     int64_t n_records, const int64_t* keep, int64_t n_keep, uint8_t* out, int64_t cap,
+                                     int64_t* out_off) {
+    if (n < 0 || n_records < 0 || n_keep < 0 || (n > 0 && !raw) || (n_records && (!hdr_start || !hdr_end)) ||
+        (n_keep && (!keep || !out)) || !out_off) {
+        rcq_fail(RCQ_ERR_ARG, "rcq_fasta_extract: bad argument");
+        return -1;
+    }
+    int64_t let = 0;
+    for (int64_t k = 0; k < n_keep; k++) {
+        const int64_t r = keep[k];
+        if (r < 0 || r >= n_records) { rcq_fail(RCQ_ERR_ARG, "rcq_fasta_extract: record index out of range"); return -1; }
+        out_off[k] = let;
+        int64_t p = hdr_end[r] + 1;
+        const int64_t end = r + 1 < n_records ? hdr_start[r + 1] : n;
+        if (end - p > cap - let) { rcq_fail(RCQ_ERR_CAPACITY, "rcq_fasta_extract: output buffer too small"); return -1; }
+        while (p < end) {
+            const uint8_t* nl = (const uint8_t*)memchr(raw + p, '\n', (size_t)(end - p));
+            const int64_t e = nl ? (int64_t)(nl - raw) : end;
+            const uint8_t* a = raw + p;
+            const int64_t len = e - p;
+            if (!memchr(a, '\r', (size_t)len) && !memchr(a, ' ', (size_t)len)) { memcpy(out + let, a, (size_t)len); let += len; }
+            else for (int64_t i = 0; i < len; i++) if (!is_skip(a[i])) out[let++] = a[i];
+            p = e + 1;
+        }
+    }
+    out_off[n_keep] = let;
+    return let;
+}
+
 // id = first whitespace-separated token of the header text raw[hdr_start+1 .. hdr_end)
 static inline void id_span(const uint8_t* raw, int64_t a, int64_t b, int64_t* s, int64_t* e) {
     auto ws = [](uint8_t c) { return c == ' ' || (c >= 9 && c <= 13) || (c >= 28 && c <= 31); };

@@ -67,6 +67,48 @@ extern "C" double rcq_evalue(int32_t score, int64_t m, int64_t n, int64_t nseq) 
 }
 extern "C" double rcq_bitscore(int32_t score) { return (RCQ_KA_LAMBDA * score - log(RCQ_KA_K)) / log(2.0); }
 
+// The three floating-point columns of a gene-matches table as blastn prints them and simple_blast parses them
+// back (find_homologs.py:124-125 reads them from the tabular output): pident = 100 nident / length to three
+// decimals; evalue = K m' n' exp(-lambda S) with the length adjustment of the row's direction, printed as 0.0
+// below 1e-180, with three significant digits below 0.0009, in BLAST's fixed formats above; bitscore truncated to
+// an integer above 99.9 bits, one decimal below.  Host code, one pass; the same arithmetic, in the same order, as
+// find_homologs.table_stats_numpy (tests compare the two).  ln_k, ln_2: the caller's log(K), log(2).
+extern "C" int rcq_table_stats(int64_t n, const int32_t* score, const int32_t* qlen, const uint8_t* reverse,
+                               const int32_t* nident, const int32_t* length, int64_t bases_fwd, int64_t seqs_fwd,
+                               int64_t bases_bwd, int64_t seqs_bwd, double ln_k, double ln_2, double* pident,
+                               double* evalue, double* bitscore) {
+    if (n < 0 || (n && (!score || !qlen || !reverse || !nident || !length || !pident || !evalue || !bitscore)))
+        return rcq_fail(RCQ_ERR_ARG, "rcq_table_stats: bad argument");
+    int32_t last_q[2] = {-1, -1};
+    double last_la[2] = {0, 0};
+    for (int64_t i = 0; i < n; i++) {
+        const int r = reverse[i] ? 1 : 0;
+        if (qlen[i] != last_q[r]) {          // rows come grouped by query gene: the adjustment rarely changes
+            last_q[r] = qlen[i];
+            last_la[r] = (double)length_adjustment((double)qlen[i], (double)(r ? bases_bwd : bases_fwd), (double)(r ? seqs_bwd : seqs_fwd));
+        }
+        const double la = last_la[r];
+        const double nb = (double)(r ? bases_bwd : bases_fwd), ns = (double)(r ? seqs_bwd : seqs_fwd);
+        double em = (double)qlen[i] - la, en = nb - ns * la;
+        if (em < 1.0) em = 1.0;
+        if (en < 1.0) en = 1.0;
+        const double e = RCQ_KA_K * em * en * exp(-RCQ_KA_LAMBDA * (double)score[i]);
+        double pe;
+        if (e < 1e-180) pe = 0.0;
+        else if (e < 0.0009) { char buf[40]; snprintf(buf, sizeof buf, "%.2e", e); pe = strtod(buf, nullptr); }
+        else if (e < 0.1) pe = nearbyint(e * 1000.0) / 1000.0;
+        else if (e < 1.0) pe = nearbyint(e * 100.0) / 100.0;
+        else if (e < 10.0) pe = nearbyint(e * 10.0) / 10.0;
+        else pe = nearbyint(e);
+        evalue[i] = pe;
+        const double b = (RCQ_KA_LAMBDA * (double)score[i] - ln_k) / ln_2;
+        bitscore[i] = b > 99.9 ? floor(b) : nearbyint(b * 10.0) / 10.0;
+        const int32_t len = length[i] > 1 ? length[i] : 1;
+        pident[i] = nearbyint(100.0 * (double)nident[i] / (double)len * 1000.0) / 1000.0;
+    }
+    return 0;
+}
+
 struct SelView {
     const Gapped* G; int64_t n;
     const int32_t *lenA, *lenB, *gidxA, *gidxB;

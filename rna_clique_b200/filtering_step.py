@@ -18,7 +18,6 @@ from __future__ import annotations
 import itertools
 import os
 import threading
-from concurrent.futures import ThreadPoolExecutor
 from pathlib import Path
 from typing import Callable, Iterable, Optional
 
@@ -30,7 +29,7 @@ from .filtered_distance import SampleSimilarity
 from .find_all_pairs import _label_and_save, make_output_path
 from .find_homologs import table_to_frame
 from .gene_matches_tables import default_extension
-from .select_top_genes import _parse_and_select
+from .select_top_genes import _parse_and_select_lean
 from .transcripts import default_parser
 
 _engine = None
@@ -54,6 +53,102 @@ def close_shared_engine() -> None:
         if _engine is not None:
             _engine.close()
             _engine = None
+    _pinned.clear()
+
+
+class _PinnedPool:
+    """Page-locked host buffers for the letters on their way to the device, kept between samples and between calls
+    (cudaHostAlloc of 100 MB costs tens of milliseconds, the copy from it 4 ms; from pageable memory it costs 40).
+    Beyond `limit` bytes in use the letters go through ordinary numpy memory."""
+
+    def __init__(self, limit: int = 6 << 30):
+        self.lock = threading.Lock()
+        self.free = []            # torch uint8 tensors, pinned
+        self.out = {}             # id(numpy base) -> tensor
+        self.held = 0
+        self.limit = limit
+
+    def get(self, nbytes: int) -> np.ndarray:
+        import torch
+        with self.lock:
+            best = None
+            for k, t in enumerate(self.free):
+                if t.numel() >= nbytes and (best is None or t.numel() < self.free[best].numel()):
+                    best = k
+            t = self.free.pop(best) if best is not None else None
+            if t is None and self.held + nbytes > self.limit:
+                return np.empty(nbytes, dtype=np.uint8)
+            if t is None:
+                cap = (nbytes + (16 << 20) - 1) >> 24 << 24
+                self.held += cap
+        if t is None:
+            try:
+                t = torch.empty(cap, dtype=torch.uint8, pin_memory=True)
+            except RuntimeError:
+                with self.lock:
+                    self.held -= cap
+                return np.empty(nbytes, dtype=np.uint8)
+        a = t.numpy()
+        with self.lock:
+            self.out[a.ctypes.data] = t
+        return a
+
+    def put(self, a: np.ndarray) -> None:
+        """a: the array get() returned, or a view that starts at its first byte."""
+        with self.lock:
+            t = self.out.pop(a.ctypes.data, None)
+            if t is not None:
+                self.free.append(t)
+
+    def clear(self) -> None:
+        with self.lock:
+            self.free.clear()
+            self.out.clear()
+            self.held = 0
+
+
+_pinned = _PinnedPool()
+
+
+class _PriorityPool:
+    """Host threads that always take the most urgent task first: parsing a transcriptome (a search is waiting for
+    it) before writing od1/ files before turning finished tables into od2/ files.  With one FIFO queue a parse
+    submitted late waited behind dozens of table tasks while the GPU ran out of resident samples."""
+
+    def __init__(self, workers: int):
+        import queue
+        from concurrent.futures import Future
+        self._Future = Future
+        self.q = queue.PriorityQueue()
+        self.seq = itertools.count()
+        self.threads = [threading.Thread(target=self._run, daemon=True) for _ in range(workers)]
+        for t in self.threads:
+            t.start()
+
+    def _run(self):
+        while True:
+            _, _, item = self.q.get()
+            if item is None:
+                return
+            fut, fn, args = item
+            if not fut.set_running_or_notify_cancel():
+                continue
+            try:
+                fut.set_result(fn(*args))
+            except BaseException as e:      # noqa: BLE001 - handed to whoever asks for the result
+                fut.set_exception(e)
+
+    def submit(self, priority: int, fn, *args):
+        fut = self._Future()
+        self.q.put((priority, next(self.seq), (fut, fn, args)))
+        return fut
+
+    def shutdown(self, wait: bool = True):
+        for _ in self.threads:
+            self.q.put((1 << 30, next(self.seq), None))
+        if wait:
+            for t in self.threads:
+                t.join()
 
 
 def _frame_and_save(cols, db, t1, t2, out_path):
@@ -85,7 +180,12 @@ def filtering_step(dirs: Iterable[Path], out_dir_1: Path, out_dir_2: Path, cache
     tables = [None] * len(pairs)
     edges = [None] * len(pairs)
     writes = [None] * len(pairs)
-    host = ThreadPoolExecutor(workers)
+    host = _PriorityPool(workers)
+    # the engine workers need the interpreter lock only for microseconds between native calls, the host pool holds it
+    # for whole pandas operations: a short switch interval keeps the GPU from waiting for the lock
+    import sys
+    switch = sys.getswitchinterval()
+    sys.setswitchinterval(min(switch, 0.0002))
     try:
         # at most `window` parsed files are alive (a parsed 100,000-transcript file is ~0.4 GB of host memory)
         window = workers + 2
@@ -95,11 +195,28 @@ def filtering_step(dirs: Iterable[Path], out_dir_1: Path, out_dir_2: Path, cache
 
         od1_writes = [None] * n
 
+        uses = {}                 # sample -> users of its letter buffer still running (upload, od1 write)
+
+        def release(k, letters):
+            with lock:
+                uses[k] -= 1
+                last = uses[k] == 0
+            if last:
+                _pinned.put(letters)
+
         def parse_task(k):
-            # the device needs the selected records only: od1/<sample>_top.fasta is formatted and written as a task
-            # of its own, behind the parses already queued
-            out, stem, rec, write = _parse_and_select(out_dir_1, transcripts, dirs[k], top_genes, id_parser)
-            od1_writes[k] = host.submit(write)
+            # the device needs the selected records only, in page-locked memory: od1/<sample>_top.fasta is formatted
+            # and written from the same buffer as a task of its own, behind the parses already queued
+            out, stem, rec, write = _parse_and_select_lean(out_dir_1, transcripts, dirs[k], top_genes, id_parser, _pinned.get)
+            uses[k] = 2
+
+            def write_and_release():
+                try:
+                    write()
+                finally:
+                    release(k, rec[1])
+
+            od1_writes[k] = host.submit(1, write_and_release)
             return out, stem, rec
 
         def submit_parse():
@@ -108,7 +225,7 @@ def filtering_step(dirs: Iterable[Path], out_dir_1: Path, out_dir_2: Path, cache
                 if k >= n:
                     return
                 state["next"] = k + 1
-                parsed[k] = host.submit(parse_task, k)
+                parsed[k] = host.submit(0, parse_task, k)
 
         for _ in range(min(window, n)):
             submit_parse()
@@ -132,7 +249,10 @@ def filtering_step(dirs: Iterable[Path], out_dir_1: Path, out_dir_2: Path, cache
             kind, x = task
             if kind == "u":
                 out, _, rec = parsed.pop(x).result()
-                samples[x] = _native.Sample(ctx, rec[1], rec[2], rec[3], rec[4], name=str(out), lengths=rec[5])
+                try:
+                    samples[x] = _native.Sample(ctx, rec[1], rec[2], rec[3], rec[4], name=str(out), lengths=rec[5])
+                finally:
+                    release(x, rec[1])
                 del rec
                 submit_parse()
                 return
@@ -142,7 +262,7 @@ def filtering_step(dirs: Iterable[Path], out_dir_1: Path, out_dir_2: Path, cache
             cols = t.download()
             tables[x] = t
             edges[x] = (cols["sgene"], cols["qgene"])
-            writes[x] = host.submit(_frame_and_save, cols, (s1.total, s1.n_seq, s2.total, s2.n_seq),
+            writes[x] = host.submit(2, _frame_and_save, cols, (s1.total, s1.n_seq, s2.total, s2.n_seq),
                                     out_paths[i], out_paths[j], table_paths[x])
 
         eng._run_tasks(tasks, ready, run, poll=0.0005)
@@ -165,6 +285,7 @@ def filtering_step(dirs: Iterable[Path], out_dir_1: Path, out_dir_2: Path, cache
             print(f"[filtering_step] parse+upload+search {t_1 - t_0:.3f} s, graph {t_2 - t_1:.3f} s, "
                   f"waiting for table files {time.perf_counter() - t_2:.3f} s", file=__import__("sys").stderr)
     finally:
+        sys.setswitchinterval(switch)
         host.shutdown(wait=True)
         for s in samples:
             if s is not None:

@@ -116,17 +116,14 @@ def blast_printed_evalue(e: np.ndarray) -> np.ndarray:
     return out
 
 
-def table_to_frame(cols: dict, n_db_bases_fwd: int, n_db_seqs_fwd: int, n_db_bases_bwd: int,
-                   n_db_seqs_bwd: int) -> pd.DataFrame:
-    """Device columns -> the reference's DataFrame.  pident / evalue / bitscore are derived here in
-    fp64 from the integer columns (blastn tabular semantics: pident = 100 nident / length;
-    bitscore printed as an integer above 99.9 bits)."""
+def table_stats_numpy(cols: dict, n_db_bases_fwd: int, n_db_seqs_fwd: int, n_db_bases_bwd: int, n_db_seqs_bwd: int):
+    """(pident, evalue, bitscore) as rcq_table_stats computes them, written with numpy (tests compare the two).
+    Karlin-Altschul statistics; the length adjustment depends only on (query length,
+    direction), so it is evaluated once per distinct value."""
     n = len(cols["length"])
     L = _native.lib()
-    rev = cols["reverse"].astype(bool)
+    rev = np.asarray(cols["reverse"]).astype(bool)
     score, qlen = cols["score"], cols["qlen"]
-    # Karlin-Altschul statistics (DESIGN.md §3.5); the length adjustment depends only on
-    # (query length, direction), so it is evaluated once per distinct value
     key = qlen.astype(np.int64) * 2 + rev
     uk, inv = np.unique(key, return_inverse=True)
     la = np.array([L.rcq_length_adjustment(int(k >> 1), *((n_db_bases_bwd, n_db_seqs_bwd) if k & 1 else
@@ -137,10 +134,27 @@ def table_to_frame(cols: dict, n_db_bases_fwd: int, n_db_seqs_fwd: int, n_db_bas
     evalue = KA_K * np.maximum(qlen - la, 1.0) * np.maximum(nb - ns * la, 1.0) * np.exp(-KA_LAMBDA * score.astype(np.float64))
     evalue = blast_printed_evalue(evalue)
     bits = blast_printed_bitscore((KA_LAMBDA * score - np.log(KA_K)) / np.log(2.0))
+    return np.round(100.0 * cols["nident"] / np.maximum(cols["length"], 1), 3), evalue, bits
+
+
+def table_to_frame(cols: dict, n_db_bases_fwd: int, n_db_seqs_fwd: int, n_db_bases_bwd: int,
+                   n_db_seqs_bwd: int) -> pd.DataFrame:
+    """Device columns -> the reference's DataFrame.  pident / evalue / bitscore are derived here in
+    fp64 from the integer columns (blastn tabular semantics: pident = 100 nident / length;
+    bitscore printed as an integer above 99.9 bits)."""
+    n = len(cols["length"])
+    pident, evalue, bits = np.empty(n), np.empty(n), np.empty(n)
+    c32 = {c: np.ascontiguousarray(cols[c], dtype=np.int32) for c in ("score", "qlen", "nident", "length")}
+    rev8 = np.ascontiguousarray(cols["reverse"], dtype=np.uint8)
+    _native.check(_native.lib().rcq_table_stats(n, c32["score"].ctypes.data, c32["qlen"].ctypes.data, rev8.ctypes.data,
+                                                c32["nident"].ctypes.data, c32["length"].ctypes.data, int(n_db_bases_fwd),
+                                                int(n_db_seqs_fwd), int(n_db_bases_bwd), int(n_db_seqs_bwd), float(np.log(KA_K)),
+                                                float(np.log(2.0)), pident.ctypes.data, evalue.ctypes.data, bits.ctypes.data))
+    rev = rev8.astype(bool)
     ic = {c: _smallest_int(np.asarray(cols[c])) for c in _INT_COLS}      # shrink_df, before the frame is built
     strands = pd.Series(["plus", "minus"])                                  # the frame's own string dtype
     df = pd.DataFrame({
-        "pident": np.round(100.0 * cols["nident"] / np.maximum(cols["length"], 1), 3),
+        "pident": pident,
         "length": ic["length"], "mismatch": ic["mismatch"], "gapopen": ic["gapopen"],
         "qstart": ic["qstart"], "qend": ic["qend"], "sstart": ic["sstart"], "send": ic["send"],
         "evalue": evalue, "bitscore": bits, "gaps": ic["gaps"], "nident": ic["nident"],

@@ -86,6 +86,40 @@ def _parse_and_select(out_dir: Path, transcripts: str, x: Path, *args):
                          lengths.astype(np.int32)), write
 
 
+def _parse_and_select_lean(out_dir: Path, transcripts: str, x: Path, top: int, parser=default_parser, alloc=None):
+    """_parse_and_select for the default id pattern without reading what is thrown away: the file is mapped, not
+    copied; ids come from the header lines; only the letters of the selected records are extracted, into a buffer
+    from alloc(nbytes) (pinned memory in the pipeline, so that the upload is one DMA transfer).  Falls back to
+    _parse_and_select for any other parser and for empty files."""
+    from . import _native
+    from .transcripts import TranscriptIDParseError, default_gene_re
+    x = Path(x)
+    path = x / transcripts
+    pat = getattr(parser, "pattern", None)
+    is_default = parser is default_parser or (pat is not None and pat.pattern == default_gene_re.pattern and pat.flags == default_gene_re.flags)
+    if not is_default or path.stat().st_size == 0:
+        return _parse_and_select(out_dir, transcripts, x, top, parser)
+    out = Path(out_dir) / (x.stem + "_top.fasta")
+    raw = np.memmap(str(path), dtype=np.uint8, mode="r")
+    hs, he = _native.fasta_headers(raw)
+    if len(hs) == 0:
+        return _parse_and_select(out_dir, transcripts, x, top, parser)
+    cov, gene, iso, bad = _native.parse_spades_ids(raw, hs, he)
+    if bad >= 0:
+        fa = Fasta(None, np.zeros(0, np.uint8), np.zeros(len(hs) + 1, np.int64), raw, hs, he)
+        raise TranscriptIDParseError(f"Could not parse transcript ID {fa.ids[bad]}.")
+    keep = top_gene_mask(cov, gene, top)
+    letters, off = _native.fasta_extract(raw, hs, he, keep, alloc)
+    starts, lengths = off[:-1], np.diff(off)
+
+    def write():
+        fa = Fasta(None, letters, off, raw, hs, he)
+        write_fasta(out, fa.header_bytes(keep), letters, starts, lengths)
+
+    return out, x.stem, (parser, letters, starts, np.asarray(gene[keep], dtype=np.int32), np.asarray(iso[keep], dtype=np.int32),
+                         lengths.astype(np.int32)), write
+
+
 def _select_and_write(out_dir: Path, transcripts: str, x: Path, *args):
     """Host half of select_top_and_save (thread-safe: no device work): returns (out path, x.stem, records),
     records = (parser, letters, starts, gene, iso, lengths) of what was written."""

@@ -95,3 +95,30 @@ def test_length_adjustment_hand_computed():
     # the size of a 50,000-gene rnaSPAdes top set (here: m = 1900, n = 2.12e8, N = 105,000 gives 8.7e-152)
     e = _native.lib().rcq_evalue(292, 1900, 212_000_000, 105_000)
     assert 5e-152 < e < 1.5e-151
+
+
+def test_native_table_statistics_equal_the_numpy_statement():
+    """rcq_table_stats (what table_to_frame calls) against find_homologs.table_stats_numpy on rows that reach every
+    printing branch: e-values below 1e-180, between 1e-180 and 0.0009, and up to tens; bit scores on both sides of
+    99.9; both directions with different database sizes."""
+    import numpy as np
+    from rna_clique_b200 import find_homologs as fh
+    rng = np.random.default_rng(1)
+    n = 60000
+    score = np.concatenate([rng.integers(8, 60, size=n // 3), rng.integers(60, 400, size=n // 3), rng.integers(400, 4200, size=n - 2 * (n // 3))]).astype(np.int32)
+    rng.shuffle(score)
+    length = rng.integers(28, 4200, size=n).astype(np.int32)
+    cols = dict(score=score, qlen=np.repeat(rng.integers(30, 9000, size=n // 4), 4).astype(np.int32), length=length,
+                nident=(length - rng.integers(0, 28, size=n)).astype(np.int32), reverse=(rng.integers(0, 2, size=n)).astype(np.uint8))
+    for k in ("mismatch", "gapopen", "qstart", "qend", "sstart", "send", "gaps", "qgene", "qiso", "sgene", "siso"):
+        cols[k] = rng.integers(0, 300, size=n).astype(np.int32)
+    cols["minus"] = rng.integers(0, 2, size=n).astype(np.uint8)
+    for db in ((102500000, 50000, 99000000, 48000), (12000, 7, 3000000, 900)):
+        want = fh.table_stats_numpy(cols, *db)
+        df = fh.table_to_frame(cols, *db)
+        assert np.array_equal(df["pident"].to_numpy(), want[0])
+        assert np.array_equal(df["evalue"].to_numpy(), want[1])
+        assert np.array_equal(df["bitscore"].to_numpy(), want[2])
+        e = want[1]
+        assert (e == 0).any() and ((e > 0) & (e < 0.0009)).any() and (e > 0.0009).any()
+        assert (want[2] < 99.9).any() and (want[2] > 99.9).any()

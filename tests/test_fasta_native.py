@@ -72,3 +72,55 @@ def test_write_fasta_native_equals_python(tmp_path):
         assert (tmp_path / "a.fa").read_bytes() == (tmp_path / "b.fa").read_bytes()
     back = read_fasta(tmp_path / "a.fa")
     assert back.headers == headers and np.array_equal(np.diff(back.offsets), lens)
+
+
+def test_lean_parse_equals_the_full_parse(tmp_path):
+    """_parse_and_select_lean (mapped file, header spans, letters of the selected records only) hands on the same
+    records and writes the same od1 file as the full parse - CRLF line ends, spaces inside sequence lines, ragged
+    line lengths, a last record without a line end, isoforms of one gene, a custom buffer allocator."""
+    from rna_clique_b200 import select_top_genes as stg
+    rng = np.random.default_rng(3)
+    lines = []
+    for g in range(40):
+        for i in range(1 + g % 3):
+            n = int(rng.integers(1, 400))
+            seq = "".join(rng.choice(list("ACGTN"), size=n))
+            w = int(rng.integers(7, 90))
+            body = [seq[k:k + w] for k in range(0, n, w)]
+            if g % 5 == 0:
+                body = [b[:3] + " " + b[3:] for b in body]
+            eol = "\r\n" if g % 4 == 1 else "\n"
+            lines.append(f">NODE_{g}_length_{n}_cov_{rng.uniform(1, 900):.4f}_g{g}_i{i} extra words" + eol + eol.join(body) + eol)
+    text = "".join(lines)
+    text = text[:-1]                                             # no line end after the last record
+    (tmp_path / "a").mkdir()
+    (tmp_path / "a" / "transcripts.fasta").write_text(text, newline="")
+    for sub in ("full", "lean"):
+        (tmp_path / sub).mkdir()
+    asked = []
+
+    def alloc(nbytes):
+        asked.append(nbytes)
+        return np.empty(nbytes + 100, dtype=np.uint8)
+
+    for top in (0, 1, 7, 40, 100):
+        o1, s1, r1, w1 = stg._parse_and_select(tmp_path / "full", "transcripts.fasta", tmp_path / "a", top, default_parser)
+        o2, s2, r2, w2 = stg._parse_and_select_lean(tmp_path / "lean", "transcripts.fasta", tmp_path / "a", top, default_parser, alloc)
+        w1(); w2()
+        assert s1 == s2 and o1.name == o2.name
+        assert o1.read_bytes() == o2.read_bytes()
+        for k in (3, 4, 5):
+            assert np.array_equal(r1[k], r2[k])
+        for a0, n, b0 in zip(r1[2], r1[5], r2[2]):
+            assert np.array_equal(r1[1][a0:a0 + n], r2[1][b0:b0 + n])
+    assert asked                                                 # the allocator was used
+    # any other parser takes the full path
+    import re
+    custom = lambda s: default_parser(s)
+    o3, _, r3, _ = stg._parse_and_select_lean(tmp_path / "lean", "transcripts.fasta", tmp_path / "a", 7, custom)
+    assert np.array_equal(r3[3], stg._parse_and_select(tmp_path / "full", "transcripts.fasta", tmp_path / "a", 7, custom)[2][3])
+    # an id the pattern does not match raises like the reference
+    (tmp_path / "b").mkdir()
+    (tmp_path / "b" / "transcripts.fasta").write_text(">NODE_1_cov_3.5_g1_i1\nACGT\n>nonsense\nACGT\n")
+    with pytest.raises(TranscriptIDParseError):
+        stg._parse_and_select_lean(tmp_path / "lean", "transcripts.fasta", tmp_path / "b", 1, default_parser)

@@ -13,7 +13,10 @@ dist = None
 if world > 1:
     import torch.distributed as dist
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-_, ts = simulate(10, 60000, seed=487, device=f"cuda:{local}")
+CONFIGS = {1: (10, 60000), 2: (30, 100000)}
+taxa, count = CONFIGS[int(os.environ.get("RCQ_TRACE_CONFIG", "1"))]
+summary = bool(os.environ.get("RCQ_TRACE_SUMMARY"))
+_, ts = simulate(taxa, count, seed=487, device=f"cuda:{local}")
 inputs, labels = [], []
 for t in ts:
     offs = t.offsets.numpy()
@@ -32,6 +35,18 @@ for r in range(world):
         dist.barrier()
     if r == rank and rank in (0, world - 1):
         print(f"--- rank {rank}: host {res['host_ms']}")
+        if summary:
+            kinds = {}
+            for w, task, a, b in eng.task_trace:
+                k = kinds.setdefault(task[0], dict(n=0, busy=0.0, first=1e9, last=0.0))
+                k["n"] += 1; k["busy"] += b - a; k["first"] = min(k["first"], a); k["last"] = max(k["last"], b)
+            for name, k in sorted(kinds.items()):
+                print(f"  task {name}: {k['n']:4d} x, busy {k['busy']*1e3:8.1f} ms (all workers), first start {k['first']*1e3:7.1f}, last end {k['last']*1e3:7.1f}")
+            for w0 in sorted({x[0] for x in eng.task_trace}):
+                tt = sorted((a, b) for w, _, a, b in eng.task_trace if w == w0)
+                busy = sum(b - a for a, b in tt)
+                print(f"  worker {w0}: busy {busy*1e3:7.1f} ms of {tt[-1][1]*1e3:7.1f}")
+            continue
         for w, task, a, b in sorted(eng.task_trace, key=lambda x: x[2]):
             print(f"  w{w} {task[0]}{task[1]:<3d} {a*1e3:7.2f} -> {b*1e3:7.2f}  ({(b-a)*1e3:5.2f} ms)")
         sys.stdout.flush()
