@@ -99,6 +99,15 @@ int rcq_graph_pickle_groups(const char* path, int32_t n_samples, const char* con
                             const int32_t* const* sgene, const int32_t* const* qgene, int64_t n_isolated,
                             const int32_t* iso_sample, const int32_t* iso_gene, int64_t counts[3]);
 
+/* graph.pkl from DEVICE-RESIDENT tables (csrc/graph_device.cu): the same file as rcq_graph_pickle_groups on the
+ * tables' (sgene, qgene) columns, with node numbering, duplicate rows, adjacency lists and memo numbers computed on
+ * the GPU and only the byte stream produced on the host.  tables[t] joins samples t_s[t] (sgene) and t_q[t]
+ * (qgene).  Returns RCQ_ERR_ARG when a table is not ordered by (qgene, sgene) or two tables join the same two
+ * samples, RCQ_ERR_CAPACITY for 2^31 rows or gene ids too sparse for dense tables: use the host writer then. */
+int rcq_graph_pickle_tables(rcq_ctx* ctx, const char* path, int32_t n_samples, const char* const* sample_names,
+                            int32_t n_tables, const rcq_table* const* tables, const int32_t* t_s, const int32_t* t_q,
+                            int64_t counts[3]);
+
 /* ---- matrix.h5 (host only).  Replaces `mat.to_hdf(output_matrix, key="matrix")` (rna_clique.py:175-177; format:
  * docs/formats.md:346-352, read back by export_matrix.py:113 pd.read_hdf): writes an HDF5 file holding ONE pandas
  * fixed-format DataFrame under `key` — group attributes pandas_type="frame", pandas_version, encoding, errors,

@@ -20,7 +20,7 @@ HSP_COLS = ["tx1", "tx2", "minus", "a0", "a1", "b0", "b1", "score2", "mismatch",
 # every symbol include/rcq.h declares (checked by tests/test_abi.py)
 SYMBOLS = [
     "rcq_last_error", "rcq_version", "rcq_ctx_create", "rcq_ctx_destroy", "rcq_ctx_sync", "rcq_ctx_stream",
-    "rcq_ctx_launches", "rcq_ctx_stage_times", "rcq_top_gene_mask", "rcq_fasta_scan", "rcq_fasta_parse", "rcq_fasta_headers", "rcq_fasta_extract", "rcq_parse_spades_ids", "rcq_fasta_format", "rcq_graph_pickle", "rcq_graph_pickle_groups", "rcq_matrix_h5_write", "rcq_sample_create", "rcq_sample_free", "rcq_sample_info", "rcq_sample_download",
+    "rcq_ctx_launches", "rcq_ctx_stage_times", "rcq_top_gene_mask", "rcq_fasta_scan", "rcq_fasta_parse", "rcq_fasta_headers", "rcq_fasta_extract", "rcq_parse_spades_ids", "rcq_fasta_format", "rcq_graph_pickle", "rcq_graph_pickle_groups", "rcq_graph_pickle_tables", "rcq_matrix_h5_write", "rcq_sample_create", "rcq_sample_free", "rcq_sample_info", "rcq_sample_download",
     "rcq_ctx_set_dust", "rcq_sample_seed_mask", "rcq_dust_mask_static", "rcq_int32_issue_peak",
     "rcq_search_pair", "rcq_table_rows", "rcq_table_download", "rcq_table_free", "rcq_debug_last_hsps", "rcq_debug_keep_hsps",
     "rcq_length_adjustment", "rcq_table_stats", "rcq_evalue", "rcq_bitscore", "rcq_phase2_host", "rcq_phase2_tables", "rcq_phase2_pack", "rcq_phase2_packed",
@@ -99,6 +99,7 @@ def lib():
         L.rcq_graph_pickle.argtypes = [C.c_char_p, C.c_int32, vp, C.c_int32, vp, vp, vp, vp, vp, i64, vp, vp, vp]
         L.rcq_fasta_format.restype = i64
         L.rcq_graph_pickle_groups.argtypes = [C.c_char_p, C.c_int32, vp, C.c_int32, vp, vp, vp, vp, vp, i64, vp, vp, vp]
+        L.rcq_graph_pickle_tables.argtypes = [vp, C.c_char_p, C.c_int32, vp, C.c_int32, vp, vp, vp, vp]
         L.rcq_matrix_h5_write.argtypes = [C.c_char_p, C.c_char_p, i64, i64, vp, vp, vp]
         L.rcq_top_gene_mask.argtypes = [vp, vp, i64, i64, vp]
         L.rcq_top_gene_mask.restype = i64
@@ -399,6 +400,20 @@ def graph_pickle(path, sample_names, groups, isolated=()) -> dict:
     check(lib().rcq_graph_pickle_groups(str(path).encode(), len(names), C.cast(arr, C.c_void_p), len(groups), _ptr(g_s), _ptr(g_q),
                                         _ptr(g_len), C.cast(sp, C.c_void_p), C.cast(qp, C.c_void_p), len(iso_s), _ptr(iso_s),
                                         _ptr(iso_g), counts.ctypes.data))
+    return dict(nodes=int(counts[0]), edges=int(counts[1]), bytes=int(counts[2]))
+
+
+def graph_pickle_tables(ctx: "Context", path, sample_names, tables, t_s, t_q) -> dict:
+    """rcq_graph_pickle_tables: graph.pkl from device-resident tables (tables[k] joins samples t_s[k], t_q[k]).
+    Raises NativeError (RCQ_ERR_ARG / RCQ_ERR_CAPACITY) when the tables do not qualify for the device path."""
+    names = [str(n).encode() for n in sample_names]
+    arr = (C.c_char_p * max(len(names), 1))(*names)
+    hp = (C.c_void_p * max(len(tables), 1))(*[t.h for t in tables])
+    ts = np.ascontiguousarray(t_s, dtype=np.int32)
+    tq = np.ascontiguousarray(t_q, dtype=np.int32)
+    counts = np.zeros(3, dtype=np.int64)
+    check(lib().rcq_graph_pickle_tables(ctx.h, str(path).encode(), len(names), C.cast(arr, C.c_void_p), len(tables),
+                                        C.cast(hp, C.c_void_p), _ptr(ts), _ptr(tq), counts.ctypes.data))
     return dict(nodes=int(counts[0]), edges=int(counts[1]), bytes=int(counts[2]))
 
 

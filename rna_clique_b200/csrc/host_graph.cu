@@ -21,6 +21,7 @@
 #include <unordered_map>
 #include <vector>
 #include "common.cuh"
+#include "host_graph.h"
 
 namespace {
 // Append-only byte buffer with bulk capacity checks: the adjacency section is hundreds of megabytes, one
@@ -65,6 +66,97 @@ void run_threads(int n_threads, F f) {                  // f(t) on n_threads thr
     for (auto& x : th) x.join();
 }
 }  // namespace
+
+// ---- the stream.  Shared by this file's host front end and the device front end (graph_device.cu).  Nodes in
+// first-appearance order; adjacency lists (CSR start/nbr) in edge-insertion order; erel[a] = RCQ_GRAPH_FIRST_VISIT
+// when entry a is the first visit of its edge (nbr[a] >= the node that owns the list: the attribute dict is created
+// and memoised there), else the memo number of that dict relative to the end of the _node section.
+int rcq_graph_emit(const char* path, int32_t n_samples, const char* const* sample_names, int64_t n_nodes,
+                   const int32_t* node_sample, const int32_t* node_gene, const int64_t* start, const int32_t* nbr,
+                   const uint32_t* erel, int64_t n_edges, int64_t counts[3]) {
+    const int n_threads = (int)std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+    static const bool trace = getenv("RCQ_TRACE") != nullptr;
+    auto T0 = std::chrono::steady_clock::now();
+    auto lap = [&](const char* what) {
+        if (!trace) return;
+        auto T1 = std::chrono::steady_clock::now();
+        fprintf(stderr, "[rcq_graph_pickle] %-14s %.3f s\n", what, std::chrono::duration<double>(T1 - T0).count());
+        T0 = T1;
+    };
+    if (n_nodes + n_edges + n_samples + 16 >= (1ll << 32)) return rcq_fail(RCQ_ERR_CAPACITY, "rcq_graph_pickle: more than 2^32 memo entries");
+    // strings and node tuples are memoised in the _node section, in node order
+    std::vector<uint32_t> sample_memo((size_t)n_samples, 0xFFFFFFFFu), node_memo((size_t)n_nodes);
+    uint32_t memo = 0;
+    for (int64_t i = 0; i < n_nodes; i++) {
+        if (sample_memo[node_sample[i]] == 0xFFFFFFFFu) sample_memo[node_sample[i]] = memo++;
+        node_memo[i] = memo++;
+    }
+    // ---- the stream: head (+ _node section) sequentially, the _adj section in parallel parts, tail
+    PickleOut H;
+    H.need((size_t)(256 + 24 * n_nodes));
+    H.op(0x80); H.op(4);                                                    // PROTO 4
+    H.str("networkx.classes.graph", 22); H.str("Graph", 5); H.op(0x93);     // STACK_GLOBAL
+    H.op(')'); H.op('R');                                                   // EMPTY_TUPLE REDUCE -> Graph()
+    H.empty_dict(); H.mark();                                               // state = {
+    H.str("graph", 5); H.empty_dict();
+    H.str("_node", 5); H.empty_dict(); H.mark();
+    {
+        std::vector<uint8_t> seen((size_t)n_samples, 0);
+        for (int64_t i = 0; i < n_nodes; i++) {
+            const int32_t s = node_sample[i];
+            H.need(32);
+            if (!seen[s]) { H.str(sample_names[s], strlen(sample_names[s])); H.need(32); H.memoize(); seen[s] = 1; }
+            else H.get(sample_memo[s]);
+            H.integer(node_gene[i]);
+            H.op(0x86);                                                     // TUPLE2
+            H.memoize();
+            H.empty_dict();
+        }
+    }
+    H.need(32);
+    H.setitems();
+    H.str("_adj", 4); H.need(8); H.empty_dict(); H.mark();
+    std::vector<PickleOut> parts((size_t)n_threads);
+    int used_parts = 1;
+    if (n_nodes >= 4096) used_parts = n_threads;
+    parallel_for(n_nodes, used_parts, [&](int t, int64_t i0, int64_t i1) {
+        PickleOut& P = parts[t];
+        P.need((size_t)(16 * (i1 - i0) + 10 * (start[i1] - start[i0]) + 64));
+        for (int64_t i = i0; i < i1; i++) {
+            P.need((size_t)(16 + 10 * (start[i + 1] - start[i])));
+            P.get(node_memo[i]);
+            P.empty_dict();
+            if (start[i + 1] > start[i]) {
+                P.mark();
+                for (int64_t a = start[i]; a < start[i + 1]; a++) {
+                    P.get(node_memo[nbr[a]]);
+                    if (erel[a] == RCQ_GRAPH_FIRST_VISIT) { P.empty_dict(); P.memoize(); } else P.get(memo + erel[a]);
+                }
+                P.setitems();
+            }
+        }
+    });
+    lap("stream");
+    PickleOut T;
+    T.need(64);
+    T.setitems();
+    T.str("__networkx_cache__", 18); T.need(8); T.empty_dict();
+    T.setitems();                                                           // }
+    T.op('b'); T.op('.');                                                   // BUILD STOP
+    FILE* f = fopen(path, "wb");
+    if (!f) return rcq_fail(RCQ_ERR_ARG, "rcq_graph_pickle: cannot open the output file");
+    size_t total = 0, wrote = 0;
+    auto put = [&](const PickleOut& P) { total += P.n; if (P.n) wrote += fwrite(P.b.data(), 1, P.n, f); };
+    put(H);
+    for (int t = 0; t < used_parts; t++) put(parts[t]);
+    put(T);
+    const bool closed = fclose(f) == 0;
+    lap("file write");
+    if (!closed || wrote != total) return rcq_fail(RCQ_ERR_ARG, "rcq_graph_pickle: short write");
+    if (counts) { counts[0] = n_nodes; counts[1] = n_edges; counts[2] = (int64_t)total; }
+    return 0;
+}
+
 
 // Groups g = 0..n_groups-1 hold rows [g_off[g], g_off[g+1]) of (sgene, qgene) between samples g_s[g] and
 // g_q[g] (indices into sample_names); isolated nodes (degree 0) follow the edges.  counts[0] = nodes,
@@ -287,14 +379,8 @@ static int graph_pickle_impl(const char* path, int32_t n_samples, const char* co
     });
     std::vector<int64_t>().swap(fill);
     lap("adjacency");
-    // ---- memo numbers.  Strings and node tuples are memoised in the _node section, in node order; an edge's
-    // attribute dict when the _adj section visits the edge for the first time, i.e. at its lower-numbered end.
-    std::vector<uint32_t> sample_memo((size_t)n_samples, 0xFFFFFFFFu), node_memo((size_t)n_nodes);
-    uint32_t memo = 0;
-    for (int64_t i = 0; i < n_nodes; i++) {
-        if (sample_memo[node_sample[i]] == 0xFFFFFFFFu) sample_memo[node_sample[i]] = memo++;
-        node_memo[i] = memo++;
-    }
+    // ---- memo numbers of the edge dictionaries, relative to the end of the _node section: an edge's attribute dict
+    // is memoised when the _adj section visits the edge for the first time, i.e. at its lower-numbered end
     std::vector<int64_t> first_before((size_t)n_nodes + 1, 0);         // first visits in the adjacency lists of earlier nodes
     parallel_for(n_nodes, n_threads, [&](int, int64_t i0, int64_t i1) {
         for (int64_t i = i0; i < i1; i++) {
@@ -304,78 +390,22 @@ static int graph_pickle_impl(const char* path, int32_t n_samples, const char* co
         }
     });
     for (int64_t i = 0; i < n_nodes; i++) first_before[i + 1] += first_before[i];
-    std::vector<uint32_t> edge_memo((size_t)n_edges);
+    std::vector<uint32_t> edge_rel((size_t)n_edges);
     parallel_for(n_nodes, n_threads, [&](int, int64_t i0, int64_t i1) {
         for (int64_t i = i0; i < i1; i++) {
-            uint32_t m = memo + (uint32_t)first_before[i];
-            for (int64_t a = start[i]; a < start[i + 1]; a++) if (nbr[a] >= i) edge_memo[via[a]] = m++;
+            uint32_t m = (uint32_t)first_before[i];
+            for (int64_t a = start[i]; a < start[i + 1]; a++) if (nbr[a] >= i) edge_rel[via[a]] = m++;
         }
     });
+    std::vector<uint32_t> erel((size_t)start[n_nodes]);
+    parallel_for(n_nodes, n_threads, [&](int, int64_t i0, int64_t i1) {
+        for (int64_t i = i0; i < i1; i++)
+            for (int64_t a = start[i]; a < start[i + 1]; a++) erel[a] = nbr[a] >= i ? RCQ_GRAPH_FIRST_VISIT : edge_rel[via[a]];
+    });
+    std::vector<int32_t>().swap(via); std::vector<uint32_t>().swap(edge_rel);
     lap("memo numbers");
-    // ---- the stream: head (+ _node section) sequentially, the _adj section in parallel parts, tail
-    PickleOut H;
-    H.need((size_t)(256 + 24 * n_nodes));
-    H.op(0x80); H.op(4);                                                    // PROTO 4
-    H.str("networkx.classes.graph", 22); H.str("Graph", 5); H.op(0x93);     // STACK_GLOBAL
-    H.op(')'); H.op('R');                                                   // EMPTY_TUPLE REDUCE -> Graph()
-    H.empty_dict(); H.mark();                                               // state = {
-    H.str("graph", 5); H.empty_dict();
-    H.str("_node", 5); H.empty_dict(); H.mark();
-    {
-        std::vector<uint8_t> seen((size_t)n_samples, 0);
-        for (int64_t i = 0; i < n_nodes; i++) {
-            const int32_t s = node_sample[i];
-            H.need(32);
-            if (!seen[s]) { H.str(sample_names[s], strlen(sample_names[s])); H.need(32); H.memoize(); seen[s] = 1; }
-            else H.get(sample_memo[s]);
-            H.integer(node_gene[i]);
-            H.op(0x86);                                                     // TUPLE2
-            H.memoize();
-            H.empty_dict();
-        }
-    }
-    H.need(32);
-    H.setitems();
-    H.str("_adj", 4); H.need(8); H.empty_dict(); H.mark();
-    std::vector<PickleOut> parts((size_t)n_threads);
-    int used_parts = 1;
-    if (n_nodes >= 4096) used_parts = n_threads;
-    parallel_for(n_nodes, used_parts, [&](int t, int64_t i0, int64_t i1) {
-        PickleOut& P = parts[t];
-        P.need((size_t)(16 * (i1 - i0) + 10 * (start[i1] - start[i0]) + 64));
-        for (int64_t i = i0; i < i1; i++) {
-            P.need((size_t)(16 + 10 * (start[i + 1] - start[i])));
-            P.get(node_memo[i]);
-            P.empty_dict();
-            if (start[i + 1] > start[i]) {
-                P.mark();
-                for (int64_t a = start[i]; a < start[i + 1]; a++) {
-                    P.get(node_memo[nbr[a]]);
-                    if (nbr[a] >= i) { P.empty_dict(); P.memoize(); } else P.get(edge_memo[via[a]]);
-                }
-                P.setitems();
-            }
-        }
-    });
-    lap("stream");
-    PickleOut T;
-    T.need(64);
-    T.setitems();
-    T.str("__networkx_cache__", 18); T.need(8); T.empty_dict();
-    T.setitems();                                                           // }
-    T.op('b'); T.op('.');                                                   // BUILD STOP
-    FILE* f = fopen(path, "wb");
-    if (!f) return rcq_fail(RCQ_ERR_ARG, "rcq_graph_pickle: cannot open the output file");
-    size_t total = 0, wrote = 0;
-    auto put = [&](const PickleOut& P) { total += P.n; if (P.n) wrote += fwrite(P.b.data(), 1, P.n, f); };
-    put(H);
-    for (int t = 0; t < used_parts; t++) put(parts[t]);
-    put(T);
-    const bool closed = fclose(f) == 0;
-    lap("file write");
-    if (!closed || wrote != total) return rcq_fail(RCQ_ERR_ARG, "rcq_graph_pickle: short write");
-    if (counts) { counts[0] = n_nodes; counts[1] = n_edges; counts[2] = (int64_t)total; }
-    return 0;
+    return rcq_graph_emit(path, n_samples, sample_names, n_nodes, node_sample.data(), node_gene.data(), start.data(), nbr.data(),
+                          erel.data(), n_edges, counts);
 }
 
 extern "C" int rcq_graph_pickle(const char* path, int32_t n_samples, const char* const* sample_names,

@@ -10,8 +10,8 @@ one dependency-driven schedule on the multi-stream engine (engine.Engine._run_ta
                                        search pair (i, j) as soon as both samples are resident, download the table
   host pool again                      table -> DataFrame -> od2/<S1>--<S2>.<ext>, while later pairs search
 
-and the device tables stay resident: the graph is built from their gene columns, graph.pkl is written natively
-from the flat edge arrays, and SampleSimilarity reduces the device tables directly (rcq_phase2_tables) instead
+and the device tables stay resident: the graph is built from their gene columns, graph.pkl is prepared on the device
+(node numbering, distinct edges, adjacency lists) and only serialised on the host, and SampleSimilarity reduces the device tables directly (rcq_phase2_tables) instead
 of reading od2/ back."""
 from __future__ import annotations
 
@@ -276,7 +276,15 @@ def filtering_step(dirs: Iterable[Path], out_dir_1: Path, out_dir_2: Path, cache
         graph.__dict__["_rcq_device"] = dict(engine=eng, tables=tables, pairs=pairs, labels=[str(p) for p in out_paths],
                                              empty=[len(t) == 0 for t in tables])
         if output_graph is not None:
-            dump_graph(graph, output_graph)
+            # graph.pkl: prepared on the device from the resident tables (csrc/graph_device.cu), by the host writer
+            # when the tables do not qualify (sparse custom gene ids)
+            try:
+                _native.graph_pickle_tables(eng.ctxs[0], output_graph, [str(p) for p in out_paths], tables,
+                                            [i for i, _ in pairs], [j for _, j in pairs])
+            except _native.RcqError as err:
+                if err.code not in (-2, -3):
+                    raise
+                dump_graph(graph, output_graph)
         t_2 = time.perf_counter()
         for f in writes + od1_writes:
             if f is not None:

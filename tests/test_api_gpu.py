@@ -182,7 +182,9 @@ def test_preloaded_sample_equals_the_one_read_back_from_od1(tmp_path):
     assert (a.n_seq, a.total, a.n_index) == (b.n_seq, b.total, b.n_index) and a.n_seq == 120
     da, db = a.download(), b.download()
     for k in da:
-        assert np.array_equal(da[k], db[k]), k
+        # index entries are sorted by key only: entries of one key come in the order the appends happened to take
+        x, y = (np.sort(da[k]), np.sort(db[k])) if k == "index" else (da[k], db[k])
+        assert np.array_equal(x, y), k
     pre.close(); plain.close()
 
 
@@ -218,3 +220,51 @@ def test_pairwise_strands_of_isoforms(ctx):
             best[(q, t)] = (row[7], row[2])
     assert {k: (-1 if v[1] else 1) for k, v in best.items()} == {(a[1], b[1]): sgn for a, b, sgn in got}
     assert list(pairwise_get_strands(recs[:1], ctx=ctx)) == []
+
+
+@pytest.mark.parametrize("kind", ["orthologs", "families"])
+def test_device_graph_pickle_equals_host_writer_and_networkx(tmp_path, kind):
+    """rcq_graph_pickle_tables (node numbering, duplicate rows, adjacency and memo numbers on the GPU) writes the
+    bytes of the host writer on the downloaded columns, which are the bytes of pickle.dump(networkx.Graph)."""
+    import itertools
+    import pickle
+    import networkx as nx
+    from rna_clique_b200 import _native
+    from rna_clique_b200.build_graph import EdgeArrays
+    from rna_clique_b200.engine import select_top_genes
+    ctx = _native.Context(0)
+    try:
+        if kind == "orthologs":
+            from rna_clique_b200.simulate import simulate
+            _, ts = simulate(5, 400, seed=21, mutation_rate=0.03)
+            samples = []
+            for t in ts:
+                offs = t.offsets.numpy()
+                keep = select_top_genes(t.coverage, t.gene, 300)
+                samples.append(_native.Sample(ctx, t.ascii, offs[:-1][keep], t.gene[keep], t.iso[keep],
+                                              lengths=np.diff(offs).astype(np.int32)[keep]))
+        else:
+            from helpers import make_family_samples
+            fam = make_family_samples(seed=4, genes=150, taxa=4)
+            samples = [_native.Sample(ctx, a, o, g, i) for a, o, g, i in fam]
+        n = len(samples)
+        names = [f"/some/dir/T{k}_top.fasta" for k in range(n)]
+        pairs = list(itertools.combinations(range(n), 2))
+        tables = [_native.search_pair(ctx, samples[i], samples[j], 1e-99, 2 if kind == "families" else 1, True) for i, j in pairs]
+        dev = _native.graph_pickle_tables(ctx, tmp_path / "dev.pkl", names, tables, [i for i, _ in pairs], [j for _, j in pairs])
+        e = EdgeArrays()
+        for (i, j), t in zip(pairs, tables):
+            c = t.download()
+            if len(c["sgene"]):
+                e.add(names[i], names[j], c["sgene"], c["qgene"])
+        host = e.write_pickle(tmp_path / "host.pkl")
+        assert dev == host and dev["edges"] > 100
+        assert (tmp_path / "dev.pkl").read_bytes() == (tmp_path / "host.pkl").read_bytes()
+        g = pickle.load(open(tmp_path / "dev.pkl", "rb"))
+        ref = e.to_networkx()
+        assert type(g) is nx.Graph and list(g.nodes) == list(ref.nodes) and list(g.edges) == list(ref.edges)
+        assert all(list(g.adj[x]) == list(ref.adj[x]) for x in ref.nodes)            # neighbours in insertion order
+        u, v = next(iter(g.edges))
+        assert g._adj[u][v] is g._adj[v][u] and g._adj[u][v] == {}                    # one shared attribute dict per edge
+    finally:
+        ctx.close()
