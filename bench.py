@@ -189,7 +189,7 @@ def reference_arm(a):
 
 # ------------------------------------------------------------------------------------------------------------
 def solo_kernel_times(eng, resident, labels, pairs):
-    """k_gapped and k_seed_probe timed alone (one stream, nothing else on the GPU) on several sample pairs:
+    """The gapped stage (k_gapped_reg passes + k_gapped) and k_seed_probe timed alone (one stream, nothing else on the GPU) on several sample pairs:
     per-launch CUDA-event times of the stage timers and the extension steps / index sizes of the same launches."""
     from rna_clique_b200 import _native
     ctx = eng.ctxs[0]
@@ -395,7 +395,7 @@ def main():
             "seconds_to_matrix": {"hbm_resident": ms_dev * 1e-3},
             "gpu_launches": launches,
             "clocks": clocks,
-            "roofline": {"kernel": "k_gapped", "bound": "int32_issue", "unit": "G lane-ops/s",
+            "roofline": {"kernel": "k_gapped_reg (gapped stage: k_gapped_reg<8,6> + <8,8> + k_gapped)", "bound": "int32_issue", "unit": "G lane-ops/s",
                          "achieved": gapped_ops / 1e9, "peak": int_peak / 1e9, "frac": gapped_ops / int_peak,
                          "traffic": traffic.get("k_gapped"),
                          "work_unit": f"one lane-operation = one thread executing one 32-bit integer instruction; an extension "

@@ -15,6 +15,7 @@ extern "C" int64_t rcq_top_gene_mask(const double* coverage, const int32_t* gene
     int32_t gmin = gene[0], gmax = gene[0];
     for (int64_t i = 1; i < n; i++) { gmin = std::min(gmin, gene[i]); gmax = std::max(gmax, gene[i]); }
     std::vector<std::pair<double, int32_t>> genes;   // (best coverage, gene id), one per distinct gene
+    genes.reserve((size_t)n);
     std::vector<int32_t> slot(n);                    // transcript -> index into `genes`
     const int64_t span = (int64_t)gmax - gmin + 1;
     if (span <= 8 * n + 1024) {
@@ -41,11 +42,12 @@ extern "C" int64_t rcq_top_gene_mask(const double* coverage, const int32_t* gene
     std::vector<uint8_t> sel((size_t)G, 0);
     if (top >= G) std::fill(sel.begin(), sel.end(), 1);
     else if (top > 0) {
-        std::vector<int32_t> order((size_t)G);
-        for (int64_t g = 0; g < G; g++) order[g] = (int32_t)g;
-        auto less = [&](int32_t a, int32_t b) { return genes[a] < genes[b]; };   // (coverage, gene id) ascending
-        std::nth_element(order.begin(), order.begin() + (G - top), order.end(), less);
-        for (int64_t k = G - top; k < G; k++) sel[order[k]] = 1;
+        // the top-th largest (coverage, gene id) pair by selection on a contiguous copy (no index indirection); gene
+        // ids are distinct, so exactly `top` genes compare >= that pair
+        std::vector<std::pair<double, int32_t>> ord(genes);
+        std::nth_element(ord.begin(), ord.begin() + (G - top), ord.end());
+        const std::pair<double, int32_t> thr = ord[(size_t)(G - top)];
+        for (int64_t g = 0; g < G; g++) sel[g] = !(genes[g] < thr);
     }
     int64_t kept = 0;
     for (int64_t i = 0; i < n; i++) { keep[i] = sel[slot[i]]; kept += keep[i]; }

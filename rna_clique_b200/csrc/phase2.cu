@@ -62,6 +62,9 @@ __global__ void k_p2_union(P2View V) {
     if (r >= V.n_rows) return;
     int32_t t = table_of(V.row_off, V.n_tables, r);
     if (V.t_flags && !(V.t_flags[t] & 1)) return;
+    // a row naming the gene pair of the row before it (the forward and the backward row of one reciprocal hit) adds
+    // nothing to the graph: half of the atomics of this kernel
+    if (r > V.row_off[t] && V.sgene[r] == V.sgene[r - 1] && V.qgene[r] == V.qgene[r - 1]) return;
     int32_t u = (int32_t)(V.t_s[t] * V.stride + V.sgene[r]);
     int32_t v = (int32_t)(V.t_q[t] * V.stride + V.qgene[r]);
     V.present[u] = 1; V.present[v] = 1;

@@ -221,11 +221,23 @@ class Engine:
         # copy hide behind the searches of earlier samples; an upload only waits for its own copy's event
         staged = self._prefetch(inputs, [k for k in range(len(inputs)) if world == 1 or k % world == rank])
 
+        # top-gene selection (host code, 5 ms per 100,000 transcripts) runs ahead of the uploads on its own threads:
+        # with the samples shared out over N GPUs a rank builds its few samples back to back at the start of the
+        # step, and every millisecond in front of a build delays the round the other ranks wait for
+        own = [k for k in range(len(inputs)) if world == 1 or k % world == rank]
+        selected = {}
+        if top_genes is not None:
+            if getattr(self, "_select_pool", None) is None:
+                from concurrent.futures import ThreadPoolExecutor
+                self._select_pool = ThreadPoolExecutor(4)
+            for k in own:
+                selected[k] = self._select_pool.submit(select_top_genes, inputs[k]["coverage"], np.asarray(inputs[k]["gene"]), top_genes)
+
         def up(ctx, k):
             s = inputs[k]
             starts, lengths, gene, iso = (np.asarray(s[c]) for c in ("starts", "lengths", "gene", "iso"))
             if top_genes is not None:
-                keep = select_top_genes(s["coverage"], gene, top_genes)
+                keep = selected.pop(k).result() if k in selected else select_top_genes(s["coverage"], gene, top_genes)
                 starts, lengths, gene, iso = starts[keep], lengths[keep], gene[keep], iso[keep]
             ascii_ = s["ascii"]
             if k in staged:
@@ -374,5 +386,8 @@ class Engine:
         if self._pool is not None:
             self._pool.shutdown()
             self._pool = None
+        if getattr(self, "_select_pool", None) is not None:
+            self._select_pool.shutdown()
+            self._select_pool = None
         for c in self.ctxs:
             c.close()
