@@ -291,9 +291,10 @@ class Table:
 
     def download(self) -> dict:
         n = len(self)
-        cols = {c: np.zeros(n, dtype=np.int32) for c in TABLE_COLS}
-        cols["minus"] = np.zeros(n, dtype=np.uint8)
-        cols["reverse"] = np.zeros(n, dtype=np.uint8)
+        block = np.empty((len(TABLE_COLS), n), dtype=np.int32)       # one allocation for the fifteen int32 columns
+        cols = {c: block[k] for k, c in enumerate(TABLE_COLS)}
+        cols["minus"] = np.empty(n, dtype=np.uint8)
+        cols["reverse"] = np.empty(n, dtype=np.uint8)
         tc = TableCols(**{k: v.ctypes.data for k, v in cols.items()})
         check(lib().rcq_table_download(self.h, C.byref(tc)))
         return cols

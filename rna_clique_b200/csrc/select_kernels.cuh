@@ -79,15 +79,18 @@ extern "C" int rcq_table_stats(int64_t n, const int32_t* score, const int32_t* q
                                double* evalue, double* bitscore) {
     if (n < 0 || (n && (!score || !qlen || !reverse || !nident || !length || !pident || !evalue || !bitscore)))
         return rcq_fail(RCQ_ERR_ARG, "rcq_table_stats: bad argument");
-    int32_t last_q[2] = {-1, -1};
-    double last_la[2] = {0, 0};
+    // the length adjustment depends on (query length, direction) only: a direct-mapped cache by length
+    constexpr int CACHE = 4096;
+    std::vector<int32_t> ckey(2 * CACHE, -1);
+    std::vector<double> cla(2 * CACHE, 0.0);
     for (int64_t i = 0; i < n; i++) {
         const int r = reverse[i] ? 1 : 0;
-        if (qlen[i] != last_q[r]) {          // rows come grouped by query gene: the adjustment rarely changes
-            last_q[r] = qlen[i];
-            last_la[r] = (double)length_adjustment((double)qlen[i], (double)(r ? bases_bwd : bases_fwd), (double)(r ? seqs_bwd : seqs_fwd));
+        const int slot = r * CACHE + (qlen[i] & (CACHE - 1));
+        if (ckey[slot] != qlen[i]) {
+            ckey[slot] = qlen[i];
+            cla[slot] = (double)length_adjustment((double)qlen[i], (double)(r ? bases_bwd : bases_fwd), (double)(r ? seqs_bwd : seqs_fwd));
         }
-        const double la = last_la[r];
+        const double la = cla[slot];
         const double nb = (double)(r ? bases_bwd : bases_fwd), ns = (double)(r ? seqs_bwd : seqs_fwd);
         double em = (double)qlen[i] - la, en = nb - ns * la;
         if (em < 1.0) em = 1.0;

@@ -195,6 +195,7 @@ def filtering_step(dirs: Iterable[Path], out_dir_1: Path, out_dir_2: Path, cache
 
         od1_writes = [None] * n
 
+        split = []                # RCQ_TRACE_API: (search, download) seconds of every search task
         uses = {}                 # sample -> users of its letter buffer still running (upload, od1 write)
 
         def release(k, letters):
@@ -258,8 +259,12 @@ def filtering_step(dirs: Iterable[Path], out_dir_1: Path, out_dir_2: Path, cache
                 return
             i, j = pairs[x]
             s1, s2 = samples[i], samples[j]
+            t_a = time.perf_counter()
             t = _native.search_pair(ctx, s1, s2, evalue, top_matches, keep_all)
+            t_b = time.perf_counter()
             cols = t.download()
+            if trace:
+                split.append((t_b - t_a, time.perf_counter() - t_b))
             tables[x] = t
             edges[x] = (cols["sgene"], cols["qgene"])
             writes[x] = host.submit(2, _frame_and_save, cols, (s1.total, s1.n_seq, s2.total, s2.n_seq),
@@ -289,6 +294,9 @@ def filtering_step(dirs: Iterable[Path], out_dir_1: Path, out_dir_2: Path, cache
         for f in writes + od1_writes:
             if f is not None:
                 f.result()
+        if trace and split:
+            print(f"[filtering_step] search tasks: search_pair {1e3 * sum(a for a, _ in split) / len(split):.1f} ms, "
+                  f"download {1e3 * sum(b for _, b in split) / len(split):.1f} ms on average", file=__import__("sys").stderr)
         if trace:
             print(f"[filtering_step] parse+upload+search {t_1 - t_0:.3f} s, graph {t_2 - t_1:.3f} s, "
                   f"waiting for table files {time.perf_counter() - t_2:.3f} s", file=__import__("sys").stderr)

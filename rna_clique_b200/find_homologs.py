@@ -161,7 +161,7 @@ def table_to_frame(cols: dict, n_db_bases_fwd: int, n_db_seqs_fwd: int, n_db_bas
         "sstrand": strands.take(cols["minus"].astype(np.int64)).reset_index(drop=True),
         "qgene": ic["qgene"], "qiso": ic["qiso"], "sgene": ic["sgene"], "siso": ic["siso"],
         "reverse": rev,
-    }, columns=COLUMNS)
+    }, columns=COLUMNS, copy=False)      # the arrays are this call's own: no defensive copy, no consolidation (16 ms of 28)
     return df
 
 
