@@ -113,6 +113,7 @@ int rcq_graph_emit(const char* path, int32_t n_samples, const char* const* sampl
             H.empty_dict();
         }
     }
+    lap("node section");
     H.need(32);
     H.setitems();
     H.str("_adj", 4); H.need(8); H.empty_dict(); H.mark();
