@@ -57,7 +57,7 @@ def parse_args():
     ap.add_argument("--e2e-calls", type=int, default=3, help="timed rna_clique() calls (N = 1)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-api-leg", action="store_true", help="e2e from pinned host buffers instead of rna_clique() on FASTA directories")
-    ap.add_argument("--streams", type=int, default=6, help="CUDA streams (host threads) per GPU")
+    ap.add_argument("--streams", type=int, default=0, help="CUDA streams (host threads) per GPU; 0 = 6 up to four GPUs, 3 beyond (measured)")
     ap.add_argument("--clock-interval", type=float, default=0.2, help="seconds between NVML clock samples (0 = off)")
     a = ap.parse_args()
     t, c, n = CONFIGS[a.config]
@@ -250,7 +250,10 @@ def run_api_leg(transcriptomes, a, engine_matrix, calls, selected_letters):
                 secs.append(dt)
             m = h5fixed.read_frame(tmp / "distance_matrix.h5", "matrix")
             same = same and bool(np.array_equal(m.to_numpy(), engine_matrix))
-            d2h = sum(68 * len(t) for t in sim._device["tables"]) + 16 * len(sim._device["tables"])
+            rows = sum(len(t) for t in sim._device["tables"])
+            # tables (17 columns), the sums, and the graph arrays of graph.pkl (two adjacency entries per distinct edge =
+            # one per row when every reciprocal hit has its forward and its backward row, 8 bytes each; 16 bytes per node)
+            d2h = 68 * rows + 16 * len(sim._device["tables"]) + 8 * rows + 16 * a.top * len(transcriptomes)
             del sim
         close_shared_engine()
         h2d = selected_letters + 28 * a.top * len(transcriptomes)      # the letters of the selected records + their tables
@@ -290,6 +293,11 @@ def main():
         dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local), pg_options=opts)
         dist = dist_mod
     from rna_clique_b200.engine import Engine, select_top_genes
+    if a.streams <= 0:
+        # six streams per GPU keep one GPU busy; with the pairs shared out over eight GPUs a rank has 54 searches and
+        # four sample builds that every other rank waits for: three streams leave the builds more of the GPU
+        # (configs[2], 8 GPUs: 156 ms per step with three streams, 182 ms with six; 4 GPUs: 284 / 280; 2 GPUs: 527 / 515)
+        a.streams = 6 if world <= 4 else 3
     eng = Engine(local, streams=a.streams)
     stream = torch.cuda.ExternalStream(eng.ctx.stream, device=torch.device("cuda", local))
 
