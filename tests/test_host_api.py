@@ -94,3 +94,40 @@ def test_pair_dict_and_schedule():
     assert len(pairs) == 15 and set(owner) == {0, 1, 2, 3}
     load = [sum(100 - 10 * i + 100 - 10 * j for (i, j), o in zip(pairs, owner) if o == r) for r in range(4)]
     assert max(load) - min(load) <= 200
+
+
+def test_priority_pool_serves_urgent_tasks_first_and_hands_on_errors():
+    """filtering_step._PriorityPool: lower priority numbers first, FIFO inside a priority, exceptions through the future."""
+    import threading
+    from rna_clique_b200.filtering_step import _PriorityPool
+    pool = _PriorityPool(1)
+    gate, order = threading.Event(), []
+    first = pool.submit(0, gate.wait)                     # occupies the only worker while the others queue up
+    futs = [pool.submit(p, order.append, (p, k)) for k, p in enumerate([2, 2, 1, 0, 1, 2, 0])]
+    boom = pool.submit(1, lambda: 1 / 0)
+    gate.set()
+    first.result(timeout=10)
+    for f in futs:
+        f.result(timeout=10)
+    assert order == [(0, 3), (0, 6), (1, 2), (1, 4), (2, 0), (2, 1), (2, 5)]
+    with pytest.raises(ZeroDivisionError):
+        boom.result(timeout=10)
+    pool.shutdown()
+
+
+def test_pinned_pool_reuses_buffers_and_falls_back_to_numpy():
+    """filtering_step._PinnedPool: a returned buffer is handed out again; beyond the limit (or without a CUDA device,
+    where page-locking fails) the caller gets ordinary memory."""
+    from rna_clique_b200.filtering_step import _PinnedPool
+    pool = _PinnedPool(limit=64 << 20)
+    a = pool.get(1000)
+    assert a.dtype == np.uint8 and len(a) >= 1000
+    addr = a.ctypes.data
+    pool.put(a[:10])                                      # a view that starts at the first byte gives it back
+    b = pool.get(500)
+    if pool.held:                                         # page-locked memory was available: same buffer again
+        assert b.ctypes.data == addr
+    big = pool.get(128 << 20)                             # over the limit: plain numpy memory
+    assert len(big) >= 128 << 20 and big.ctypes.data not in pool.out
+    pool.put(big)
+    pool.clear()
