@@ -78,6 +78,11 @@ int64_t rcq_fasta_extract(const uint8_t* raw, int64_t n, const int64_t* hdr_star
  * od1/<sample>_top.fasta, select_top_genes_all.py:37-45); out == NULL returns the size only. */
 int64_t rcq_fasta_format(const uint8_t* ascii, const int64_t* starts, const int64_t* lengths, int64_t n,
                          const uint8_t* hdr, const int64_t* hdr_off, int32_t width, uint8_t* out);
+/* The same text written to a file straight from the mapped input (header spans) and the letters rcq_fasta_extract
+ * produced, streamed through a small buffer; returns the bytes written, or -1 with the error set. */
+int64_t rcq_fasta_write(const char* path, const uint8_t* raw, const int64_t* hdr_start, const int64_t* hdr_end,
+                        int64_t n_records, const int64_t* keep, int64_t n_keep, const uint8_t* letters,
+                        const int64_t* off, int32_t width);
 int64_t rcq_parse_spades_ids(const uint8_t* raw, const int64_t* hdr_start, const int64_t* hdr_end,
                              int64_t n_records, double* coverage, int32_t* gene, int32_t* iso);
 

@@ -20,7 +20,7 @@ HSP_COLS = ["tx1", "tx2", "minus", "a0", "a1", "b0", "b1", "score2", "mismatch",
 # every symbol include/rcq.h declares (checked by tests/test_abi.py)
 SYMBOLS = [
     "rcq_last_error", "rcq_version", "rcq_ctx_create", "rcq_ctx_destroy", "rcq_ctx_sync", "rcq_ctx_stream",
-    "rcq_ctx_launches", "rcq_ctx_stage_times", "rcq_top_gene_mask", "rcq_fasta_scan", "rcq_fasta_parse", "rcq_fasta_headers", "rcq_fasta_extract", "rcq_parse_spades_ids", "rcq_fasta_format", "rcq_graph_pickle", "rcq_graph_pickle_groups", "rcq_graph_pickle_tables", "rcq_matrix_h5_write", "rcq_sample_create", "rcq_sample_free", "rcq_sample_info", "rcq_sample_download",
+    "rcq_ctx_launches", "rcq_ctx_stage_times", "rcq_top_gene_mask", "rcq_fasta_scan", "rcq_fasta_parse", "rcq_fasta_headers", "rcq_fasta_extract", "rcq_fasta_write", "rcq_parse_spades_ids", "rcq_fasta_format", "rcq_graph_pickle", "rcq_graph_pickle_groups", "rcq_graph_pickle_tables", "rcq_matrix_h5_write", "rcq_sample_create", "rcq_sample_free", "rcq_sample_info", "rcq_sample_download",
     "rcq_ctx_set_dust", "rcq_sample_seed_mask", "rcq_dust_mask_static", "rcq_int32_issue_peak",
     "rcq_search_pair", "rcq_table_rows", "rcq_table_download", "rcq_table_free", "rcq_debug_last_hsps", "rcq_debug_keep_hsps",
     "rcq_length_adjustment", "rcq_table_stats", "rcq_evalue", "rcq_bitscore", "rcq_phase2_host", "rcq_phase2_tables", "rcq_phase2_pack", "rcq_phase2_packed",
@@ -93,6 +93,8 @@ def lib():
         L.rcq_fasta_headers.argtypes = [vp, i64, i64, vp, vp]
         L.rcq_fasta_extract.argtypes = [vp, i64, vp, vp, i64, vp, i64, vp, i64, vp]
         L.rcq_fasta_extract.restype = i64
+        L.rcq_fasta_write.argtypes = [C.c_char_p, vp, vp, vp, i64, vp, i64, vp, vp, C.c_int32]
+        L.rcq_fasta_write.restype = i64
         L.rcq_parse_spades_ids.argtypes = [vp, vp, vp, i64, vp, vp, vp]
         L.rcq_parse_spades_ids.restype = i64
         L.rcq_fasta_format.argtypes = [vp, vp, vp, i64, vp, vp, C.c_int32, vp]
@@ -358,6 +360,19 @@ def fasta_extract(raw: np.ndarray, hs: np.ndarray, he: np.ndarray, keep: np.ndar
     if tot < 0:
         raise RuntimeError(L.rcq_last_error().decode())
     return out[:max(int(tot), 1)], off
+
+
+def fasta_write(path, raw: np.ndarray, hs: np.ndarray, he: np.ndarray, keep: np.ndarray, letters: np.ndarray, off: np.ndarray,
+                width: int = 60) -> int:
+    """rcq_fasta_write: the records `keep` as FASTA text (headers from the file bytes, letters from fasta_extract)."""
+    keep = np.ascontiguousarray(keep, dtype=np.int64)
+    off = np.ascontiguousarray(off, dtype=np.int64)
+    L = lib()
+    n = L.rcq_fasta_write(str(path).encode(), raw.ctypes.data, hs.ctypes.data, he.ctypes.data, len(hs), keep.ctypes.data, len(keep),
+                          letters.ctypes.data, off.ctypes.data, int(width))
+    if n < 0:
+        raise RuntimeError(L.rcq_last_error().decode())
+    return int(n)
 
 
 def fasta_format(ascii_: np.ndarray, starts, lengths, headers, width: int = 60) -> np.ndarray:

@@ -94,12 +94,14 @@ extern "C" int64_t rcq_fasta_extract(const uint8_t* raw, int64_t n, const int64_
         int64_t p = hdr_end[r] + 1;
         const int64_t end = r + 1 < n_records ? hdr_start[r + 1] : n;
         if (end - p > cap - let) { rcq_fail(RCQ_ERR_CAPACITY, "rcq_fasta_extract: output buffer too small"); return -1; }
+        // CR and spaces are looked for once per record (two scans of a few kilobytes), not once per line
+        const bool plain = !memchr(raw + p, '\r', (size_t)(end - p)) && !memchr(raw + p, ' ', (size_t)(end - p));
         while (p < end) {
             const uint8_t* nl = (const uint8_t*)memchr(raw + p, '\n', (size_t)(end - p));
             const int64_t e = nl ? (int64_t)(nl - raw) : end;
             const uint8_t* a = raw + p;
             const int64_t len = e - p;
-            if (!memchr(a, '\r', (size_t)len) && !memchr(a, ' ', (size_t)len)) { memcpy(out + let, a, (size_t)len); let += len; }
+            if (plain) { memcpy(out + let, a, (size_t)len); let += len; }
             else for (int64_t i = 0; i < len; i++) if (!is_skip(a[i])) out[let++] = a[i];
             p = e + 1;
         }
@@ -147,9 +149,19 @@ extern "C" int64_t rcq_parse_spades_ids(const uint8_t* raw, const int64_t* hdr_s
             if (i + 2 > end || i[0] != '_' || i[1] != 'i') continue;
             const int64_t d4 = digits(i + 2, end);
             if (!d4 || d3 > 9 || d4 > 9 || d1 + d2 > 300) continue;
-            char buf[320];
-            memcpy(buf, q, (size_t)(d1 + 1 + d2)); buf[d1 + 1 + d2] = 0;
-            coverage[r] = strtod(buf, nullptr);
+            if (d1 + d2 <= 15) {
+                // Clinger's fast path: at most 15 significant digits and a power of ten up to 10^15 are exact doubles,
+                // and one IEEE division rounds their quotient correctly - the value strtod (and Python's float) gives
+                static const double P10[16] = {1e0, 1e1, 1e2, 1e3, 1e4, 1e5, 1e6, 1e7, 1e8, 1e9, 1e10, 1e11, 1e12, 1e13, 1e14, 1e15};
+                int64_t m = 0;
+                for (int64_t k = 0; k < d1; k++) m = m * 10 + (q[k] - '0');
+                for (int64_t k = 0; k < d2; k++) m = m * 10 + (q[d1 + 1 + k] - '0');
+                coverage[r] = (double)m / P10[d2];
+            } else {
+                char buf[320];
+                memcpy(buf, q, (size_t)(d1 + 1 + d2)); buf[d1 + 1 + d2] = 0;
+                coverage[r] = strtod(buf, nullptr);
+            }
             int64_t gv = 0, iv = 0;
             for (int64_t k = 0; k < d3; k++) gv = gv * 10 + (g[2 + k] - '0');
             for (int64_t k = 0; k < d4; k++) iv = iv * 10 + (i[2 + k] - '0');
@@ -180,4 +192,58 @@ extern "C" int64_t rcq_fasta_format(const uint8_t* ascii, const int64_t* starts,
         }
     }
     return at;
+}
+
+// od1/<sample>_top.fasta written straight from the mapped input and the extracted letters (the lean path): record
+// keep[k] gets '>' + its header text (raw[hdr_start + 1 .. hdr_end), a trailing CR dropped) + LF and the letters
+// letters[off[k] .. off[k + 1]) in lines of `width` - the bytes rcq_fasta_format produces - streamed through a small
+// buffer instead of being assembled in memory first.  Returns the bytes written, or -1 with the error set.
+extern "C" int64_t rcq_fasta_write(const char* path, const uint8_t* raw, const int64_t* hdr_start, const int64_t* hdr_end,
+                                   int64_t n_records, const int64_t* keep, int64_t n_keep, const uint8_t* letters,
+                                   const int64_t* off, int32_t width) {
+    if (!path || n_keep < 0 || width < 1 || (n_keep && (!raw || !hdr_start || !hdr_end || !keep || !letters || !off))) {
+        rcq_fail(RCQ_ERR_ARG, "rcq_fasta_write: bad argument");
+        return -1;
+    }
+    FILE* f = fopen(path, "wb");
+    if (!f) { rcq_fail(RCQ_ERR_ARG, "rcq_fasta_write: cannot open the output file"); return -1; }
+    const size_t CAP = 4u << 20;
+    std::vector<uint8_t> buf(CAP + 65536);
+    size_t at = 0;
+    int64_t total = 0;
+    bool ok = true;
+    auto flush = [&]() { if (at) { ok = ok && fwrite(buf.data(), 1, at, f) == at; total += (int64_t)at; at = 0; } };
+    for (int64_t k = 0; k < n_keep && ok; k++) {
+        const int64_t r = keep[k];
+        if (r < 0 || r >= n_records) { fclose(f); rcq_fail(RCQ_ERR_ARG, "rcq_fasta_write: record index out of range"); return -1; }
+        int64_t a = hdr_start[r] + 1, b = hdr_end[r];
+        if (b > a && raw[b - 1] == '\r') b--;
+        if (b < a) b = a;
+        const size_t hl = (size_t)(b - a);
+        if (hl + 2 > 65536) {                      // a header longer than the slack: written on its own
+            flush();
+            ok = ok && fputc('>', f) != EOF && fwrite(raw + a, 1, hl, f) == hl && fputc('\n', f) != EOF;
+            total += (int64_t)hl + 2;
+        } else {
+            if (at + hl + 2 > CAP + 65536) flush();
+            buf[at++] = '>'; memcpy(buf.data() + at, raw + a, hl); at += hl; buf[at++] = '\n';
+        }
+        const int64_t L = off[k + 1] - off[k];
+        const uint8_t* seq = letters + off[k];
+        for (int64_t p = 0; p < L; p += width) {
+            const size_t n = (size_t)(L - p < width ? L - p : width);
+            if (n + 1 > 65536) {                   // absurd line width: no buffering
+                flush();
+                ok = ok && fwrite(seq + p, 1, n, f) == n && fputc('\n', f) != EOF;
+                total += (int64_t)n + 1;
+                continue;
+            }
+            if (at + n + 1 > CAP) flush();
+            memcpy(buf.data() + at, seq + p, n); at += n; buf[at++] = '\n';
+        }
+    }
+    flush();
+    const bool closed = fclose(f) == 0;
+    if (!ok || !closed) { rcq_fail(RCQ_ERR_ARG, "rcq_fasta_write: short write"); return -1; }
+    return total;
 }

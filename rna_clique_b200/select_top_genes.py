@@ -113,8 +113,7 @@ def _parse_and_select_lean(out_dir: Path, transcripts: str, x: Path, top: int, p
     starts, lengths = off[:-1], np.diff(off)
 
     def write():
-        fa = Fasta(None, letters, off, raw, hs, he)
-        write_fasta(out, fa.header_bytes(keep), letters, starts, lengths)
+        _native.fasta_write(out, raw, hs, he, keep, letters, off)
 
     return out, x.stem, (parser, letters, starts, np.asarray(gene[keep], dtype=np.int32), np.asarray(iso[keep], dtype=np.int32),
                          lengths.astype(np.int32)), write

@@ -124,3 +124,23 @@ def test_lean_parse_equals_the_full_parse(tmp_path):
     (tmp_path / "b" / "transcripts.fasta").write_text(">NODE_1_cov_3.5_g1_i1\nACGT\n>nonsense\nACGT\n")
     with pytest.raises(TranscriptIDParseError):
         stg._parse_and_select_lean(tmp_path / "lean", "transcripts.fasta", tmp_path / "b", 1, default_parser)
+
+
+def test_native_coverage_values_equal_python_float():
+    """rcq_parse_spades_ids reads short decimals (at most 15 digits) as integer / power of ten - one correctly rounded
+    division - and longer ones with strtod: every value must be the double float() gives."""
+    from rna_clique_b200 import _native
+    rng = np.random.default_rng(5)
+    strs = []
+    for _ in range(20000):
+        d1, d2 = int(rng.integers(1, 10)), int(rng.integers(1, 12))
+        strs.append("".join(rng.choice(list("0123456789"), size=d1)) + "." + "".join(rng.choice(list("0123456789"), size=d2)))
+    strs += ["0.1", "0.3", "123456789.123456", "99999999.9999999", "1.000000000000001", "12345678901234567.123",
+             "0.000000000000001", "2.675", "1.005", "0.29999999999999999", "0.0"]
+    text = "".join(f">NODE_{i}_length_10_cov_{s}_g{i % 1000}_i{1 + i % 3}\nACGT\n" for i, s in enumerate(strs)).encode()
+    raw = np.frombuffer(text, dtype=np.uint8)
+    hs, he = _native.fasta_headers(raw)
+    cov, gene, iso, bad = _native.parse_spades_ids(raw, hs, he)
+    assert bad == -1
+    assert np.array_equal(cov, np.array([float(s) for s in strs]))
+    assert np.array_equal(gene, np.arange(len(strs)) % 1000) and np.array_equal(iso, 1 + np.arange(len(strs)) % 3)
