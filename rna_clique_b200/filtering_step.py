@@ -54,6 +54,7 @@ def close_shared_engine() -> None:
             _engine.close()
             _engine = None
     _pinned.clear()
+    _close_table_writers()
 
 
 class _PinnedPool:
@@ -108,6 +109,127 @@ class _PinnedPool:
 
 
 _pinned = _PinnedPool()
+
+
+class _TableWriters:
+    """Helper PROCESSES for the od2/ files (_od2_worker.py): frame building and pickling hold the interpreter lock, so
+    threads do not scale (seven threads write 1.5 times the tables of one) and at BASELINE configs[2] the 435 tables
+    were what the call waited for.  Each process is fed by one thread of this process: the columns go through a file
+    under /dev/shm (or the temp directory), the request through the process's stdin.  Whatever goes wrong with a
+    process, its task is finished by the feeding thread itself, so the files are always written."""
+
+    def __init__(self, n_procs: int):
+        import queue
+        import subprocess
+        import sys
+        import tempfile
+        from concurrent.futures import Future
+        self._Future = Future
+        self.q = queue.Queue()
+        self.seq = itertools.count()
+        base = "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else None
+        self.dir = tempfile.mkdtemp(prefix="rcq_od2_", dir=base)
+        self.procs, self.threads = [], []
+        pkg_parent = str(Path(__file__).resolve().parent.parent)
+        for _ in range(n_procs):
+            try:
+                p = subprocess.Popen([sys.executable, "-m", "rna_clique_b200._od2_worker"], stdin=subprocess.PIPE,
+                                     stdout=subprocess.PIPE, cwd=pkg_parent, text=True, bufsize=1)
+            except OSError:
+                break
+            self.procs.append(p)
+            t = threading.Thread(target=self._feed, args=(p,), daemon=True)
+            t.start()
+            self.threads.append(t)
+
+    def __bool__(self):
+        return bool(self.procs)
+
+    def _feed(self, proc):
+        import json
+        alive = True
+        try:
+            alive = proc.stdout.readline().strip() == "ready"       # the process has imported pandas
+        except Exception:  # noqa: BLE001
+            alive = False
+        while True:
+            item = self.q.get()
+            if item is None:
+                break
+            fut, cols, db, t1, t2, out = item
+            if not fut.set_running_or_notify_cancel():
+                continue
+            try:
+                done = False
+                if alive:
+                    try:
+                        n = len(cols["length"])
+                        block = os.path.join(self.dir, f"t{next(self.seq)}.bin")
+                        with open(block, "wb") as f:
+                            for c in _native.TABLE_COLS:
+                                f.write(np.ascontiguousarray(cols[c], dtype=np.int32).data)
+                            f.write(np.ascontiguousarray(cols["minus"], dtype=np.uint8).data)
+                            f.write(np.ascontiguousarray(cols["reverse"], dtype=np.uint8).data)
+                        proc.stdin.write(json.dumps(dict(block=block, n=n, db=[int(x) for x in db], t1=str(t1), t2=str(t2),
+                                                         out=os.path.abspath(str(out)))) + "\n")
+                        proc.stdin.flush()
+                        reply = proc.stdout.readline().strip()
+                        done = reply == "ok"
+                        if not done and not reply:
+                            alive = False                          # the process is gone
+                    except Exception:  # noqa: BLE001 - broken pipe, full disk, ...: this thread does the task itself
+                        alive = False
+                if not done:
+                    _frame_and_save(cols, db, t1, t2, out)
+                fut.set_result(None)
+            except BaseException as e:  # noqa: BLE001 - handed to whoever asks for the result
+                fut.set_exception(e)
+
+    def submit(self, cols, db, t1, t2, out):
+        fut = self._Future()
+        self.q.put((fut, cols, db, t1, t2, out))
+        return fut
+
+    def close(self):
+        import shutil
+        for _ in self.threads:
+            self.q.put(None)
+        for t in self.threads:
+            t.join(timeout=30)
+        for p in self.procs:
+            try:
+                p.stdin.close()
+                p.wait(timeout=5)
+            except Exception:  # noqa: BLE001
+                p.kill()
+        self.procs, self.threads = [], []
+        shutil.rmtree(self.dir, ignore_errors=True)
+
+
+_writers = None
+
+
+def _table_writers(workers: int):
+    """The process-wide helper processes, started at the first call that has enough host threads to feed them
+    (RCQ_TABLE_PROCS overrides the count; 0 keeps the work on threads)."""
+    global _writers
+    with _engine_lock:
+        if _writers is None:
+            want = os.environ.get("RCQ_TABLE_PROCS")
+            n = int(want) if want is not None else (min(8, workers // 2) if workers >= 4 else 0)
+            _writers = _TableWriters(n) if n > 0 else False
+            if _writers:
+                import atexit
+                atexit.register(_close_table_writers)
+        return _writers or None
+
+
+def _close_table_writers() -> None:
+    global _writers
+    with _engine_lock:
+        w, _writers = _writers, None
+    if w:
+        w.close()
 
 
 class _PriorityPool:
@@ -181,6 +303,7 @@ def filtering_step(dirs: Iterable[Path], out_dir_1: Path, out_dir_2: Path, cache
     edges = [None] * len(pairs)
     writes = [None] * len(pairs)
     host = _PriorityPool(workers)
+    writers = _table_writers(workers)        # helper processes for the od2/ files (None: the host pool does them)
     # the engine workers need the interpreter lock only for microseconds between native calls, the host pool holds it
     # for whole pandas operations: a short switch interval keeps the GPU from waiting for the lock
     import sys
@@ -267,8 +390,9 @@ def filtering_step(dirs: Iterable[Path], out_dir_1: Path, out_dir_2: Path, cache
                 split.append((t_b - t_a, time.perf_counter() - t_b))
             tables[x] = t
             edges[x] = (cols["sgene"], cols["qgene"])
-            writes[x] = host.submit(2, _frame_and_save, cols, (s1.total, s1.n_seq, s2.total, s2.n_seq),
-                                    out_paths[i], out_paths[j], table_paths[x])
+            db = (s1.total, s1.n_seq, s2.total, s2.n_seq)
+            writes[x] = (writers.submit(cols, db, out_paths[i], out_paths[j], table_paths[x]) if writers else
+                         host.submit(2, _frame_and_save, cols, db, out_paths[i], out_paths[j], table_paths[x]))
 
         eng._run_tasks(tasks, ready, run, poll=0.0005)
         t_1 = time.perf_counter()

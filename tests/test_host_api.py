@@ -131,3 +131,46 @@ def test_pinned_pool_reuses_buffers_and_falls_back_to_numpy():
     assert len(big) >= 128 << 20 and big.ctypes.data not in pool.out
     pool.put(big)
     pool.clear()
+
+
+def _fake_table(seed, n):
+    from rna_clique_b200 import _native
+    rng = np.random.default_rng(seed)
+    block = rng.integers(1, 2000, size=(len(_native.TABLE_COLS), max(n, 0))).astype(np.int32)
+    cols = {c: block[k] for k, c in enumerate(_native.TABLE_COLS)}
+    cols["length"][:] = rng.integers(200, 2100, size=n)
+    cols["nident"][:] = cols["length"] - rng.integers(0, 30, size=n)
+    cols["score"][:] = rng.integers(40, 4000, size=n)
+    cols["minus"] = rng.integers(0, 2, size=n).astype(np.uint8)
+    cols["reverse"] = (np.arange(n) % 2).astype(np.uint8)
+    return cols
+
+
+def test_table_writer_processes_write_the_files_the_threads_write(tmp_path):
+    """filtering_step._TableWriters: od2 files written by the helper processes load as the frames _frame_and_save
+    writes in-process; a helper that dies leaves its task to the feeding thread."""
+    import pandas as pd
+    from rna_clique_b200.filtering_step import _TableWriters, _frame_and_save
+    w = _TableWriters(2)
+    if not w:
+        pytest.skip("helper processes cannot be started here")
+    try:
+        db = (1_000_000, 500, 900_000, 480)
+        tabs = [_fake_table(k, n) for k, n in enumerate([5000, 1, 0, 12000, 300])]
+        futs = [w.submit(t, db, "/x/A_top.fasta", "/x/B_top.fasta", tmp_path / f"p{k}.pkl") for k, t in enumerate(tabs)]
+        for f in futs:
+            f.result(timeout=120)
+        for k, t in enumerate(tabs):
+            _frame_and_save(t, db, "/x/A_top.fasta", "/x/B_top.fasta", tmp_path / f"t{k}.pkl")
+            a, b = pd.read_pickle(tmp_path / f"p{k}.pkl"), pd.read_pickle(tmp_path / f"t{k}.pkl")
+            assert a.equals(b) and list(a.dtypes) == list(b.dtypes) and list(a.columns) == list(b.columns)
+        assert not list(Path(w.dir).iterdir())                   # the column files are gone
+        for p in w.procs:                                        # helpers gone: the feeding threads take over
+            p.kill()
+            p.wait()
+        futs = [w.submit(tabs[0], db, "/x/A_top.fasta", "/x/B_top.fasta", tmp_path / f"q{k}.pkl") for k in range(4)]
+        for f in futs:
+            f.result(timeout=120)
+        assert pd.read_pickle(tmp_path / "q3.pkl").equals(pd.read_pickle(tmp_path / "t0.pkl"))
+    finally:
+        w.close()
