@@ -217,11 +217,16 @@ def _table_writers(workers: int):
         if _writers is None:
             want = os.environ.get("RCQ_TABLE_PROCS")
             n = int(want) if want is not None else (min(8, workers // 2) if workers >= 4 else 0)
-            _writers = _TableWriters(n) if n > 0 else False
-            if _writers:
-                import atexit
-                atexit.register(_close_table_writers)
-        return _writers or None
+            if n <= 0:
+                return None                   # this call keeps the work on its threads; a later call may start them
+            w = _TableWriters(n)
+            if not w:
+                w.close()
+                return None
+            _writers = w
+            import atexit
+            atexit.register(_close_table_writers)
+        return _writers
 
 
 def _close_table_writers() -> None:
