@@ -5,14 +5,16 @@ The reference runs three joblib stages one after the other (select_top_and_save 
 makeblastdb per sample and blastn per pair inside find_all_pairs :144-156, build_graph :157).  Here they are
 one dependency-driven schedule on the multi-stream engine (engine.Engine._run_tasks):
 
-  host pool (up to `jobs` threads)    read + parse + select + write od1/<sample>_top.fasta   (native, GIL released)
+  host pool (up to `jobs` threads)    map the file, decode ids, select, extract the selected records into page-locked
+                                       memory; write od1/<sample>_top.fasta  (native, GIL released; parses are served first)
   engine workers (one per CUDA stream) upload sample k as soon as its records exist (pack, DUST, seed index),
                                        search pair (i, j) as soon as both samples are resident, download the table
-  host pool again                      table -> DataFrame -> od2/<S1>--<S2>.<ext>, while later pairs search
+  helper processes (_od2_worker.py)    table -> DataFrame -> od2/<S1>--<S2>.<ext>, while later pairs search (pandas and
+                                       pickle hold the interpreter lock: processes, not threads)
 
-and the device tables stay resident: the graph is built from their gene columns, graph.pkl is prepared on the device
-(node numbering, distinct edges, adjacency lists) and only serialised on the host, and SampleSimilarity reduces the device tables directly (rcq_phase2_tables) instead
-of reading od2/ back."""
+and the device tables stay resident: graph.pkl is prepared on the device (node numbering, distinct edges, adjacency
+lists) and only serialised on the host, and SampleSimilarity reduces the device tables directly (rcq_phase2_tables)
+instead of reading od2/ back."""
 from __future__ import annotations
 
 import itertools
@@ -43,7 +45,8 @@ def shared_engine(jobs: Optional[int] = None, device: int = 0):
     from .engine import Engine
     with _engine_lock:
         if _engine is None:
-            _engine = Engine(device, streams=max(2, min(6, int(jobs or 4))))
+            want = os.environ.get("RCQ_API_STREAMS")
+            _engine = Engine(device, streams=int(want) if want else max(2, min(6, int(jobs or 4))))
         return _engine
 
 
