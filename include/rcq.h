@@ -108,7 +108,9 @@ int rcq_graph_pickle_groups(const char* path, int32_t n_samples, const char* con
  * tables' (sgene, qgene) columns, with node numbering, duplicate rows, adjacency lists and memo numbers computed on
  * the GPU and only the byte stream produced on the host.  tables[t] joins samples t_s[t] (sgene) and t_q[t]
  * (qgene).  Returns RCQ_ERR_ARG when a table is not ordered by (qgene, sgene) or two tables join the same two
- * samples, RCQ_ERR_CAPACITY for 2^31 rows or gene ids too sparse for dense tables: use the host writer then. */
+ * samples, RCQ_ERR_CAPACITY for 2^31 rows or gene ids too sparse for dense tables: use the host writer then.
+ * The arrays reach the host through ctx's page-locked staging, which grows to 16 bytes per node + 8 bytes per
+ * adjacency entry (0.35 GB at BASELINE configs[2]) and is kept until rcq_ctx_destroy. */
 int rcq_graph_pickle_tables(rcq_ctx* ctx, const char* path, int32_t n_samples, const char* const* sample_names,
                             int32_t n_tables, const rcq_table* const* tables, const int32_t* t_s, const int32_t* t_q,
                             int64_t counts[3]);
